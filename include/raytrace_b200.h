@@ -1,0 +1,190 @@
+/* raytrace_b200.h -- C ABI of the B200-native tracing path (libraytrace_b200.so).
+ *
+ * This is the drop-in boundary for the per-pixel tracing hot path of j-dong/rust-raytrace.  The upstream crate
+ * has no FFI; its boundary is the public Rust API of `lib.rs` (src/lib.rs:4-13) and the call sequence of the
+ * `raytrace` binary (src/main.rs:13-60).  Every entry point below names the upstream item it replaces.
+ * INTEGRATION.md shows the `extern "C"` block a maintainer of the Rust crate would add to bind these.
+ *
+ * Conventions
+ *   - plain C types only; all vectors/colours are `const double[3]` (x,y,z / r,g,b);
+ *   - every function that can fail returns 0 on success or a negative rt_status; rt_last_error() returns a
+ *     thread-local message for the last failure on the calling thread;
+ *   - a scene (rt_scene) is host-side, mutable until it is handed to rt_context_create / rt_render; the library
+ *     copies every array it is given (caller keeps ownership of its inputs);
+ *   - a context (rt_context) owns the device-resident copy of one scene on one GPU (flattened primitives,
+ *     device-built BVH, ray queues, accumulators); one render at a time per context;
+ *   - there is NO CPU fallback: without a CUDA device every render/trace entry point fails with RT_ERR_CUDA.
+ */
+#ifndef RAYTRACE_B200_H
+#define RAYTRACE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_API __attribute__((visibility("default")))
+
+typedef enum rt_status {
+    RT_OK = 0,
+    RT_ERR_INVALID = -1, /* bad argument / scene incomplete */
+    RT_ERR_SYNTAX = -2,  /* rt_scene_parse: message is the reference's `row:col: msg` */
+    RT_ERR_IO = -3,      /* file open/read/write */
+    RT_ERR_CUDA = -4,    /* no device, allocation or launch failure */
+    RT_ERR_UNSUPPORTED = -5
+} rt_status;
+
+typedef struct rt_scene rt_scene;
+typedef struct rt_context rt_context;
+
+/* ---------------------------------------------------------------------------------------------------------
+ * library
+ * ------------------------------------------------------------------------------------------------------- */
+RT_API const char* rt_last_error(void);
+RT_API const char* rt_version(void);
+/* number of visible CUDA devices (0 when there is none; never an error) */
+RT_API int rt_device_count(void);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * scene construction  (replaces the `pub` structs of src/scene.rs:32-212, src/shapes.rs:43-98)
+ * ------------------------------------------------------------------------------------------------------- */
+RT_API rt_scene* rt_scene_new(void);
+RT_API void rt_scene_free(rt_scene* scene);
+
+/* serialize::deserialize (src/serialize.rs:427-441).  On RT_ERR_SYNTAX `err` receives "row:col: message" exactly
+ * as upstream's `impl Display for SyntaxError` (src/serialize.rs:268-272).  Warnings that upstream println!s
+ * (src/serialize.rs:452,455,464) are appended to the scene's warning log, see rt_scene_warnings. */
+RT_API int rt_scene_parse(const char* text, size_t len, rt_scene** out, char* err, size_t errcap);
+RT_API int rt_scene_parse_file(const char* path, rt_scene** out, char* err, size_t errcap);
+RT_API const char* rt_scene_warnings(const rt_scene* scene);
+
+/* materials (src/scene.rs:32-89); each returns the new material's index (>= 0) or a negative rt_status */
+RT_API int rt_scene_add_material_phong(rt_scene*, const double diffuse[3], const double specular[3], double exponent,
+                                       const double ambient[3]);
+RT_API int rt_scene_add_material_indirect(rt_scene*, const double diffuse[3], const double specular[3], double exponent,
+                                          const double ambient[3], uint32_t samples);
+RT_API int rt_scene_add_material_fresnel(rt_scene*, const double diffuse[3], const double specular[3], double exponent,
+                                         const double ambient[3], double ior);
+RT_API int rt_scene_add_material_transparent(rt_scene*, const double specular[3], double exponent, double ior);
+
+/* objects (src/scene.rs:93-98, src/shapes.rs:43-48, :93-98).  Object index = order of insertion, as in
+ * `Scene.objects`; it is the id reported for primary hits and the tie-break of the closest-hit search. */
+RT_API int rt_scene_add_spheres(rt_scene*, uint64_t n, const double* center_xyz_radius /* 4n */, const uint32_t* material /* n */);
+RT_API int rt_scene_add_plane(rt_scene*, const double point[3], const double normal[3], uint32_t material);
+
+/* lights (src/scene.rs:109-155) */
+RT_API int rt_scene_add_light_point(rt_scene*, const double location[3], const double color[3]);
+RT_API int rt_scene_add_light_directional(rt_scene*, const double direction[3], const double color[3]);
+RT_API int rt_scene_add_light_area(rt_scene*, const double origin[3], const double side1[3], const double side2[3],
+                                   const double color[3]);
+
+/* cameras: SimplePerspectiveCamera::new (src/camera.rs:51-63), ::look_at (:67-73), DepthOfFieldCamera::new (:97-106).
+ * rt_scene_set_camera_dof wraps the perspective camera that is currently set. */
+RT_API int rt_scene_set_camera_spc_new(rt_scene*, const double position[3], const double look[3], const double up[3], double im_dist);
+RT_API int rt_scene_set_camera_spc_look_at(rt_scene*, const double focus[3], const double look[3], const double up[3], double pov_rad,
+                                           double h);
+RT_API int rt_scene_set_camera_dof(rt_scene*, double focus, double aperture, uint32_t samples);
+RT_API int rt_scene_get_camera(const rt_scene*, double position[3], double matrix_rowmajor[9]);
+
+/* backgrounds (src/scene.rs:165-188).  Skybox faces are RGB8, row 0 = top row of the decoded image
+ * (what `image::open(..).to_rgb().into_raw()` yields, src/texture.rs:34-37); face order px nx py ny pz nz. */
+RT_API int rt_scene_set_background_solid(rt_scene*, const double color[3]);
+RT_API int rt_scene_set_skybox_face(rt_scene*, int face, uint32_t width, uint32_t height, const uint8_t* rgb);
+/* Texture::load (src/texture.rs:34-37) for the formats decodable without the `image` crate: 24-bit BMP, binary PPM */
+RT_API int rt_scene_load_skybox_face(rt_scene*, int face, const char* path);
+
+/* Options (src/scene.rs:191-198) */
+RT_API int rt_scene_set_options(rt_scene*, uint32_t width, uint32_t height, uint32_t antialias);
+RT_API int rt_scene_get_options(const rt_scene*, uint32_t* width, uint32_t* height, uint32_t* antialias);
+
+/* introspection (parser tests): counts and a canonical text dump of everything the scene holds */
+typedef struct rt_scene_info {
+    uint64_t n_objects, n_spheres, n_planes, n_materials, n_lights;
+    int32_t camera_kind;     /* 0 = SimplePerspectiveCamera, 1 = DepthOfFieldCamera */
+    int32_t background_kind; /* 0 = solid, 1 = skybox */
+} rt_scene_info;
+RT_API int rt_scene_get_info(const rt_scene*, rt_scene_info* info);
+/* writes a NUL-terminated dump (hex-float numbers, one item per line) of at most cap-1 bytes; returns the full length */
+RT_API size_t rt_scene_dump(const rt_scene*, char* buf, size_t cap);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * rendering  (replaces src/main.rs:39-59 and everything below it: src/raytrace.rs, Scene::intersect, ...)
+ * ------------------------------------------------------------------------------------------------------- */
+enum { RT_ACCEL_AUTO = 0, RT_ACCEL_LINEAR = 1, RT_ACCEL_BVH = 2 };
+enum { RT_FP_STRICT = 0, RT_FP_FAST = 1 };
+
+typedef struct rt_render_opts {
+    uint32_t width, height;    /* 0 = take from the scene's Options */
+    uint32_t antialias;        /* 0xFFFFFFFF = take from the scene's Options (0 is a legal upstream value: NaN -> 255) */
+    uint32_t max_depth;        /* upstream const MAX_DEPTH = 4 (src/raytrace.rs:18) */
+    double min_significance;   /* upstream const MIN_SIGNIFICANCE = 1/512 (src/raytrace.rs:17) */
+    uint64_t seed;             /* counter RNG seed (DESIGN.md "RNG") */
+    int32_t accel;             /* RT_ACCEL_*: AUTO = BVH when the scene has >= 64 spheres */
+    int32_t fp_mode;           /* RT_FP_STRICT: no FMA contraction (bit-parity with the reference's op order); RT_FP_FAST */
+    int32_t device;            /* CUDA device ordinal */
+    int32_t rank, world;       /* image-space shard: this context renders the row bands b with b % world == rank */
+    uint32_t band_rows;        /* rows per band (multiple of 4); 0 = default (4) */
+    uint64_t max_rays_in_flight; /* ray-queue capacity per wavefront level; 0 = default */
+} rt_render_opts;
+RT_API void rt_render_opts_default(rt_render_opts* opts);
+
+typedef struct rt_stats {
+    uint64_t rays_total;      /* closest-hit + shadow queries = Scene::intersect calls upstream (src/scene.rs:247) */
+    uint64_t rays_primary, rays_secondary, rays_shadow;
+    uint64_t paths;           /* pixel samples x camera samples traced by this context */
+    uint64_t kernel_launches; /* kernels of this library launched by the last render */
+    double render_ms;         /* device time of the last render (CUDA events on the context's stream) */
+    double bvh_build_ms;      /* device time of the BVH build at context creation */
+    uint64_t n_bvh_nodes;
+    uint32_t local_rows;      /* rows this shard produces (padded to whole bands) */
+    uint32_t bytewidth;       /* bytes per output row = (3*width + 3) & ~3 (src/bmp.rs:11) */
+    int32_t accel_used, fp_mode_used;
+} rt_stats;
+
+/* One-call frame render: upload, (build BVH), trace, resolve, copy back.
+ *   bgr_rows     host buffer of bytewidth*height bytes; row 0 is y = 0, i.e. BMP bottom-up order (src/main.rs:45-58)
+ *   primary_ids  optional host buffer of width*height int32: object index hit by the first sample's primary ray, -1 = miss
+ *   accum        optional host buffer of width*height*3 doubles: per-pixel SUM of the sample colours in linear RGB;
+ *                the value handed to the quantiser (src/main.rs:56) is (accum / camera_samples) / antialias
+ * Requires world == 1 in opts. */
+RT_API int rt_render(const rt_scene*, const rt_render_opts*, uint8_t* bgr_rows, int32_t* primary_ids, double* accum, rt_stats* stats);
+
+/* Device-resident path (bench / multi-GPU): the scene and all buffers stay in HBM between frames. */
+RT_API int rt_context_create(const rt_scene*, const rt_render_opts*, rt_context** out);
+RT_API void rt_context_destroy(rt_context*);
+/* traces the shard and leaves quantised BGR rows (local_rows x bytewidth) in the context's device framebuffer */
+RT_API int rt_context_render(rt_context*, rt_stats* stats);
+RT_API int rt_context_stats(const rt_context*, rt_stats* stats);
+/* device pointer of the local framebuffer (local_rows*bytewidth bytes), e.g. to wrap as a tensor for the NCCL gather */
+RT_API void* rt_context_framebuffer(rt_context*);
+RT_API size_t rt_context_framebuffer_bytes(const rt_context*);
+/* copies the local framebuffer / ids / accumulators to host memory (shard-local row order) */
+RT_API int rt_context_download(rt_context*, uint8_t* bgr_rows, int32_t* primary_ids, double* accum);
+/* After an all-gather of every rank's local framebuffer (rank-major, world*local_rows*bytewidth bytes, device memory)
+ * writes the final bytewidth*height image in BMP row order into `out_dev`.  Runs on the context's device/stream. */
+RT_API int rt_context_untile(rt_context*, const void* gathered_dev, void* out_dev);
+RT_API int rt_context_synchronize(rt_context*);
+
+/* Scene::intersect for a batch of rays (src/scene.rs:247-249): origin xyz + direction xyz per ray.
+ * ids: object index or -1; t: hit distance (+inf on miss); normal: shape normal as upstream returns it. */
+RT_API int rt_trace_rays(const rt_scene*, const rt_render_opts*, uint64_t n, const double* origin_dir, int32_t* ids, double* t,
+                         double* normal);
+/* Camera::project for a batch of normalised image positions (src/camera.rs:77-79, :110-121); ray i uses the
+ * counter-RNG key of (seed, pixel i, sample 0, camera sample 0). */
+RT_API int rt_project(const rt_scene*, const rt_render_opts*, uint64_t n, const double* pos_xy, double* origin_dir);
+/* Color::write_bgr over n colours (src/color.rs:593-600, :628-632), on the device */
+RT_API int rt_quantize_bgr(const double* rgb, uint64_t n, uint8_t* bgr, int device);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * BMP sink  (src/bmp.rs:10-61 + the row writes of src/main.rs:42,58)
+ * ------------------------------------------------------------------------------------------------------- */
+RT_API uint32_t rt_bmp_bytewidth(uint32_t width);
+RT_API void rt_bmp_header(uint32_t width, uint32_t height, uint8_t out122[122]);
+RT_API int rt_bmp_write(const char* path, uint32_t width, uint32_t height, const uint8_t* rows);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RAYTRACE_B200_H */

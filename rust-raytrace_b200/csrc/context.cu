@@ -1,0 +1,506 @@
+// context.cu -- device-resident scene + the host driver of the wavefront (replaces the frame loop of
+// src/main.rs:39-59 and the recursion of src/raytrace.rs:261-276).
+//
+// The recursion `ray_color -> material.color -> ray_color` becomes a stack of ray queues, one per depth.
+// A level is processed in slices small enough that whatever the slice spawns fits the next level's queue and
+// the shadow queue, so memory is bounded for any branching factor (TransparentMaterial doubles, IndirectPhong
+// multiplies by `samples`):
+//
+//   process(level d, n rays):  for each slice:  closest-hit -> shade (emits shadow rays + level d+1 rays)
+//                                               -> shadow kernel -> process(level d+1)
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/raytrace_b200.h"
+#include "host_scene.h"
+#include "kernels.h"
+
+using namespace rt;
+
+#define CUDA_TRY(expr)                                                                                     \
+    do {                                                                                                   \
+        cudaError_t e_ = (expr);                                                                           \
+        if (e_ != cudaSuccess) {                                                                           \
+            set_error(std::string(#expr) + ": " + cudaGetErrorString(e_));                                 \
+            return RT_ERR_CUDA;                                                                            \
+        }                                                                                                  \
+    } while (0)
+
+namespace {
+
+template <typename T>
+int dev_alloc(T** p, size_t count) {
+    *p = nullptr;
+    if (count == 0) return RT_OK;
+    CUDA_TRY(cudaMalloc((void**)p, count * sizeof(T)));
+    return RT_OK;
+}
+template <typename T>
+int dev_upload(T** p, const std::vector<T>& v) {
+    int rc = dev_alloc(p, v.size());
+    if (rc != RT_OK) return rc;
+    if (!v.empty()) CUDA_TRY(cudaMemcpy(*p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+    return RT_OK;
+}
+
+// device copy of a scene: flattened buffers + optional BVH
+struct DeviceSceneHolder {
+    DeviceScene ds{};
+    std::vector<void*> allocs;
+    BvhBuildResult bvh{};
+    bool use_bvh = false;
+    double bvh_ms = 0.0;
+    uint32_t build_launches = 0;
+
+    ~DeviceSceneHolder() { release(); }
+    void release() {
+        for (void* p : allocs) cudaFree(p);
+        allocs.clear();
+        bvh_free(&bvh);
+    }
+    template <typename T>
+    int up(const std::vector<T>& v, const T** out) {
+        T* p = nullptr;
+        int rc = dev_upload(&p, v);
+        if (rc != RT_OK) return rc;
+        if (p) allocs.push_back(p);
+        *out = p;
+        return RT_OK;
+    }
+
+    int init(const rt_scene* s, int accel, cudaStream_t st) {
+        FlatScene f;
+        int rc = flatten_scene(s, &f);
+        if (rc != RT_OK) return rc;
+        fill_scene_header(s, f, &ds);
+        const double* clo = f.centroid_lo;
+        const double* chi = f.centroid_hi;
+        if ((rc = up(f.sph, &ds.sph)) != RT_OK) return rc;
+        if ((rc = up(f.sph_obj, &ds.sph_obj)) != RT_OK) return rc;
+        if ((rc = up(f.planes, &ds.planes)) != RT_OK) return rc;
+        if ((rc = up(f.obj_shape, &ds.obj_shape)) != RT_OK) return rc;
+        if ((rc = up(f.obj_material, &ds.obj_material)) != RT_OK) return rc;
+        if ((rc = up(s->materials, &ds.materials)) != RT_OK) return rc;
+        if ((rc = up(s->lights, &ds.lights)) != RT_OK) return rc;
+        if (s->bg_kind == BG_SKYBOX)
+            for (int k = 0; k < 6; k++) {
+                const uint8_t* p = nullptr;
+                if ((rc = up(s->faces[k].data, &p)) != RT_OK) return rc;
+                ds.faces[k].data = p;
+            }
+        std::vector<double> vals(SRGB_VALUES, SRGB_VALUES + 256), avg(SRGB_AVERAGE, SRGB_AVERAGE + 255);
+        if ((rc = up(vals, &ds.srgb_values)) != RT_OK) return rc;
+        if ((rc = up(avg, &ds.srgb_average)) != RT_OK) return rc;
+        use_bvh = accel_uses_bvh(accel, ds.n_spheres);
+        if (use_bvh) {
+            cudaEvent_t e0, e1;
+            CUDA_TRY(cudaEventCreate(&e0));
+            CUDA_TRY(cudaEventCreate(&e1));
+            CUDA_TRY(cudaEventRecord(e0, st));
+            cudaError_t e = bvh_build(st, ds.sph, ds.sph_obj, ds.n_spheres, clo, chi, &bvh);
+            if (e != cudaSuccess) { set_error(std::string("bvh_build: ") + cudaGetErrorString(e)); return RT_ERR_CUDA; }
+            CUDA_TRY(cudaEventRecord(e1, st));
+            CUDA_TRY(cudaEventSynchronize(e1));
+            float ms = 0;
+            cudaEventElapsedTime(&ms, e0, e1);
+            bvh_ms = ms;
+            cudaEventDestroy(e0); cudaEventDestroy(e1);
+            ds.bvh_nodes = bvh.nodes; ds.bvh_sph = bvh.sph; ds.bvh_obj = bvh.obj; ds.n_bvh_nodes = bvh.n_nodes;
+            build_launches = bvh.launches;
+        }
+        return RT_OK;
+    }
+};
+
+int alloc_ray_queue(RayQueue* q, uint32_t cap, std::vector<void*>* allocs, bool full) {
+    std::memset(q, 0, sizeof *q);
+    q->cap = cap;
+    if (cap == 0) return RT_OK;
+    const size_t c = cap;
+    const size_t n_d = full ? 11 : 7;  // doubles per ray: o, d, (T, sig), hit_t
+    const size_t bytes = c * (n_d * 8 + (full ? 8 + 4 + 4 : 0) + 4);
+    unsigned char* base = nullptr;
+    CUDA_TRY(cudaMalloc((void**)&base, bytes));
+    allocs->push_back(base);
+    double* d = (double*)base;
+    q->ox = d; q->oy = d + c; q->oz = d + 2 * c; q->dx = d + 3 * c; q->dy = d + 4 * c; q->dz = d + 5 * c;
+    q->hit_t = d + 6 * c;
+    unsigned char* p = (unsigned char*)(d + 7 * c);
+    if (full) {
+        q->tr = d + 7 * c; q->tg = d + 8 * c; q->tb = d + 9 * c; q->sig = d + 10 * c;
+        q->key = (uint64_t*)(d + 11 * c);
+        p = (unsigned char*)(q->key + c);
+        q->pixel = (uint32_t*)p; p += 4 * c;
+        q->meta = (uint32_t*)p; p += 4 * c;
+    }
+    q->hit_id = (int32_t*)p;
+    return RT_OK;
+}
+
+int alloc_shadow_queue(ShadowQueue* q, uint32_t cap, std::vector<void*>* allocs) {
+    std::memset(q, 0, sizeof *q);
+    q->cap = cap;
+    if (cap == 0) return RT_OK;
+    const size_t c = cap;
+    unsigned char* base = nullptr;
+    CUDA_TRY(cudaMalloc((void**)&base, c * (10 * 8 + 4)));
+    allocs->push_back(base);
+    double* d = (double*)base;
+    q->ox = d; q->oy = d + c; q->oz = d + 2 * c; q->dx = d + 3 * c; q->dy = d + 4 * c; q->dz = d + 5 * c;
+    q->r2 = d + 6 * c; q->cr = d + 7 * c; q->cg = d + 8 * c; q->cb = d + 9 * c;
+    q->pixel = (uint32_t*)(d + 10 * c);
+    return RT_OK;
+}
+
+}  // namespace
+
+struct rt_context {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int sm_count = 148;
+    DeviceSceneHolder scene;
+    const KernelTable* k = nullptr;
+    FrameParams fp{};
+    rt_render_opts opts{};
+    uint32_t bytewidth = 0;
+    std::vector<void*> allocs;
+    std::vector<RayQueue> levels;
+    ShadowQueue shadowq{};
+    RayQueue null_queue{};
+    Counters* counters = nullptr;       // device
+    Counters* counters_host = nullptr;  // pinned
+    double* accum = nullptr;
+    int32_t* ids = nullptr;
+    uint8_t* framebuffer = nullptr;
+    size_t fb_bytes = 0;
+    uint32_t slice = 0;
+    uint64_t total_paths = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    rt_stats stats{};
+
+    ~rt_context() {
+        cudaSetDevice(device);
+        for (void* p : allocs) cudaFree(p);
+        if (counters_host) cudaFreeHost(counters_host);
+        if (ev0) cudaEventDestroy(ev0);
+        if (ev1) cudaEventDestroy(ev1);
+        scene.release();
+        if (stream) cudaStreamDestroy(stream);
+    }
+};
+
+namespace {
+
+int ctx_fetch_counters(rt_context* c) {
+    CUDA_TRY(cudaMemcpyAsync(c->counters_host, c->counters, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    if (c->counters_host->overflow) { set_error("internal error: ray queue overflow"); return RT_ERR_CUDA; }
+    return RT_OK;
+}
+
+int process_level(rt_context* c, uint32_t d, uint32_t n) {
+    const bool last = d + 1 >= c->levels.size();
+    RayQueue& in = c->levels[d];
+    RayQueue& out = last ? c->null_queue : c->levels[d + 1];
+    uint32_t* next_count = &c->counters->level_count[last ? 63 : d + 1];
+    for (uint32_t first = 0; first < n; first += c->slice) {
+        const uint32_t cnt = std::min(c->slice, n - first);
+        c->k->closest(c->stream, c->scene.ds, c->scene.use_bvh, in, first, cnt, &c->counters->cursor, c->sm_count);
+        CUDA_TRY(cudaMemsetAsync(next_count, 0, sizeof(uint32_t), c->stream));
+        CUDA_TRY(cudaMemsetAsync(&c->counters->shadow_count, 0, sizeof(uint32_t), c->stream));
+        c->k->shade(c->stream, c->scene.ds, c->fp, in, first, cnt, out, next_count, c->shadowq, &c->counters->shadow_count, &c->counters->overflow,
+                    c->accum, c->ids);
+        c->stats.kernel_launches += 2 + (c->scene.use_bvh ? 0 : 0);
+        int rc = ctx_fetch_counters(c);
+        if (rc != RT_OK) return rc;
+        const uint32_t n_shadow = c->counters_host->shadow_count;
+        const uint32_t n_next = last ? 0 : c->counters_host->level_count[d + 1];
+        if (d == 0) c->stats.rays_primary += cnt; else c->stats.rays_secondary += cnt;
+        c->stats.rays_shadow += n_shadow;
+        if (n_shadow) {
+            c->k->shadow(c->stream, c->scene.ds, c->scene.use_bvh, c->shadowq, n_shadow, c->accum, &c->counters->cursor, c->sm_count);
+            c->stats.kernel_launches += 1;
+        }
+        if (n_next) {
+            rc = process_level(c, d + 1, n_next);
+            if (rc != RT_OK) return rc;
+        }
+    }
+    return RT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rt_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int rt_context_create(const rt_scene* s, const rt_render_opts* o, rt_context** out) {
+    if (!s || !o || !out) { set_error("rt_context_create: null argument"); return RT_ERR_INVALID; }
+    *out = nullptr;
+    if (rt_device_count() <= 0) { set_error("no CUDA device: this library has no CPU fallback"); return RT_ERR_CUDA; }
+    rt_context* c = new rt_context();
+    c->device = o->device;
+    c->opts = *o;
+    auto fail = [&](int rc) { delete c; return rc; };
+    if (cudaSetDevice(o->device) != cudaSuccess) { set_error("cudaSetDevice failed"); return fail(RT_ERR_CUDA); }
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { set_error("cudaStreamCreate failed"); return fail(RT_ERR_CUDA); }
+    cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, o->device);
+    c->k = o->fp_mode == RT_FP_FAST ? kernels_fast() : kernels_strict();
+    int rc = c->scene.init(s, o->accel, c->stream);
+    if (rc != RT_OK) return fail(rc);
+
+    FrameParams& fp = c->fp;
+    if ((rc = make_frame_params(s, o, &fp)) != RT_OK) return fail(rc);
+    c->bytewidth = rt_bmp_bytewidth(fp.width);
+    c->total_paths = fp.npix_padded * fp.antialias * fp.cam_samples;
+
+    // queue sizing
+    const uint32_t branch = (uint32_t)std::max(1, c->scene.ds.max_children);
+    const uint32_t lights = std::max(1u, c->scene.ds.n_lights);
+    uint64_t cap = o->max_rays_in_flight ? o->max_rays_in_flight : (1ull << 24);
+    const uint64_t want = std::max<uint64_t>(c->total_paths * branch, 1024);
+    cap = std::min(cap, want);
+    cap = std::max<uint64_t>(cap, (uint64_t)branch * 32);
+    cap = (cap + 1023) & ~1023ull;
+    const uint64_t shadow_cap = std::min<uint64_t>(cap * 2, (std::max<uint64_t>(c->total_paths * lights, 1024) + 1023) & ~1023ull);
+    c->slice = (uint32_t)std::max<uint64_t>(32, std::min<uint64_t>(cap / branch, shadow_cap / lights));
+    const uint32_t n_levels = fp.max_depth + 2;
+    c->levels.resize(n_levels);
+    for (uint32_t d = 0; d < n_levels; d++)
+        if ((rc = alloc_ray_queue(&c->levels[d], (uint32_t)cap, &c->allocs, true)) != RT_OK) return fail(rc);
+    if ((rc = alloc_shadow_queue(&c->shadowq, (uint32_t)shadow_cap, &c->allocs)) != RT_OK) return fail(rc);
+    std::memset(&c->null_queue, 0, sizeof c->null_queue);
+
+    const size_t npix = (size_t)fp.local_rows * fp.width;
+    c->fb_bytes = (size_t)fp.local_rows * c->bytewidth;
+    if ((rc = dev_alloc(&c->accum, npix * 3)) != RT_OK) return fail(rc);
+    c->allocs.push_back(c->accum);
+    if ((rc = dev_alloc(&c->ids, npix)) != RT_OK) return fail(rc);
+    c->allocs.push_back(c->ids);
+    if ((rc = dev_alloc(&c->framebuffer, c->fb_bytes + 16)) != RT_OK) return fail(rc);
+    c->allocs.push_back(c->framebuffer);
+    if ((rc = dev_alloc(&c->counters, 1)) != RT_OK) return fail(rc);
+    c->allocs.push_back(c->counters);
+    if (cudaMallocHost((void**)&c->counters_host, sizeof(Counters)) != cudaSuccess) { set_error("cudaMallocHost failed"); return fail(RT_ERR_CUDA); }
+    if (cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess) { set_error("cudaEventCreate failed"); return fail(RT_ERR_CUDA); }
+    std::memset(&c->stats, 0, sizeof c->stats);
+    c->stats.bvh_build_ms = c->scene.bvh_ms;
+    c->stats.n_bvh_nodes = c->scene.ds.n_bvh_nodes;
+    c->stats.local_rows = fp.local_rows;
+    c->stats.bytewidth = c->bytewidth;
+    c->stats.accel_used = c->scene.use_bvh ? RT_ACCEL_BVH : RT_ACCEL_LINEAR;
+    c->stats.fp_mode_used = o->fp_mode == RT_FP_FAST ? RT_FP_FAST : RT_FP_STRICT;
+    *out = c;
+    return RT_OK;
+}
+
+void rt_context_destroy(rt_context* c) { delete c; }
+
+int rt_context_render(rt_context* c, rt_stats* stats) {
+    if (!c) { set_error("null context"); return RT_ERR_INVALID; }
+    CUDA_TRY(cudaSetDevice(c->device));
+    const FrameParams& fp = c->fp;
+    const size_t npix = (size_t)fp.local_rows * fp.width;
+    c->stats.rays_total = c->stats.rays_primary = c->stats.rays_secondary = c->stats.rays_shadow = 0;
+    c->stats.kernel_launches = 0;
+    c->stats.paths = 0;
+    CUDA_TRY(cudaEventRecord(c->ev0, c->stream));
+    CUDA_TRY(cudaMemsetAsync(c->accum, 0, npix * 3 * sizeof(double), c->stream));
+    CUDA_TRY(cudaMemsetAsync(c->ids, 0xFF, npix * sizeof(int32_t), c->stream));
+    CUDA_TRY(cudaMemsetAsync(c->counters, 0, sizeof(Counters), c->stream));
+    const uint64_t batch = c->levels[0].cap;
+    for (uint64_t base = 0; base < c->total_paths; base += batch) {
+        const uint32_t n = (uint32_t)std::min<uint64_t>(batch, c->total_paths - base);
+        CUDA_TRY(cudaMemsetAsync(&c->counters->level_count[0], 0, sizeof(uint32_t), c->stream));
+        c->k->primary(c->stream, c->scene.ds, fp, c->levels[0], &c->counters->level_count[0], &c->counters->overflow, base, n);
+        c->stats.kernel_launches += 1;
+        int rc = ctx_fetch_counters(c);
+        if (rc != RT_OK) return rc;
+        const uint32_t n0 = c->counters_host->level_count[0];
+        c->stats.paths += n0;
+        if (n0) {
+            rc = process_level(c, 0, n0);
+            if (rc != RT_OK) return rc;
+        }
+    }
+    c->k->resolve(c->stream, c->scene.ds, fp, c->accum, c->framebuffer, c->bytewidth);
+    c->stats.kernel_launches += 1;
+    CUDA_TRY(cudaEventRecord(c->ev1, c->stream));
+    CUDA_TRY(cudaEventSynchronize(c->ev1));
+    CUDA_TRY(cudaGetLastError());
+    float ms = 0;
+    CUDA_TRY(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    c->stats.render_ms = ms;
+    c->stats.rays_total = c->stats.rays_primary + c->stats.rays_secondary + c->stats.rays_shadow;
+    if (stats) *stats = c->stats;
+    return RT_OK;
+}
+
+int rt_context_stats(const rt_context* c, rt_stats* stats) {
+    if (!c || !stats) { set_error("null argument"); return RT_ERR_INVALID; }
+    *stats = c->stats;
+    return RT_OK;
+}
+
+void* rt_context_framebuffer(rt_context* c) { return c ? c->framebuffer : nullptr; }
+size_t rt_context_framebuffer_bytes(const rt_context* c) { return c ? c->fb_bytes : 0; }
+
+int rt_context_download(rt_context* c, uint8_t* bgr_rows, int32_t* primary_ids, double* accum) {
+    if (!c) { set_error("null context"); return RT_ERR_INVALID; }
+    CUDA_TRY(cudaSetDevice(c->device));
+    const size_t npix = (size_t)c->fp.local_rows * c->fp.width;
+    if (bgr_rows) CUDA_TRY(cudaMemcpyAsync(bgr_rows, c->framebuffer, c->fb_bytes, cudaMemcpyDeviceToHost, c->stream));
+    if (primary_ids) CUDA_TRY(cudaMemcpyAsync(primary_ids, c->ids, npix * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    if (accum) CUDA_TRY(cudaMemcpyAsync(accum, c->accum, npix * 3 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+int rt_context_untile(rt_context* c, const void* gathered_dev, void* out_dev) {
+    if (!c || !gathered_dev || !out_dev) { set_error("null argument"); return RT_ERR_INVALID; }
+    CUDA_TRY(cudaSetDevice(c->device));
+    launch_untile(c->stream, (const uint32_t*)gathered_dev, (uint32_t*)out_dev, c->fp.height, c->bytewidth / 4, c->fp.band_rows, c->fp.world,
+                  c->fp.local_rows);
+    CUDA_TRY(cudaGetLastError());
+    return RT_OK;
+}
+
+int rt_context_synchronize(rt_context* c) {
+    if (!c) { set_error("null context"); return RT_ERR_INVALID; }
+    CUDA_TRY(cudaSetDevice(c->device));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+int rt_render(const rt_scene* s, const rt_render_opts* o, uint8_t* bgr_rows, int32_t* primary_ids, double* accum, rt_stats* stats) {
+    if (!s || !o) { set_error("rt_render: null argument"); return RT_ERR_INVALID; }
+    if (o->world != 1) { set_error("rt_render renders whole frames: world must be 1 (use rt_context_* for shards)"); return RT_ERR_INVALID; }
+    rt_context* c = nullptr;
+    int rc = rt_context_create(s, o, &c);
+    if (rc != RT_OK) return rc;
+    rc = rt_context_render(c, stats);
+    if (rc == RT_OK) {
+        // world == 1: local rows are the image rows (plus band padding at the end, which is not copied)
+        const size_t npix = (size_t)c->fp.height * c->fp.width;
+        cudaError_t e = cudaSuccess;
+        if (bgr_rows) e = cudaMemcpyAsync(bgr_rows, c->framebuffer, (size_t)c->fp.height * c->bytewidth, cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess && primary_ids) e = cudaMemcpyAsync(primary_ids, c->ids, npix * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess && accum) e = cudaMemcpyAsync(accum, c->accum, npix * 3 * sizeof(double), cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) { set_error(std::string("copy back: ") + cudaGetErrorString(e)); rc = RT_ERR_CUDA; }
+    }
+    rt_context_destroy(c);
+    return rc;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// test hooks: batch Scene::intersect, Camera::project, Color::write_bgr
+// ---------------------------------------------------------------------------------------------------------
+int rt_trace_rays(const rt_scene* s, const rt_render_opts* o, uint64_t n, const double* origin_dir, int32_t* ids, double* t, double* normal) {
+    if (!s || !o || (n && (!origin_dir || !ids))) { set_error("rt_trace_rays: null argument"); return RT_ERR_INVALID; }
+    if (rt_device_count() <= 0) { set_error("no CUDA device: this library has no CPU fallback"); return RT_ERR_CUDA; }
+    if (n == 0) return RT_OK;
+    if (n > 0x7FFFFFFFull) { set_error("too many rays"); return RT_ERR_INVALID; }
+    CUDA_TRY(cudaSetDevice(o->device));
+    cudaStream_t st;
+    CUDA_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    int sm_count = 148;
+    cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, o->device);
+    int rc = RT_OK;
+    {
+        DeviceSceneHolder holder;
+        const rt_scene* use = s;  // scenes used only for intersection tests may lack camera/background
+        rt_scene patched;
+        if (!s->camera_set || !s->background_set) {
+            patched = *s;
+            patched.camera_set = true; patched.background_set = true; patched.bg_kind = BG_SOLID;
+            use = &patched;
+        }
+        rc = holder.init(use, o->accel, st);
+        std::vector<void*> allocs;
+        RayQueue q{};
+        double *d_t = nullptr, *d_n = nullptr;
+        uint32_t* cursor = nullptr;
+        if (rc == RT_OK) rc = alloc_ray_queue(&q, (uint32_t)n, &allocs, false);
+        if (rc == RT_OK) rc = dev_alloc(&d_t, n);
+        if (rc == RT_OK) rc = dev_alloc(&d_n, 3 * n);
+        if (rc == RT_OK) rc = dev_alloc(&cursor, 1);
+        if (rc == RT_OK) {
+            std::vector<double> soa(6 * n);
+            for (uint64_t i = 0; i < n; i++)
+                for (int k = 0; k < 6; k++) soa[(size_t)k * n + i] = origin_dir[6 * i + k];
+            cudaError_t e = cudaMemcpyAsync(q.ox, soa.data(), sizeof(double) * 6 * n, cudaMemcpyHostToDevice, st);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+            const KernelTable* k = o->fp_mode == RT_FP_FAST ? kernels_fast() : kernels_strict();
+            if (e == cudaSuccess) {
+                k->closest(st, holder.ds, holder.use_bvh, q, 0, (uint32_t)n, cursor, sm_count);
+                k->hit_normals(st, holder.ds, q, (uint32_t)n, d_t, d_n);
+                e = cudaMemcpyAsync(ids, q.hit_id, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, st);
+            }
+            if (e == cudaSuccess && t) e = cudaMemcpyAsync(t, d_t, sizeof(double) * n, cudaMemcpyDeviceToHost, st);
+            if (e == cudaSuccess && normal) e = cudaMemcpyAsync(normal, d_n, sizeof(double) * 3 * n, cudaMemcpyDeviceToHost, st);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+            if (e == cudaSuccess) e = cudaGetLastError();
+            if (e != cudaSuccess) { set_error(std::string("rt_trace_rays: ") + cudaGetErrorString(e)); rc = RT_ERR_CUDA; }
+        }
+        for (void* p : allocs) cudaFree(p);
+        cudaFree(d_t); cudaFree(d_n); cudaFree(cursor);
+    }
+    cudaStreamDestroy(st);
+    return rc;
+}
+
+int rt_project(const rt_scene* s, const rt_render_opts* o, uint64_t n, const double* pos_xy, double* origin_dir) {
+    if (!s || !o || (n && (!pos_xy || !origin_dir))) { set_error("rt_project: null argument"); return RT_ERR_INVALID; }
+    if (!s->camera_set) { set_error("rt_project: scene has no camera"); return RT_ERR_INVALID; }
+    if (rt_device_count() <= 0) { set_error("no CUDA device: this library has no CPU fallback"); return RT_ERR_CUDA; }
+    if (n == 0) return RT_OK;
+    CUDA_TRY(cudaSetDevice(o->device));
+    DeviceScene ds{};
+    ds.camera = s->camera;
+    double *d_pos = nullptr, *d_od = nullptr;
+    CUDA_TRY(cudaMalloc((void**)&d_pos, sizeof(double) * 2 * n));
+    cudaError_t e = cudaMalloc((void**)&d_od, sizeof(double) * 6 * n);
+    if (e == cudaSuccess) e = cudaMemcpy(d_pos, pos_xy, sizeof(double) * 2 * n, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        const KernelTable* k = o->fp_mode == RT_FP_FAST ? kernels_fast() : kernels_strict();
+        k->project(0, ds, o->seed, (uint32_t)n, d_pos, d_od);
+        e = cudaMemcpy(origin_dir, d_od, sizeof(double) * 6 * n, cudaMemcpyDeviceToHost);
+    }
+    cudaFree(d_pos); cudaFree(d_od);
+    if (e != cudaSuccess) { set_error(std::string("rt_project: ") + cudaGetErrorString(e)); return RT_ERR_CUDA; }
+    return RT_OK;
+}
+
+int rt_quantize_bgr(const double* rgb, uint64_t n, uint8_t* bgr, int device) {
+    if (n && (!rgb || !bgr)) { set_error("rt_quantize_bgr: null argument"); return RT_ERR_INVALID; }
+    if (rt_device_count() <= 0) { set_error("no CUDA device: this library has no CPU fallback"); return RT_ERR_CUDA; }
+    if (n == 0) return RT_OK;
+    CUDA_TRY(cudaSetDevice(device));
+    double *d_rgb = nullptr, *d_avg = nullptr;
+    uint8_t* d_bgr = nullptr;
+    CUDA_TRY(cudaMalloc((void**)&d_rgb, sizeof(double) * 3 * n));
+    cudaError_t e = cudaMalloc((void**)&d_bgr, 3 * n);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&d_avg, sizeof(double) * 255);
+    if (e == cudaSuccess) e = cudaMemcpy(d_rgb, rgb, sizeof(double) * 3 * n, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d_avg, SRGB_AVERAGE, sizeof(double) * 255, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        kernels_strict()->quantize(0, d_avg, d_rgb, n, d_bgr);
+        e = cudaMemcpy(bgr, d_bgr, 3 * n, cudaMemcpyDeviceToHost);
+    }
+    cudaFree(d_rgb); cudaFree(d_bgr); cudaFree(d_avg);
+    if (e != cudaSuccess) { set_error(std::string("rt_quantize_bgr: ") + cudaGetErrorString(e)); return RT_ERR_CUDA; }
+    return RT_OK;
+}
+
+}  // extern "C"

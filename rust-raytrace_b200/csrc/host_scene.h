@@ -1,0 +1,86 @@
+// host_scene.h -- host-side scene model behind the opaque `rt_scene` handle.
+//
+// Mirrors the reference's `Scene` (src/scene.rs:201-212) as flat tagged records instead of boxed trait objects.
+// The host only *describes* the scene; all tracing happens on the device.
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "rt_types.h"
+
+struct rt_render_opts;
+
+namespace rt {
+
+struct HostTexture {
+    uint32_t width = 0, height = 0;
+    std::vector<uint8_t> data;  // RGB8, row 0 = top
+};
+
+struct HostObject {
+    bool is_plane;
+    double p[3];     // sphere centre | plane point
+    double n[3];     // plane normal
+    double radius;   // sphere
+    uint32_t material;
+};
+
+}  // namespace rt
+
+// the C handle
+struct rt_scene {
+    std::vector<rt::HostObject> objects;
+    std::vector<rt::MaterialRec> materials;
+    std::vector<rt::LightRec> lights;
+    rt::CameraRec camera{};
+    bool camera_set = false;
+    int32_t bg_kind = rt::BG_SOLID;
+    double bg_color[3] = {0.0, 0.0, 0.0};
+    bool background_set = false;
+    rt::HostTexture faces[6];
+    uint32_t width = 0, height = 0, antialias = 1;
+    bool options_set = false;
+    std::string warnings;
+    uint64_t n_spheres = 0, n_planes = 0;
+};
+
+namespace rt {
+
+void set_error(const std::string& msg);
+const char* get_error();
+
+// camera constructors (src/camera.rs:51-73, :97-106)
+void camera_spc_new(CameraRec* cam, const double* position, const double* look, const double* up, double im_dist);
+void camera_spc_look_at(CameraRec* cam, const double* focus, const double* look, const double* up, double pov, double h);
+void camera_make_dof(CameraRec* cam, double focus, double aperture, uint32_t samples);
+
+// texture file loaders (24-bit BMP, binary PPM); returns false and sets `err` on failure
+bool load_texture_file(const std::string& path, HostTexture* out, std::string* err);
+
+// serialize::deserialize; returns RT_OK or RT_ERR_SYNTAX with `err` = "row:col: message"
+int parse_scene_text(const char* text, size_t len, rt_scene* scene, std::string* err);
+
+// Flattened scene: the reference's Vec<Object> of boxed trait objects (src/scene.rs:93-98) as tagged SoA buffers.
+struct FlatScene {
+    std::vector<SphereRec> sph;         // scan order = object order among spheres
+    std::vector<int32_t> sph_obj;
+    std::vector<PlaneRec> planes;
+    std::vector<uint32_t> obj_shape, obj_material;
+    double centroid_lo[3], centroid_hi[3];
+    double cmax, rmin;
+    int32_t max_children;
+};
+// returns RT_OK or RT_ERR_INVALID (missing camera/background/skybox face)
+int flatten_scene(const rt_scene* s, FlatScene* out);
+// fills the fields of DeviceScene that do not point into device memory
+void fill_scene_header(const rt_scene* s, const FlatScene& f, DeviceScene* ds);
+// image-space shard + frame parameters from the scene's Options and the render options
+int make_frame_params(const rt_scene* s, const struct ::rt_render_opts* o, FrameParams* fp);
+bool accel_uses_bvh(int accel, uint32_t n_spheres);
+
+// sRGB tables (generated; see tools/gen_srgb_tables.py)
+extern const double SRGB_VALUES[256];
+extern const double SRGB_AVERAGE[255];
+
+}  // namespace rt

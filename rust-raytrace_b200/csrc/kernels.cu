@@ -1,0 +1,464 @@
+// kernels.cu -- the wavefront ray-queue kernels (sm_100a).  Compiled twice, see rt_device.cuh / build.py:
+//   -DRT_NS=strict -fmad=false   and   -DRT_NS=fast -fmad=true
+//
+// Kernel            replaces (reference file:line)
+//   k_primary       src/main.rs:50-53 + src/camera.rs:77-79,110-121      one thread per path, coalesced SoA ray writes
+//   k_closest_scan  src/scene.rs:247-249 + src/shapes.rs:50-112          sphere records staged through shared memory
+//                                                                        with 1-D TMA bulk copies (cp.async.bulk + mbarrier)
+//   k_closest_bvh   same, through the device-built LBVH                  persistent warps pulling rays off a cursor
+//   k_shade         src/raytrace.rs:30-256, src/scene.rs:117-155,        material switch on a tag, warp-aggregated queue
+//                   src/texture.rs:39-58, src/color.rs ops               appends (__ballot_sync/__popc/__shfl_sync)
+//   k_shadow_*      src/raytrace.rs:43-50 (and siblings)                 any-hit with range, adds the pending contribution
+//   k_resolve       src/main.rs:56 + src/color.rs:593-600,628-632        threshold-table search, BGR pack, 128-bit stores
+#include <cuda_runtime.h>
+
+#include "kernels.h"
+#include "rt_device.cuh"
+
+namespace rt {
+namespace RT_NS {
+
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_TILE = 1024;  // spheres per shared-memory tile (32 KB), double buffered
+constexpr int BVH_THREADS = 128;
+constexpr int SHADE_THREADS = 128;
+
+// ---------------------------------------------------------------------------------------------------------
+// small PTX wrappers: mbarrier + 1-D TMA bulk copy (global -> shared)
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)), "l"(src), "r"(bytes),
+                 "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(ok)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// warp-aggregated queue append: one atomicAdd per warp.  Must be called by all 32 lanes.
+// Returns the slot for lanes with want == true (0xFFFFFFFF when the queue is full -> overflow flag).
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t warp_append(bool want, uint32_t* counter, uint32_t cap, uint32_t* overflow) {
+    const unsigned m = __ballot_sync(0xFFFFFFFFu, want);
+    if (m == 0) return 0xFFFFFFFFu;
+    const int lane = threadIdx.x & 31;
+    const int leader = __ffs(m) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(counter, (uint32_t)__popc(m));
+    base = __shfl_sync(0xFFFFFFFFu, base, leader);
+    uint32_t slot = base + (uint32_t)__popc(m & ((1u << lane) - 1u));
+    if (want && slot >= cap) {
+        *overflow = 1u;
+        return 0xFFFFFFFFu;
+    }
+    return want ? slot : 0xFFFFFFFFu;
+}
+
+__device__ __forceinline__ void accum_add(double* accum, uint32_t pixel, C3 c) {
+    if (c.r == 0.0 && c.g == 0.0 && c.b == 0.0) return;  // x + 0 == x; NaN is != 0 and still added
+    double* p = accum + (size_t)pixel * 3;
+    atomicAdd(p, c.r);
+    atomicAdd(p + 1, c.g);
+    atomicAdd(p + 2, c.b);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// k_primary
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_primary(const __grid_constant__ DeviceScene sc, const __grid_constant__ FrameParams fp, RayQueue q,
+                                                 uint32_t* q_count, uint32_t* overflow, uint64_t path_base, uint32_t n_paths) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    bool valid = i < n_paths;
+    uint32_t x = 0, y = 0, lp = 0, aa = 0, cs = 0;
+    if (valid) {
+        const uint64_t g = path_base + i;
+        const uint64_t plane = g / fp.npix_padded;
+        const uint64_t slot = g - plane * fp.npix_padded;
+        aa = (uint32_t)(plane / fp.cam_samples);
+        cs = (uint32_t)(plane - (uint64_t)aa * fp.cam_samples);
+        valid = slot_to_pixel(fp, slot, x, y, lp);
+    }
+    V3 o = v3(0, 0, 0), d = v3(0, 0, 0);
+    uint64_t ck = 0;
+    if (valid) {
+        const uint64_t pixel = (uint64_t)y * fp.width + x;
+        const uint64_t sk = key_sample(fp.seed, pixel, aa);
+        double px, py;
+        pixel_position(fp, x, y, sk, px, py);
+        ck = child_key(sk, CODE_CAMERA0 + cs);
+        camera_project(sc.camera, px, py, ck, o, d);
+    }
+    const uint32_t s = warp_append(valid, q_count, q.cap, overflow);
+    if (s != 0xFFFFFFFFu) {
+        q.ox[s] = o.x; q.oy[s] = o.y; q.oz[s] = o.z;
+        q.dx[s] = d.x; q.dy[s] = d.y; q.dz[s] = d.z;
+        q.tr[s] = 1.0; q.tg[s] = 1.0; q.tb[s] = 1.0;
+        q.sig[s] = 1.0;
+        q.key[s] = ck;
+        q.pixel[s] = lp;
+        q.meta[s] = (aa == 0 && cs == 0) ? META_RECORD_ID : 0u;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// linear scan with shared-memory staging.  All lanes test the same sphere (shared-memory broadcast); the
+// sphere buffer streams through two 32 KB tiles filled by 1-D TMA bulk copies that overlap the arithmetic.
+// ---------------------------------------------------------------------------------------------------------
+struct ScanSmem {
+    SphereRec tile[2][SCAN_TILE];
+    uint64_t bar[2];
+};
+
+template <bool SHADOW>
+__device__ __forceinline__ void scan_spheres(const DeviceScene& sc, ScanSmem* sm, const RayQ& r, bool active, Closest& best, double range2, Shadow& sh) {
+    const uint32_t n = sc.n_spheres;
+    if (n == 0) return;
+    const uint32_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+    if (threadIdx.x == 0) {
+        mbar_init(&sm->bar[0], 1);
+        mbar_init(&sm->bar[1], 1);
+        mbar_fence_init();
+        const uint32_t cnt = n < (uint32_t)SCAN_TILE ? n : (uint32_t)SCAN_TILE;
+        mbar_expect_tx(&sm->bar[0], cnt * (uint32_t)sizeof(SphereRec));
+        tma_load_1d(sm->tile[0], sc.sph, cnt * (uint32_t)sizeof(SphereRec), &sm->bar[0]);
+    }
+    __syncthreads();
+    bool done = !active;
+    for (uint32_t k = 0; k < ntiles; k++) {
+        const uint32_t buf = k & 1u;
+        if (threadIdx.x == 0 && k + 1 < ntiles) {
+            const uint32_t first = (k + 1) * SCAN_TILE;
+            const uint32_t cnt = (n - first) < (uint32_t)SCAN_TILE ? (n - first) : (uint32_t)SCAN_TILE;
+            mbar_expect_tx(&sm->bar[buf ^ 1u], cnt * (uint32_t)sizeof(SphereRec));
+            tma_load_1d(sm->tile[buf ^ 1u], sc.sph + first, cnt * (uint32_t)sizeof(SphereRec), &sm->bar[buf ^ 1u]);
+        }
+        mbar_wait(&sm->bar[buf], (k >> 1) & 1u);
+        const uint32_t first = k * SCAN_TILE;
+        const uint32_t cnt = (n - first) < (uint32_t)SCAN_TILE ? (n - first) : (uint32_t)SCAN_TILE;
+        if (!done) {
+            const SphereRec* t = sm->tile[buf];
+#pragma unroll 4
+            for (uint32_t j = 0; j < cnt; j++) {
+                const double2 c01 = *reinterpret_cast<const double2*>(&t[j].cx);
+                const double2 c23 = *reinterpret_cast<const double2*>(&t[j].cz);
+                double th;
+                if (sphere_hit(r, c01.x, c01.y, c23.x, c23.y, th)) {
+                    if (SHADOW) {
+                        if (shadow_hit_counts(th, range2)) { sh.any = true; done = true; break; }
+                    } else {
+                        closest_update(best, th, __ldg(sc.sph_obj + first + j));
+                    }
+                }
+            }
+        }
+        // all reads of tile[buf] are complete before it is refilled two iterations later
+        const int all_done = __syncthreads_and(done ? 1 : 0);
+        if (SHADOW && all_done) {
+            if (k + 1 < ntiles) mbar_wait(&sm->bar[buf ^ 1u], ((k + 1) >> 1) & 1u);  // drain the in-flight copy before exit
+            break;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) k_closest_scan(const __grid_constant__ DeviceScene sc, RayQueue q, uint32_t first, uint32_t n) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    ScanSmem* sm = reinterpret_cast<ScanSmem*>(smem_raw);
+    const uint32_t li = blockIdx.x * SCAN_THREADS + threadIdx.x;
+    const bool active = li < n;
+    const uint32_t i = first + (active ? li : 0);
+    RayQ r = make_rayq(v3(q.ox[i], q.oy[i], q.oz[i]), v3(q.dx[i], q.dy[i], q.dz[i]));
+    Closest best = closest_none();
+    planes_closest(sc, r, best);
+    Shadow dummy; dummy.nan = false; dummy.any = false;
+    scan_spheres<false>(sc, sm, r, active && !best.nan, best, -1.0, dummy);
+    if (active) {
+        q.hit_id[i] = closest_id(best);
+        q.hit_t[i] = best.t;
+    }
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) k_shadow_scan(const __grid_constant__ DeviceScene sc, ShadowQueue sq, uint32_t n, double* accum) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    ScanSmem* sm = reinterpret_cast<ScanSmem*>(smem_raw);
+    const uint32_t li = blockIdx.x * SCAN_THREADS + threadIdx.x;
+    const bool active = li < n;
+    const uint32_t i = active ? li : 0;
+    RayQ r = make_rayq(v3(sq.ox[i], sq.oy[i], sq.oz[i]), v3(sq.dx[i], sq.dy[i], sq.dz[i]));
+    const double range2 = sq.r2[i];
+    Shadow s; s.nan = false; s.any = false;
+    planes_shadow(sc, r, range2, s);
+    Closest dummy = closest_none();
+    scan_spheres<true>(sc, sm, r, active && !s.nan && !s.any, dummy, range2, s);
+    if (active && !shadow_result(s, range2)) accum_add(accum, sq.pixel[i], c3(sq.cr[i], sq.cg[i], sq.cb[i]));
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// BVH traversal: persistent warps, each pulling 32 rays at a time off a global cursor
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_constant__ DeviceScene sc, RayQueue q, uint32_t first, uint32_t n, uint32_t* cursor) {
+    const int lane = threadIdx.x & 31;
+    while (true) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(cursor, 32u);
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+        if (base >= n) break;
+        const uint32_t li = base + lane;
+        if (li < n) {
+            const uint32_t i = first + li;
+            RayQ r = make_rayq(v3(q.ox[i], q.oy[i], q.oz[i]), v3(q.dx[i], q.dy[i], q.dz[i]));
+            int32_t id;
+            double t;
+            closest_bvh(sc, r, id, t);
+            q.hit_id[i] = id;
+            q.hit_t[i] = t;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(BVH_THREADS) k_shadow_bvh(const __grid_constant__ DeviceScene sc, ShadowQueue sq, uint32_t n, double* accum, uint32_t* cursor) {
+    const int lane = threadIdx.x & 31;
+    while (true) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(cursor, 32u);
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+        if (base >= n) break;
+        const uint32_t i = base + lane;
+        if (i < n) {
+            RayQ r = make_rayq(v3(sq.ox[i], sq.oy[i], sq.oz[i]), v3(sq.dx[i], sq.dy[i], sq.dz[i]));
+            if (!shadow_bvh(sc, r, sq.r2[i])) accum_add(accum, sq.pixel[i], c3(sq.cr[i], sq.cg[i], sq.cb[i]));
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// k_shade
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(SHADE_THREADS) k_shade(const __grid_constant__ DeviceScene sc, const __grid_constant__ FrameParams fp, RayQueue in,
+                                                         uint32_t first, uint32_t n, RayQueue out, uint32_t* out_count, ShadowQueue sq,
+                                                         uint32_t* sq_count, uint32_t* overflow, double* accum, int32_t* ids) {
+    const uint32_t li = blockIdx.x * SHADE_THREADS + threadIdx.x;
+    const bool active = li < n;
+    ShadeCtx s;
+    s.alive = false; s.lit = false;
+    uint32_t pixel = 0, depth = 0;
+    if (active) {
+        const uint32_t i = first + li;
+        const V3 o = v3(in.ox[i], in.oy[i], in.oz[i]);
+        const V3 d = v3(in.dx[i], in.dy[i], in.dz[i]);
+        const C3 T = c3(in.tr[i], in.tg[i], in.tb[i]);
+        const uint32_t meta = in.meta[i];
+        const int32_t hid = in.hit_id[i];
+        pixel = in.pixel[i];
+        depth = meta & META_DEPTH_MASK;
+        if ((meta & META_RECORD_ID) && ids) ids[pixel] = hid;
+        const C3 add = shade_begin(sc, fp, o, d, T, in.sig[i], in.key[i], depth, hid, in.hit_t[i], s);
+        accum_add(accum, pixel, add);
+    }
+    // light loop: uniform trip count, per-lane predicate
+    for (uint32_t li2 = 0; li2 < sc.n_lights; li2++) {
+        ShadowRay sr;
+        const bool want = shade_light(sc, s, li2, sr);
+        const uint32_t slot = warp_append(want, sq_count, sq.cap, overflow);
+        if (slot != 0xFFFFFFFFu) {
+            sq.ox[slot] = sr.o.x; sq.oy[slot] = sr.o.y; sq.oz[slot] = sr.o.z;
+            sq.dx[slot] = sr.d.x; sq.dy[slot] = sr.d.y; sq.dz[slot] = sr.d.z;
+            sq.r2[slot] = sr.range2;
+            sq.cr[slot] = sr.c.r; sq.cg[slot] = sr.c.g; sq.cb[slot] = sr.c.b;
+            sq.pixel[slot] = pixel;
+        }
+    }
+    // spawned rays: slot k of every lane in lock step
+    for (uint32_t k = 0; k < (uint32_t)sc.max_children; k++) {
+        ChildRay cr;
+        const bool want = shade_child(sc, s, k, cr);
+        const uint32_t slot = warp_append(want, out_count, out.cap, overflow);
+        if (slot != 0xFFFFFFFFu) {
+            out.ox[slot] = cr.o.x; out.oy[slot] = cr.o.y; out.oz[slot] = cr.o.z;
+            out.dx[slot] = cr.d.x; out.dy[slot] = cr.d.y; out.dz[slot] = cr.d.z;
+            out.tr[slot] = cr.T.r; out.tg[slot] = cr.T.g; out.tb[slot] = cr.T.b;
+            out.sig[slot] = cr.sig;
+            out.key[slot] = cr.key;
+            out.pixel[slot] = pixel;
+            out.meta[slot] = depth + 1u;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// k_resolve: each thread produces 16 consecutive output bytes (one 128-bit store)
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_resolve(const __grid_constant__ DeviceScene sc, const __grid_constant__ FrameParams fp, const double* accum,
+                                                 uint8_t* out, uint32_t bytewidth, uint64_t total_bytes) {
+    __shared__ double avg[255];
+    for (int i = threadIdx.x; i < 255; i += blockDim.x) avg[i] = sc.srgb_average[i];
+    __syncthreads();
+    const uint64_t chunk = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t b0 = chunk * 16;
+    if (b0 >= total_bytes) return;
+    const double cam_div = (double)fp.cam_samples;
+    const double aa_div = (double)fp.antialias;
+    uint32_t row = (uint32_t)(b0 / bytewidth);
+    uint32_t col = (uint32_t)(b0 - (uint64_t)row * bytewidth);
+    uint32_t px = col / 3, ch = col - px * 3;
+    uint32_t words[4] = {0, 0, 0, 0};
+    const uint32_t rowbytes = fp.width * 3;
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        uint32_t v = 0;
+        if (b0 + k < total_bytes && col < rowbytes) {
+            const double a = accum[((size_t)row * fp.width + px) * 3 + (2 - ch)];
+            v = to_srgb(avg, (a / cam_div) / aa_div);  // raytrace(): res / samples (src/raytrace.rs:275); main: res / aa (src/main.rs:56)
+        }
+        words[k >> 2] |= v << (8 * (k & 3));
+        col++; ch++;
+        if (ch == 3) { ch = 0; px++; }
+        if (col == bytewidth) { col = 0; px = 0; ch = 0; row++; }
+    }
+    if (b0 + 16 <= total_bytes) {
+        *reinterpret_cast<uint4*>(out + b0) = make_uint4(words[0], words[1], words[2], words[3]);
+    } else {
+        for (int k = 0; b0 + k < total_bytes; k++) out[b0 + k] = (uint8_t)(words[k >> 2] >> (8 * (k & 3)));
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// test hooks
+// ---------------------------------------------------------------------------------------------------------
+__global__ void k_hit_normals(const __grid_constant__ DeviceScene sc, RayQueue q, uint32_t n, double* t_out, double* normal_out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int32_t id = q.hit_id[i];
+    V3 nrm = v3(0, 0, 0);
+    double t = (double)INFINITY;
+    if (id >= 0) {
+        t = q.hit_t[i];
+        nrm = shape_normal(sc, id, v3(q.ox[i], q.oy[i], q.oz[i]), v3(q.dx[i], q.dy[i], q.dz[i]), t);
+    }
+    t_out[i] = t;
+    normal_out[3 * (size_t)i] = nrm.x; normal_out[3 * (size_t)i + 1] = nrm.y; normal_out[3 * (size_t)i + 2] = nrm.z;
+}
+
+__global__ void k_project(const __grid_constant__ DeviceScene sc, uint64_t seed, uint32_t n, const double* pos, double* od) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint64_t ck = child_key(key_sample(seed, i, 0), CODE_CAMERA0);
+    V3 o, d;
+    camera_project(sc.camera, pos[2 * (size_t)i], pos[2 * (size_t)i + 1], ck, o, d);
+    double* p = od + 6 * (size_t)i;
+    p[0] = o.x; p[1] = o.y; p[2] = o.z; p[3] = d.x; p[4] = d.y; p[5] = d.z;
+}
+
+__global__ void k_quantize(const double* srgb_average, const double* rgb, uint64_t n, uint8_t* bgr) {
+    __shared__ double avg[255];
+    for (int i = threadIdx.x; i < 255; i += blockDim.x) avg[i] = srgb_average[i];
+    __syncthreads();
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    bgr[3 * i] = to_srgb(avg, rgb[3 * i + 2]);
+    bgr[3 * i + 1] = to_srgb(avg, rgb[3 * i + 1]);
+    bgr[3 * i + 2] = to_srgb(avg, rgb[3 * i]);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// launch wrappers
+// ---------------------------------------------------------------------------------------------------------
+static inline uint32_t div_up(uint64_t a, uint32_t b) { return (uint32_t)((a + b - 1) / b); }
+
+static void l_primary(cudaStream_t st, const DeviceScene& sc, const FrameParams& fp, RayQueue q, uint32_t* q_count, uint32_t* overflow,
+                      uint64_t path_base, uint32_t n_paths) {
+    if (!n_paths) return;
+    k_primary<<<div_up(n_paths, 256), 256, 0, st>>>(sc, fp, q, q_count, overflow, path_base, n_paths);
+}
+
+static void scan_attr_once() {
+    static bool done = false;
+    if (!done) {
+        cudaFuncSetAttribute(k_closest_scan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScanSmem));
+        cudaFuncSetAttribute(k_shadow_scan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScanSmem));
+        done = true;
+    }
+}
+
+static void l_closest(cudaStream_t st, const DeviceScene& sc, bool bvh, RayQueue q, uint32_t first, uint32_t n, uint32_t* cursor, int sm_count) {
+    if (!n) return;
+    if (bvh) {
+        cudaMemsetAsync(cursor, 0, sizeof(uint32_t), st);
+        uint32_t want = div_up(n, BVH_THREADS);
+        uint32_t grid = (uint32_t)sm_count * 8u;  // 8 resident CTAs of 128 threads per SM
+        k_closest_bvh<<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, q, first, n, cursor);
+    } else {
+        scan_attr_once();
+        k_closest_scan<<<div_up(n, SCAN_THREADS), SCAN_THREADS, sizeof(ScanSmem), st>>>(sc, q, first, n);
+    }
+}
+
+static void l_shade(cudaStream_t st, const DeviceScene& sc, const FrameParams& fp, RayQueue in, uint32_t first, uint32_t n, RayQueue out,
+                    uint32_t* out_count, ShadowQueue sq, uint32_t* sq_count, uint32_t* overflow, double* accum, int32_t* ids) {
+    if (!n) return;
+    k_shade<<<div_up(n, SHADE_THREADS), SHADE_THREADS, 0, st>>>(sc, fp, in, first, n, out, out_count, sq, sq_count, overflow, accum, ids);
+}
+
+static void l_shadow(cudaStream_t st, const DeviceScene& sc, bool bvh, ShadowQueue sq, uint32_t n, double* accum, uint32_t* cursor, int sm_count) {
+    if (!n) return;
+    if (bvh) {
+        cudaMemsetAsync(cursor, 0, sizeof(uint32_t), st);
+        uint32_t want = div_up(n, BVH_THREADS);
+        uint32_t grid = (uint32_t)sm_count * 8u;
+        k_shadow_bvh<<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, cursor);
+    } else {
+        scan_attr_once();
+        k_shadow_scan<<<div_up(n, SCAN_THREADS), SCAN_THREADS, sizeof(ScanSmem), st>>>(sc, sq, n, accum);
+    }
+}
+
+static void l_resolve(cudaStream_t st, const DeviceScene& sc, const FrameParams& fp, const double* accum, uint8_t* out, uint32_t bytewidth) {
+    const uint64_t total = (uint64_t)bytewidth * fp.local_rows;
+    if (!total) return;
+    k_resolve<<<div_up((total + 15) / 16, 256), 256, 0, st>>>(sc, fp, accum, out, bytewidth, total);
+}
+
+static void l_hit_normals(cudaStream_t st, const DeviceScene& sc, RayQueue q, uint32_t n, double* t_out, double* normal_out) {
+    if (!n) return;
+    k_hit_normals<<<div_up(n, 256), 256, 0, st>>>(sc, q, n, t_out, normal_out);
+}
+static void l_project(cudaStream_t st, const DeviceScene& sc, uint64_t seed, uint32_t n, const double* pos, double* od) {
+    if (!n) return;
+    k_project<<<div_up(n, 256), 256, 0, st>>>(sc, seed, n, pos, od);
+}
+static void l_quantize(cudaStream_t st, const double* avg, const double* rgb, uint64_t n, uint8_t* bgr) {
+    if (!n) return;
+    k_quantize<<<div_up(n, 256), 256, 0, st>>>(avg, rgb, n, bgr);
+}
+
+static const KernelTable g_table = {l_primary, l_closest, l_shade, l_shadow, l_resolve, l_hit_normals, l_project, l_quantize};
+
+}  // namespace RT_NS
+
+#define RT_CAT_(a, b) a##b
+#define RT_CAT(a, b) RT_CAT_(a, b)
+const KernelTable* RT_CAT(kernels_, RT_NS)() { return &RT_NS::g_table; }
+
+}  // namespace rt

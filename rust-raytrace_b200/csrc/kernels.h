@@ -1,0 +1,59 @@
+// kernels.h -- launch interface of the wavefront kernels.  kernels.cu is compiled twice (see rt_device.cuh):
+// rt::kernels_strict() (-fmad=false) and rt::kernels_fast() (-fmad=true) return the two instantiations.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "rt_types.h"
+
+namespace rt {
+
+// device-side counters of one context (one allocation, zeroed/reset by the host driver)
+struct Counters {
+    uint32_t overflow;      // a queue append was dropped (host sizing bug) -> render fails loudly
+    uint32_t shadow_count;  // shadow queue length
+    uint32_t cursor;        // persistent-thread work cursor (reset before each persistent launch)
+    uint32_t _pad;
+    uint32_t level_count[64];  // ray-queue length per wavefront level
+};
+
+struct KernelTable {
+    // camera.rs primary-ray generation: paths [path_base, path_base + n_paths) -> level-0 queue
+    void (*primary)(cudaStream_t, const DeviceScene&, const FrameParams&, RayQueue q, uint32_t* q_count, uint32_t* overflow, uint64_t path_base,
+                    uint32_t n_paths);
+    // Scene::intersect for rays [first, first+n) of q; fills hit_id / hit_t
+    void (*closest)(cudaStream_t, const DeviceScene&, bool bvh, RayQueue q, uint32_t first, uint32_t n, uint32_t* cursor, int sm_count);
+    // material evaluation: pixel accumulation, shadow-ray and child-ray emission with warp-aggregated appends
+    void (*shade)(cudaStream_t, const DeviceScene&, const FrameParams&, RayQueue in, uint32_t first, uint32_t n, RayQueue out, uint32_t* out_count,
+                  ShadowQueue sq, uint32_t* sq_count, uint32_t* overflow, double* accum, int32_t* ids);
+    // shadow queries; unoccluded rays add their pending contribution to the pixel
+    void (*shadow)(cudaStream_t, const DeviceScene&, bool bvh, ShadowQueue sq, uint32_t n, double* accum, uint32_t* cursor, int sm_count);
+    // average, quantise (threshold table) and pack BGR rows with padding; 128-bit stores
+    void (*resolve)(cudaStream_t, const DeviceScene&, const FrameParams&, const double* accum, uint8_t* out, uint32_t bytewidth);
+    // test hooks
+    void (*hit_normals)(cudaStream_t, const DeviceScene&, RayQueue q, uint32_t n, double* t_out, double* normal_out);
+    void (*project)(cudaStream_t, const DeviceScene&, uint64_t seed, uint32_t n, const double* pos_xy, double* origin_dir);
+    void (*quantize)(cudaStream_t, const double* srgb_average, const double* rgb, uint64_t n, uint8_t* bgr);
+};
+
+const KernelTable* kernels_strict();
+const KernelTable* kernels_fast();
+
+// mode-independent kernels (bvh_build.cu)
+struct BvhBuildResult {
+    BvhNode* nodes;       // [n_nodes]
+    SphereRec* sph;       // Morton order
+    int32_t* obj;
+    uint32_t n_nodes;
+    uint32_t launches;
+};
+// Builds the LBVH over `n` spheres (scan-order records + object ids, device pointers).  Device-side throughout:
+// Morton codes -> bitonic sort -> Karras hierarchy -> bottom-up refit -> packed f32 child boxes.
+cudaError_t bvh_build(cudaStream_t, const SphereRec* sph, const int32_t* sph_obj, uint32_t n, const double* centroid_lo, const double* centroid_hi,
+                      BvhBuildResult* out);
+void bvh_free(BvhBuildResult* r);
+
+// de-interleave row bands after the framebuffer all-gather (rank-major input)
+void launch_untile(cudaStream_t, const uint32_t* gathered, uint32_t* out, uint32_t height, uint32_t words_per_row, uint32_t band_rows, uint32_t world,
+                   uint32_t local_rows);
+
+}  // namespace rt

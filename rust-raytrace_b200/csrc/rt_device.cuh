@@ -1,0 +1,746 @@
+// rt_device.cuh -- per-ray arithmetic of the tracing path: RNG, cameras, shape tests, BVH traversal, shading,
+// backgrounds, quantiser.  Everything here is a pure function over rt_types.h records.
+//
+// The functions are `__host__ __device__` so that tests/emu/ can compile them with g++ and run the wavefront
+// formulation serially on the CPU *as a test of this header* (the product library never contains a CPU render
+// path; see tests/emu/README.md).  In the product they are only ever called from the kernels in kernels.cu.
+//
+// Arithmetic order follows the reference expression by expression (file:line cited per function).  The
+// translation unit is compiled twice: -fmad=false (namespace rt::strict, bit-parity with the reference's
+// unfused x86-64 arithmetic) and -fmad=true (namespace rt::fast).
+#pragma once
+#include <math.h>
+#include <stdint.h>
+
+#include "rt_types.h"
+
+#if defined(__CUDACC__)
+#define RT_HD __host__ __device__ __forceinline__
+#else
+#define RT_HD inline
+#endif
+
+#if defined(__CUDA_ARCH__)
+#define RT_LDG(p) __ldg(p)
+#else
+#define RT_LDG(p) (*(p))
+#endif
+
+#ifndef RT_NS
+#define RT_NS strict
+#endif
+
+namespace rt {
+namespace RT_NS {
+
+// ---------------------------------------------------------------------------------------------------------
+// value types (src/types.rs:10-25, src/color.rs:15-67)
+// ---------------------------------------------------------------------------------------------------------
+struct V3 {
+    double x, y, z;
+};
+RT_HD V3 v3(double x, double y, double z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
+RT_HD V3 v3(const double* p) { return v3(p[0], p[1], p[2]); }
+RT_HD V3 operator+(V3 a, V3 b) { return v3(a.x + b.x, a.y + b.y, a.z + b.z); }
+RT_HD V3 operator-(V3 a, V3 b) { return v3(a.x - b.x, a.y - b.y, a.z - b.z); }
+RT_HD V3 operator-(V3 a) { return v3(-a.x, -a.y, -a.z); }
+RT_HD V3 operator*(V3 a, double s) { return v3(a.x * s, a.y * s, a.z * s); }
+RT_HD V3 operator/(V3 a, double s) { return v3(a.x / s, a.y / s, a.z / s); }
+RT_HD double dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+RT_HD double sqnorm(V3 a) { return dot(a, a); }
+RT_HD V3 normalize(V3 a) { return a / sqrt(sqnorm(a)); }
+
+struct C3 {
+    double r, g, b;
+};
+RT_HD C3 c3(double r, double g, double b) { C3 c; c.r = r; c.g = g; c.b = b; return c; }
+RT_HD C3 c3(const double* p) { return c3(p[0], p[1], p[2]); }
+RT_HD C3 operator+(C3 a, C3 b) { return c3(a.r + b.r, a.g + b.g, a.b + b.b); }
+RT_HD C3 operator*(C3 a, C3 b) { return c3(a.r * b.r, a.g * b.g, a.b * b.b); }
+RT_HD C3 operator*(C3 a, double s) { return c3(a.r * s, a.g * s, a.b * s); }
+RT_HD C3 operator/(C3 a, double s) { return c3(a.r / s, a.g / s, a.b / s); }
+RT_HD double significance(C3 c) { return c.r + c.g + c.b; }  // src/color.rs:637-639
+
+RT_HD double clamp_zero(double x) { return x < 0.0 ? 0.0 : x; }  // src/raytrace.rs:21-23
+RT_HD double clamp_one(double x) { return x > 1.0 ? 1.0 : x; }   // src/raytrace.rs:25-28
+
+// ---------------------------------------------------------------------------------------------------------
+// counter RNG (DESIGN.md "RNG"); replaces the sequential XorShiftRng of src/types.rs:27 / src/main.rs:43
+// ---------------------------------------------------------------------------------------------------------
+RT_HD uint64_t mix64(uint64_t z) {
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    return z ^ (z >> 31);
+}
+#define RT_GOLD 0x9E3779B97F4A7C15ULL
+RT_HD uint64_t key_sample(uint64_t seed, uint64_t pixel, uint64_t aa) {
+    uint64_t k = mix64(seed ^ 0x243F6A8885A308D3ULL);
+    k = mix64(k + RT_GOLD * (pixel + 1));
+    return mix64(k + RT_GOLD * (aa + 1));
+}
+RT_HD uint64_t child_key(uint64_t k, uint64_t code) { return mix64(k + RT_GOLD * (code + 1)); }
+RT_HD uint64_t draw_bits(uint64_t k, uint64_t dim) { return mix64((k ^ 0xD6E8FEB86659FD93ULL) + RT_GOLD * (dim + 1)); }
+RT_HD double draw_f64(uint64_t k, uint64_t dim) { return (double)(draw_bits(k, dim) >> 11) * 0x1.0p-53; }
+RT_HD double draw_closed01(uint64_t k, uint64_t dim) { return (double)(draw_bits(k, dim) >> 11) / 9007199254740991.0; }
+constexpr uint64_t CODE_REFLECT = 1, CODE_REFRACT = 2, CODE_INDIRECT0 = 3, CODE_CAMERA0 = 1ULL << 32;
+
+#define RT_PI 3.14159265358979323846264338327950288
+#define RT_FRAC_1_PI 0.318309886183790671537767526745028724
+
+// ---------------------------------------------------------------------------------------------------------
+// cameras (src/camera.rs:77-79, :110-121)
+// ---------------------------------------------------------------------------------------------------------
+RT_HD V3 mat_mul(const double* m, V3 v) {
+    return v3(m[0] * v.x + m[1] * v.y + m[2] * v.z, m[3] * v.x + m[4] * v.y + m[5] * v.z, m[6] * v.x + m[7] * v.y + m[8] * v.z);
+}
+
+RT_HD void camera_project(const CameraRec& cam, double px, double py, uint64_t key, V3& origin, V3& direction) {
+    V3 dir = mat_mul(cam.m, v3(px, py, 1.0));
+    if (cam.kind == CAM_SPC) {
+        origin = v3(cam.pos);
+        direction = normalize(dir);
+        return;
+    }
+    V3 pos = v3(cam.pos);
+    V3 ip = pos + dir;
+    V3 fp = pos + dir * (cam.focus / cam.im_dist);
+    double theta = draw_f64(key, 0) * (2.0 * RT_PI);
+    double r2 = draw_closed01(key, 1);
+    double r = sqrt(r2) * cam.aperture;
+    V3 orig = ip + mat_mul(cam.m, v3(cos(theta) * r, sin(theta) * r, 0.0));
+    origin = orig;
+    direction = normalize(fp - orig);
+}
+
+// pixel -> normalised image position with jitter (src/main.rs:39-53)
+RT_HD void pixel_position(const FrameParams& fp, uint32_t x, uint32_t y, uint64_t sample_key, double& px, double& py) {
+    double halfwidth = (double)fp.width / 2.0;
+    double halfheight = (double)fp.height / 2.0;
+    double scale = fmax(1.0 / halfwidth, 1.0 / halfheight);
+    double u1 = draw_f64(sample_key, 0);
+    double u2 = draw_f64(sample_key, 1);
+    px = (((double)x + u1) - halfwidth) * scale;
+    py = (((double)y + u2) - halfheight) * scale;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// shapes (src/shapes.rs:50-89, :100-112).  `a`, `fa` = 4a, `ta` = 2a are per-ray invariants of the quadratic.
+// ---------------------------------------------------------------------------------------------------------
+struct RayQ {
+    V3 o, d;
+    double a, fa, ta;
+};
+RT_HD RayQ make_rayq(V3 o, V3 d) {
+    RayQ r;
+    r.o = o; r.d = d;
+    r.a = sqnorm(d);
+    r.fa = 4.0 * r.a;
+    r.ta = 2.0 * r.a;
+    return r;
+}
+
+RT_HD bool sphere_hit(const RayQ& r, double cx, double cy, double cz, double r2, double& t_out) {
+    V3 oc = v3(r.o.x - cx, r.o.y - cy, r.o.z - cz);
+    double b = 2.0 * dot(r.d, oc);
+    double c = sqnorm(oc) - r2;
+    double disc = b * b - r.fa * c;
+    if (disc > 0.0) {
+        double dsqrt = sqrt(disc);
+        double t = (-b - dsqrt) / r.ta;
+        if (t > 0.0) { t_out = t; return true; }
+        double t2 = (-b + dsqrt) / r.ta;
+        if (t2 > 0.0) { t_out = t2; return true; }
+    }
+    return false;
+}
+
+// `t <= 0` rejects, so +inf and NaN are hits (src/shapes.rs:102-104)
+RT_HD bool plane_hit(const RayQ& r, V3 p, V3 n, double& t_out) {
+    double t = dot(n, p - r.o) / dot(n, r.d);
+    if (t <= 0.0) return false;
+    t_out = t;
+    return true;
+}
+
+// closest-hit bookkeeping with the reference's ordering (src/scene.rs:223-249):
+// key = Option<FloatNotNan(t)>, None (NaN) sorts first, ties keep the lowest object index.
+struct Closest {
+    double t;
+    int32_t obj;
+    bool nan;
+};
+RT_HD Closest closest_none() { Closest c; c.t = (double)INFINITY; c.obj = 0x7FFFFFFF; c.nan = false; return c; }
+RT_HD void closest_update(Closest& c, double t, int32_t obj) {
+    if (c.nan) {
+        if (t != t && obj < c.obj) c.obj = obj;
+        return;
+    }
+    if (t != t) { c.nan = true; c.t = t; c.obj = obj; return; }
+    if (t < c.t || (t == c.t && obj < c.obj)) { c.t = t; c.obj = obj; }
+}
+RT_HD int32_t closest_id(const Closest& c) { return c.obj == 0x7FFFFFFF ? -1 : c.obj; }
+
+RT_HD void planes_closest(const DeviceScene& sc, const RayQ& r, Closest& best) {
+    for (uint32_t i = 0; i < sc.n_planes; i++) {
+        const PlaneRec* p = sc.planes + i;
+        double t;
+        if (plane_hit(r, v3(RT_LDG(&p->p[0]), RT_LDG(&p->p[1]), RT_LDG(&p->p[2])), v3(RT_LDG(&p->n[0]), RT_LDG(&p->n[1]), RT_LDG(&p->n[2])), t))
+            closest_update(best, t, RT_LDG(&p->obj));
+    }
+}
+
+// Shadow query semantics (src/raytrace.rs:43-50): occluded iff the CLOSEST hit exists and (no range or t*t < r2).
+// `range2 < 0` encodes "no range".  Equivalent any-hit form: a NaN plane hit is the closest hit by the ordering
+// above (occluded iff no range); otherwise occluded iff some hit has t*t < r2 (squaring is monotone for t > 0).
+struct Shadow {
+    bool nan, any;
+};
+RT_HD bool shadow_hit_counts(double t, double range2) { return range2 < 0.0 ? true : (t * t < range2); }
+RT_HD void planes_shadow(const DeviceScene& sc, const RayQ& r, double range2, Shadow& s) {
+    for (uint32_t i = 0; i < sc.n_planes; i++) {
+        const PlaneRec* p = sc.planes + i;
+        double t;
+        if (plane_hit(r, v3(RT_LDG(&p->p[0]), RT_LDG(&p->p[1]), RT_LDG(&p->p[2])), v3(RT_LDG(&p->n[0]), RT_LDG(&p->n[1]), RT_LDG(&p->n[2])), t)) {
+            if (t != t) s.nan = true;
+            else if (shadow_hit_counts(t, range2)) s.any = true;
+        }
+    }
+}
+RT_HD bool shadow_result(const Shadow& s, double range2) { return s.nan ? (range2 < 0.0) : s.any; }
+
+// ---------------------------------------------------------------------------------------------------------
+// BVH traversal.  The box test is a conservative filter (f32 boxes rounded outward at build time, widened per
+// ray by `pad`); the leaf test is the same f64 expression as the linear scan, so the result is the scan's.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int BVH_STACK = 96;          // >= 63 Morton bits + 32 tie-break bits
+#define RT_BVH_TSLACK 1.000000000001   // relative slack on t comparisons of the filter
+
+struct BoxRay {
+    double ix, iy, iz;     // clamped reciprocal direction
+    double px, py, pz;     // (o + pad) * inv
+    double mx, my, mz;     // (o - pad) * inv
+    bool finite;
+};
+
+RT_HD double safe_inv(double d) {
+    return fabs(d) < 1e-150 ? copysign(1e150, d) : 1.0 / d;
+}
+
+RT_HD BoxRay make_boxray(const DeviceScene& sc, V3 o, V3 d) {
+    BoxRay b;
+    double s = fmax(fmax(fabs(o.x), fabs(o.y)), fabs(o.z));
+    double dm = fmax(fmax(fabs(d.x), fabs(d.y)), fabs(d.z));
+    // any non-finite origin/direction makes every sphere discriminant NaN (=> miss); skip the tree
+    b.finite = (s < 1e150) && (dm < 1e150) && (o.x == o.x) && (o.y == o.y) && (o.z == o.z) && (d.x == d.x) && (d.y == d.y) && (d.z == d.z);
+    double S = s + sc.bvh_cmax;
+    double E = 64.0 * 2.220446049250313e-16 * S * S;  // bound on the rounding error of the discriminant, in r^2 units
+    double pad = S * 0x1.0p-40 + fmin(E / (2.0 * sc.bvh_rmin), sqrt(E));
+    b.ix = safe_inv(d.x); b.iy = safe_inv(d.y); b.iz = safe_inv(d.z);
+    b.px = (o.x + pad) * b.ix; b.py = (o.y + pad) * b.iy; b.pz = (o.z + pad) * b.iz;
+    b.mx = (o.x - pad) * b.ix; b.my = (o.y - pad) * b.iy; b.mz = (o.z - pad) * b.iz;
+    return b;
+}
+
+// returns entry distance (clamped at 0) if the padded box is hit within [0, bound], else -1
+RT_HD double box_entry(const BoxRay& b, const float* lo, const float* hi, double bound) {
+    double ax = fma((double)lo[0], b.ix, -b.px), bx = fma((double)hi[0], b.ix, -b.mx);
+    double ay = fma((double)lo[1], b.iy, -b.py), by = fma((double)hi[1], b.iy, -b.my);
+    double az = fma((double)lo[2], b.iz, -b.pz), bz = fma((double)hi[2], b.iz, -b.mz);
+    double tn = fmax(fmax(fmin(ax, bx), fmin(ay, by)), fmax(fmin(az, bz), 0.0));
+    double tf = fmin(fmin(fmax(ax, bx), fmax(ay, by)), fmax(az, bz));
+    return (tn <= tf * RT_BVH_TSLACK && tn <= bound) ? tn : -1.0;
+}
+
+#if defined(__CUDA_ARCH__)
+RT_HD BvhNode load_node(const BvhNode* p) {
+    BvhNode n;
+    const float4* q = reinterpret_cast<const float4*>(p);
+    float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), d = __ldg(q + 3);
+    n.lo0[0] = a.x; n.lo0[1] = a.y; n.lo0[2] = a.z; n.hi0[0] = a.w;
+    n.hi0[1] = b.x; n.hi0[2] = b.y; n.lo1[0] = b.z; n.lo1[1] = b.w;
+    n.lo1[2] = c.x; n.hi1[0] = c.y; n.hi1[1] = c.z; n.hi1[2] = c.w;
+    n.c0 = __float_as_int(d.x); n.c1 = __float_as_int(d.y);
+    return n;
+}
+RT_HD float f64_to_f32_down(double x) { return __double2float_rd(x); }
+#else
+RT_HD BvhNode load_node(const BvhNode* p) { return *p; }
+RT_HD float f64_to_f32_down(double x) {
+    float f = (float)x;
+    return ((double)f > x) ? nextafterf(f, -INFINITY) : f;
+}
+#endif
+
+// SHADOW = false: closest hit among spheres merged into `best` (which already holds the plane result).
+// SHADOW = true : sets s.any as soon as one sphere hit counts for the range.
+template <bool SHADOW>
+RT_HD void bvh_traverse(const DeviceScene& sc, const RayQ& r, Closest& best, double range2, Shadow& s) {
+    if (sc.n_spheres == 0) return;
+    BoxRay br = make_boxray(sc, r.o, r.d);
+    if (!br.finite) return;
+    int32_t stack_node[BVH_STACK];
+    float stack_t[BVH_STACK];
+    int sp = 0;
+    int32_t node = 0;
+    double bound;
+    if (SHADOW) bound = range2 < 0.0 ? (double)INFINITY : sqrt(range2) * RT_BVH_TSLACK;
+    else bound = best.t * RT_BVH_TSLACK;  // NaN best never reaches here (caller skips), inf stays inf
+    while (true) {
+        BvhNode n = load_node(sc.bvh_nodes + node);
+        double t0 = box_entry(br, n.lo0, n.hi0, bound);
+        double t1 = box_entry(br, n.lo1, n.hi1, bound);
+        if (t0 >= 0.0 && n.c0 < 0) {
+            int32_t k = ~n.c0;
+            const SphereRec* sp_ = sc.bvh_sph + k;
+            double t;
+            if (sphere_hit(r, RT_LDG(&sp_->cx), RT_LDG(&sp_->cy), RT_LDG(&sp_->cz), RT_LDG(&sp_->r2), t)) {
+                if (SHADOW) {
+                    if (shadow_hit_counts(t, range2)) { s.any = true; return; }
+                } else {
+                    closest_update(best, t, RT_LDG(sc.bvh_obj + k));
+                    bound = best.t * RT_BVH_TSLACK;
+                }
+            }
+            t0 = -1.0;
+        }
+        if (t1 >= 0.0 && n.c1 < 0) {
+            if (t1 <= bound) {
+                int32_t k = ~n.c1;
+                const SphereRec* sp_ = sc.bvh_sph + k;
+                double t;
+                if (sphere_hit(r, RT_LDG(&sp_->cx), RT_LDG(&sp_->cy), RT_LDG(&sp_->cz), RT_LDG(&sp_->r2), t)) {
+                    if (SHADOW) {
+                        if (shadow_hit_counts(t, range2)) { s.any = true; return; }
+                    } else {
+                        closest_update(best, t, RT_LDG(sc.bvh_obj + k));
+                        bound = best.t * RT_BVH_TSLACK;
+                    }
+                }
+            }
+            t1 = -1.0;
+        }
+        if (t0 >= 0.0 && t0 > bound) t0 = -1.0;
+        if (t1 >= 0.0 && t1 > bound) t1 = -1.0;
+        if (t0 >= 0.0 && t1 >= 0.0) {
+            int32_t nearc = n.c0, farc = n.c1;
+            double tfar = t1;
+            if (t1 < t0) { nearc = n.c1; farc = n.c0; tfar = t0; }
+            if (sp < BVH_STACK) { stack_node[sp] = farc; stack_t[sp] = f64_to_f32_down(tfar); sp++; }
+            node = nearc;
+            continue;
+        }
+        if (t0 >= 0.0) { node = n.c0; continue; }
+        if (t1 >= 0.0) { node = n.c1; continue; }
+        bool found = false;
+        while (sp > 0) {
+            --sp;
+            if ((double)stack_t[sp] <= bound) { node = stack_node[sp]; found = true; break; }
+        }
+        if (!found) return;
+    }
+}
+
+// Scene::intersect through the BVH
+RT_HD void closest_bvh(const DeviceScene& sc, const RayQ& r, int32_t& id, double& t) {
+    Closest best = closest_none();
+    planes_closest(sc, r, best);
+    if (!best.nan) {
+        Shadow dummy; dummy.nan = false; dummy.any = false;
+        bvh_traverse<false>(sc, r, best, -1.0, dummy);
+    }
+    id = closest_id(best);
+    t = best.t;
+}
+RT_HD bool shadow_bvh(const DeviceScene& sc, const RayQ& r, double range2) {
+    Shadow s; s.nan = false; s.any = false;
+    planes_shadow(sc, r, range2, s);
+    if (!s.nan && !s.any) {
+        Closest dummy = closest_none();
+        bvh_traverse<true>(sc, r, dummy, range2, s);
+    }
+    return shadow_result(s, range2);
+}
+
+// plain scan over global memory (emulation harness and tiny batches; the kernel stages tiles through smem)
+RT_HD void closest_linear(const DeviceScene& sc, const RayQ& r, int32_t& id, double& t) {
+    Closest best = closest_none();
+    planes_closest(sc, r, best);
+    if (!best.nan) {
+        for (uint32_t k = 0; k < sc.n_spheres; k++) {
+            const SphereRec* s = sc.sph + k;
+            double th;
+            if (sphere_hit(r, RT_LDG(&s->cx), RT_LDG(&s->cy), RT_LDG(&s->cz), RT_LDG(&s->r2), th)) closest_update(best, th, RT_LDG(sc.sph_obj + k));
+        }
+    }
+    id = closest_id(best);
+    t = best.t;
+}
+RT_HD bool shadow_linear(const DeviceScene& sc, const RayQ& r, double range2) {
+    Shadow s; s.nan = false; s.any = false;
+    planes_shadow(sc, r, range2, s);
+    if (!s.nan && !s.any) {
+        for (uint32_t k = 0; k < sc.n_spheres; k++) {
+            const SphereRec* q = sc.sph + k;
+            double th;
+            if (sphere_hit(r, RT_LDG(&q->cx), RT_LDG(&q->cy), RT_LDG(&q->cz), RT_LDG(&q->r2), th) && shadow_hit_counts(th, range2)) { s.any = true; break; }
+        }
+    }
+    return shadow_result(s, range2);
+}
+
+// normal the shape's `intersect` returns (src/shapes.rs:72,79 / :108)
+RT_HD V3 shape_normal(const DeviceScene& sc, int32_t obj, V3 o, V3 d, double t) {
+    uint32_t sh = RT_LDG(sc.obj_shape + obj);
+    if (sh & 0x80000000u) {
+        const PlaneRec* p = sc.planes + (sh & 0x7FFFFFFFu);
+        return v3(RT_LDG(&p->n[0]), RT_LDG(&p->n[1]), RT_LDG(&p->n[2]));
+    }
+    const SphereRec* s = sc.sph + sh;
+    V3 c = v3(RT_LDG(&s->cx), RT_LDG(&s->cy), RT_LDG(&s->cz));
+    return normalize((o + d * t) - c);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// backgrounds + bilinear texture (src/raytrace.rs:228-256, src/texture.rs:26-58, src/color.rs:611-613)
+// ---------------------------------------------------------------------------------------------------------
+RT_HD double clamp01(double x) { return x < 0.0 ? 0.0 : (x > 1.0 ? 1.0 : x); }
+RT_HD uint32_t f64_as_u32(double x) {  // Rust `as u32`: saturating, NaN -> 0
+    if (!(x > 0.0)) return 0u;
+    if (x >= 4294967295.0) return 4294967295u;
+    return (uint32_t)x;
+}
+RT_HD C3 tex_at(const DeviceScene& sc, const TextureRec& t, uint32_t x, uint32_t y) {
+    size_t idx = 3 * ((size_t)x + (size_t)y * t.width);
+    return c3(RT_LDG(sc.srgb_values + RT_LDG(t.data + idx)), RT_LDG(sc.srgb_values + RT_LDG(t.data + idx + 1)), RT_LDG(sc.srgb_values + RT_LDG(t.data + idx + 2)));
+}
+RT_HD C3 tex_sample(const DeviceScene& sc, const TextureRec& t, double xs, double ys) {
+    double x = clamp01(xs) * (double)(t.width - 1);
+    double y = clamp01(ys) * (double)(t.height - 1);
+    uint32_t x0 = f64_as_u32(x);
+    uint32_t x1 = x0 >= t.width - 1 ? t.width - 1 : x0 + 1;
+    double xx = x - (double)x0;
+    uint32_t y0 = f64_as_u32(y);
+    uint32_t y1 = y0 >= t.height - 1 ? t.height - 1 : y0 + 1;
+    double yy = y - (double)y0;
+    C3 cx0 = tex_at(sc, t, x0, y0) * (1.0 - yy) + tex_at(sc, t, x0, y1) * yy;
+    C3 cx1 = tex_at(sc, t, x1, y0) * (1.0 - yy) + tex_at(sc, t, x1, y1) * yy;
+    return cx0 * (1.0 - xx) + cx1 * xx;
+}
+RT_HD C3 background_color(const DeviceScene& sc, V3 d) {
+    if (sc.bg_kind == BG_SOLID) return c3(sc.bg_color);
+    double ax = fabs(d.x), ay = fabs(d.y), az = fabs(d.z);
+    if (ax > az && ax > ay) {
+        double px = -d.z / d.x, py = -d.y / ax;
+        return tex_sample(sc, sc.faces[d.x > 0.0 ? 0 : 1], px * 0.5 + 0.5, py * 0.5 + 0.5);
+    }
+    if (ay > ax && ay > az) {
+        double px = d.x / ay, py = d.z / d.y;
+        return tex_sample(sc, sc.faces[d.y > 0.0 ? 2 : 3], px * 0.5 + 0.5, py * 0.5 + 0.5);
+    }
+    if (az > ax && az > ay) {
+        double px = d.x / d.z, py = -d.y / az;
+        return tex_sample(sc, sc.faces[d.z > 0.0 ? 4 : 5], px * 0.5 + 0.5, py * 0.5 + 0.5);
+    }
+    return c3(0.0, 0.0, 0.0);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// quantiser (src/color.rs:593-600): smallest i with val < SRGB_AVERAGE[i], else 255.  The table is strictly
+// increasing, so a binary search returns the same index as the reference's linear scan (NaN -> 255).
+// ---------------------------------------------------------------------------------------------------------
+RT_HD uint8_t to_srgb(const double* avg, double val) {
+    int lo = 0, hi = 255;  // answer in [lo, hi]
+    while (lo < hi) {
+        int mid = (lo + hi) >> 1;
+        if (val < avg[mid]) hi = mid;
+        else lo = mid + 1;
+    }
+    return (uint8_t)lo;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// shading (src/raytrace.rs:30-226) in path-throughput form.
+//
+// The reference's colour recursion is linear in every child colour, so a node's contribution to its pixel is
+// throughput (x) local terms, and each child inherits throughput (x) weight.  shade_begin does the
+// part before the light loop, shade_light one iteration of the light loop, shade_child one spawned ray.
+// ---------------------------------------------------------------------------------------------------------
+struct ShadeCtx {
+    V3 d;           // incoming direction
+    V3 pt, normal;  // hit point, viewer-facing normal
+    C3 T;           // throughput
+    C3 mdiff, mspec;
+    double exponent, sig, ssig, fresnel;
+    double ndv, omf;
+    V3 refr;  // normalised refraction direction
+    uint64_t key;
+    uint32_t depth, samples;
+    int32_t kind;
+    bool alive;  // hit, depth <= max_depth
+    bool diffuse, specular, lit, has_refr;
+};
+
+struct ShadowRay {
+    V3 o, d;
+    double range2;
+    C3 c;
+};
+struct ChildRay {
+    V3 o, d;
+    C3 T;
+    double sig;
+    uint64_t key;
+};
+
+// Returns the immediate pixel contribution (throughput x ambient, or throughput x background on a miss).
+RT_HD C3 shade_begin(const DeviceScene& sc, const FrameParams& fp, V3 o, V3 d, C3 T, double sig, uint64_t key, uint32_t depth, int32_t hit_id,
+                     double hit_t, ShadeCtx& s) {
+    s.alive = false; s.lit = false; s.diffuse = false; s.specular = false; s.has_refr = false;
+    s.kind = -1; s.samples = 0;
+    if (hit_id < 0) return T * background_color(sc, d);
+    const MaterialRec* m = sc.materials + RT_LDG(sc.obj_material + hit_id);
+    const int32_t kind = RT_LDG(&m->kind);
+    C3 ambient = kind == MAT_TRANSPARENT ? c3(0.0, 0.0, 0.0) : c3(RT_LDG(&m->ambient[0]), RT_LDG(&m->ambient[1]), RT_LDG(&m->ambient[2]));
+    C3 add = T * ambient;
+    if (depth > fp.max_depth) return add;  // src/raytrace.rs:33,72,126,172
+    s.alive = true;
+    s.kind = kind;
+    s.d = d; s.T = T; s.sig = sig; s.key = key; s.depth = depth;
+    s.mdiff = c3(RT_LDG(&m->diffuse[0]), RT_LDG(&m->diffuse[1]), RT_LDG(&m->diffuse[2]));
+    s.mspec = c3(RT_LDG(&m->specular[0]), RT_LDG(&m->specular[1]), RT_LDG(&m->specular[2]));
+    s.exponent = RT_LDG(&m->exponent);
+    s.samples = RT_LDG(&m->samples);
+    s.ssig = significance(s.mspec);
+    s.pt = o + d * hit_t;
+    V3 rn = shape_normal(sc, hit_id, o, d, hit_t);
+    double nd = dot(rn, d);
+    s.normal = nd > 0.0 ? -rn : rn;
+    s.fresnel = 1.0;
+    s.omf = 0.0;
+    s.ndv = 0.0;
+    if (kind == MAT_PHONG || kind == MAT_INDIRECT) {
+        s.diffuse = significance(s.mdiff) * sig > fp.min_significance;
+        s.specular = s.ssig * sig > fp.min_significance;
+        s.lit = s.diffuse || s.specular;
+    } else {
+        double ior = RT_LDG(&m->ior);
+        double r0 = (ior - 1.0) / (ior + 1.0);
+        r0 = r0 * r0;
+        if (kind == MAT_FRESNEL) {
+            double omcos = 1.0 - fabs(nd);
+            double omcos2 = omcos * omcos;
+            s.fresnel = clamp_one(r0 + (1.0 - r0) * omcos2 * omcos2 * omcos);
+            s.diffuse = significance(s.mdiff) * sig > fp.min_significance;
+            s.specular = s.ssig * s.fresnel * sig > fp.min_significance;
+            s.lit = s.diffuse || s.specular;
+        } else {  // MAT_TRANSPARENT, src/raytrace.rs:169-226
+            s.ndv = dot(s.normal, d);
+            double n = nd > 0.0 ? ior : 1.0 / ior;
+            double sin2 = n * n * (1.0 - nd * nd);
+            bool has = sin2 < 1.0;
+            V3 refract = v3(0.0, 0.0, 0.0);
+            if (has) {
+                double cs = sqrt(1.0 - sin2);
+                refract = d * n - s.normal * (n * fabs(nd) + cs);
+            }
+            double omcos = nd > 0.0 ? (has ? 1.0 - dot(s.normal, refract) : 0.0) : 1.0 - fabs(nd);
+            double omcos2 = omcos * omcos;
+            s.fresnel = has ? clamp_one(r0 + (1.0 - r0) * omcos2 * omcos2 * omcos) : 1.0;
+            s.specular = s.ssig * s.fresnel * sig > fp.min_significance;
+            s.lit = s.specular;
+            if (s.fresnel < 1.0 && has) {
+                s.has_refr = true;
+                s.omf = clamp_one(1.0 - s.fresnel);
+                s.refr = normalize(refract);
+            }
+        }
+    }
+    return add;
+}
+
+// one iteration of `for light in &scene.lights` (src/raytrace.rs:39-58 and its three siblings).
+// Returns false when this hit casts no shadow ray towards light li.
+RT_HD bool shade_light(const DeviceScene& sc, const ShadeCtx& s, uint32_t li, ShadowRay& out) {
+    if (!s.alive || !s.lit) return false;
+    const LightRec* l = sc.lights + li;
+    const int32_t lk = RT_LDG(&l->kind);
+    V3 la = v3(RT_LDG(&l->a[0]), RT_LDG(&l->a[1]), RT_LDG(&l->a[2]));
+    V3 ldir;
+    double range2;
+    if (lk == LIGHT_DIRECTIONAL) {  // src/scene.rs:136-138
+        ldir = -la;
+        range2 = -1.0;
+    } else {
+        V3 loc = la;
+        if (lk == LIGHT_AREA) {  // src/scene.rs:151-155
+            double u1 = draw_f64(s.key, 2 + 2 * (uint64_t)li);
+            double u2 = draw_f64(s.key, 3 + 2 * (uint64_t)li);
+            V3 s1 = v3(RT_LDG(&l->s1[0]), RT_LDG(&l->s1[1]), RT_LDG(&l->s1[2]));
+            V3 s2 = v3(RT_LDG(&l->s2[0]), RT_LDG(&l->s2[1]), RT_LDG(&l->s2[2]));
+            loc = la + s1 * u1 + s2 * u2;
+        }
+        V3 diff = v3(loc.x - s.pt.x, loc.y - s.pt.y, loc.z - s.pt.z);  // src/scene.rs:124-126
+        ldir = normalize(diff);
+        range2 = sqnorm(diff);
+    }
+    C3 lcol = c3(RT_LDG(&l->color[0]), RT_LDG(&l->color[1]), RT_LDG(&l->color[2]));
+    C3 c = c3(0.0, 0.0, 0.0);
+    if (s.diffuse) c = c + s.T * (s.mdiff * lcol * clamp_zero(dot(ldir, s.normal)) * RT_FRAC_1_PI);
+    if (s.specular) {
+        double pw = pow(clamp_zero(dot(s.normal, normalize(ldir - s.d))), s.exponent);
+        C3 sl = s.mspec * lcol;
+        if (s.kind == MAT_FRESNEL || s.kind == MAT_TRANSPARENT) sl = sl * s.fresnel;
+        c = c + s.T * (sl * pw);
+    }
+    out.o = s.pt + ldir * 0.00001;
+    out.d = ldir;
+    out.range2 = range2;
+    out.c = c;
+    return true;
+}
+
+// child slot k of this hit: 0 = reflection (Phong/Fresnel/Transparent), 1 = refraction (Transparent),
+// k < samples = hemisphere sample k (IndirectPhong).  Returns false when the slot spawns nothing.
+RT_HD bool shade_child(const DeviceScene& sc, const ShadeCtx& s, uint32_t k, ChildRay& out) {
+    if (!s.alive) return false;
+    if (s.kind == MAT_INDIRECT) {  // src/raytrace.rs:98-117
+        if (!s.lit || k >= s.samples) return false;
+        const uint64_t dim0 = 2 + 2 * (uint64_t)sc.n_lights + 2 * (uint64_t)k;
+        double r1 = draw_f64(s.key, dim0) * 2.0 - 1.0;
+        double r2 = draw_f64(s.key, dim0 + 1) * (2.0 * RT_PI);
+        double sin_theta = 1.0 - r1 * r1;  // sic (src/raytrace.rs:103)
+        double x = sin_theta * cos(r2);
+        double z = sin_theta * sin(r2);
+        V3 d0 = v3(x, r1, z);
+        V3 dir = dot(d0, s.normal) >= 0.0 ? d0 : -d0;
+        double fac = (double)s.samples * 0.5;
+        C3 w = c3(0.0, 0.0, 0.0);
+        if (s.diffuse) w = w + s.mdiff * dot(s.normal, dir) / fac;
+        if (s.specular) {
+            // upstream evaluates normalize(dir - ray.direction) with `ray` shadowed by the new ray, i.e. the
+            // zero vector: 0/0 = NaN (src/raytrace.rs:108,115).  Kept: it defines the output.
+            V3 h = normalize(dir - dir);
+            w = w + s.mspec * pow(clamp_zero(dot(s.normal, h)), s.exponent) / fac;
+        }
+        out.o = s.pt + dir * 0.00001;
+        out.d = dir;
+        out.T = s.T * w;
+        out.sig = s.sig;
+        out.key = child_key(s.key, CODE_INDIRECT0 + k);
+        return true;
+    }
+    if (k == 0) {
+        if (!s.specular) return false;
+        V3 rd;
+        if (s.kind == MAT_TRANSPARENT) rd = s.d - s.normal * (2.0 * s.ndv);       // src/raytrace.rs:210
+        else rd = s.d - s.normal * (2.0 * dot(s.d, s.normal));                    // src/raytrace.rs:61,161
+        out.o = s.pt + rd * 0.00001;
+        out.d = rd;
+        if (s.kind == MAT_PHONG) {
+            out.T = s.T * s.mspec;
+            out.sig = s.sig * s.ssig;
+        } else {
+            out.T = s.T * s.mspec * s.fresnel;
+            out.sig = s.fresnel * s.sig * s.ssig;
+        }
+        out.key = child_key(s.key, CODE_REFLECT);
+        return true;
+    }
+    if (k == 1 && s.kind == MAT_TRANSPARENT && s.has_refr) {  // src/raytrace.rs:214-223
+        out.o = s.pt + s.refr * 0.00001;
+        out.d = s.refr;
+        out.T = s.T * s.omf;
+        out.sig = s.omf * s.sig;
+        out.key = child_key(s.key, CODE_REFRACT);
+        return true;
+    }
+    return false;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// image-space shard mapping: tile-ordered pixel slot -> (x, global y, local pixel index)
+// A sample plane is npix_padded slots; slot q covers tile q/32 (8 wide x 4 high), lane q%32.
+// ---------------------------------------------------------------------------------------------------------
+RT_HD bool slot_to_pixel(const FrameParams& fp, uint64_t q, uint32_t& x, uint32_t& y, uint32_t& local_pixel) {
+    uint32_t tile = (uint32_t)(q >> 5), lane = (uint32_t)(q & 31);
+    uint32_t tx = tile % fp.tiles_x, ty = tile / fp.tiles_x;
+    x = tx * 8 + (lane & 7);
+    uint32_t yl = ty * 4 + (lane >> 3);
+    uint32_t band = yl / fp.band_rows;
+    y = (band * fp.world + fp.rank) * fp.band_rows + yl % fp.band_rows;
+    local_pixel = yl * fp.width + x;
+    return x < fp.width && yl < fp.local_rows && y < fp.height;
+}
+
+// final-image word w (4 bytes) -> index of the same word in the rank-major all-gathered buffer
+RT_HD uint64_t untile_source_word(uint64_t w, uint32_t words_per_row, uint32_t band_rows, uint32_t world, uint32_t local_rows) {
+    const uint32_t y = (uint32_t)(w / words_per_row);
+    const uint32_t c = (uint32_t)(w - (uint64_t)y * words_per_row);
+    const uint32_t band = y / band_rows;
+    const uint32_t rank = band % world;
+    const uint32_t yl = (band / world) * band_rows + y % band_rows;
+    return ((uint64_t)rank * local_rows + yl) * words_per_row + c;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// LBVH construction helpers (Morton codes, Karras 2012 hierarchy); the kernels in bvh_build.cu call these
+// ---------------------------------------------------------------------------------------------------------
+RT_HD uint64_t spread21(uint64_t v) {
+    v &= 0x1FFFFFULL;
+    v = (v | (v << 32)) & 0x001F00000000FFFFULL;
+    v = (v | (v << 16)) & 0x001F0000FF0000FFULL;
+    v = (v | (v << 8)) & 0x100F00F00F00F00FULL;
+    v = (v | (v << 4)) & 0x10C30C30C30C30C3ULL;
+    v = (v | (v << 2)) & 0x1249249249249249ULL;
+    return v;
+}
+RT_HD uint64_t morton63(double cx, double cy, double cz, const double* lo, const double* inv_ext) {
+    double fx = (cx - lo[0]) * inv_ext[0], fy = (cy - lo[1]) * inv_ext[1], fz = (cz - lo[2]) * inv_ext[2];
+    fx = fmin(fmax(fx * 2097152.0, 0.0), 2097151.0);
+    fy = fmin(fmax(fy * 2097152.0, 0.0), 2097151.0);
+    fz = fmin(fmax(fz * 2097152.0, 0.0), 2097151.0);
+    if (!(fx == fx)) fx = 0.0;
+    if (!(fy == fy)) fy = 0.0;
+    if (!(fz == fz)) fz = 0.0;
+    return (spread21((uint64_t)fx) << 2) | (spread21((uint64_t)fy) << 1) | spread21((uint64_t)fz);
+}
+
+RT_HD int clz64(uint64_t x) {
+#if defined(__CUDA_ARCH__)
+    return __clzll((long long)x);
+#else
+    return x ? __builtin_clzll(x) : 64;
+#endif
+}
+// common-prefix length of sorted keys i and j (position as tie-break); -1 outside [0, n)
+RT_HD int lbvh_delta(const uint64_t* keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    uint64_t a = RT_LDG(keys + i), b = RT_LDG(keys + j);
+    if (a != b) return clz64(a ^ b);
+    return 64 + clz64((uint64_t)(uint32_t)i ^ (uint64_t)(uint32_t)j);
+}
+// internal node i of a tree over n >= 2 sorted leaves: children (internal index, or ~leaf)
+RT_HD void lbvh_node(const uint64_t* keys, int n, int i, int32_t& left, int32_t& right) {
+    int d = (lbvh_delta(keys, n, i, i + 1) - lbvh_delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    int dmin = lbvh_delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (lbvh_delta(keys, n, i, i + lmax * d) > dmin) lmax *= 2;
+    int l = 0;
+    for (int t = lmax / 2; t >= 1; t /= 2)
+        if (lbvh_delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    int j = i + l * d;
+    int dnode = lbvh_delta(keys, n, i, j);
+    int s = 0;
+    int t = l;
+    do {
+        t = (t + 1) >> 1;
+        if (lbvh_delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+    } while (t > 1);
+    int gamma = i + s * d + (d < 0 ? -1 : 0);
+    int lo = i < j ? i : j, hi = i < j ? j : i;
+    left = (lo == gamma) ? ~gamma : gamma;
+    right = (hi == gamma + 1) ? ~(gamma + 1) : gamma + 1;
+}
+
+}  // namespace RT_NS
+}  // namespace rt
