@@ -1,0 +1,251 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle on the same seeded inputs.
+
+Bars (BASELINE.json north_star): primary hit ids bit-exact; every byte of the quantised frame within +-1 LSB and
+>= 99.9 % identical; ray counts (Scene::intersect calls) equal.  In RT_FP_STRICT mode geometry is the same
+unfused f64 arithmetic as the oracle, so hit distances are required to be bit-identical too.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+REF_TEXT_SCENE = """
+{
+    objects: [
+        { bounds: Plane { point: (0, 0, -3) normal: (0, 0, 1) }
+          material: IndirectPhongMaterial { diffuse: rgb(1.0, 1.0, 1.0) specular: rgb(0.0, 0.0, 0.0) exponent: 1.0 ambient: rgb(0.0, 0.0, 0.0) samples: 1 } }
+        { bounds: Plane { point: (0, 0, 0) normal: (0, 1.0, 0) }
+          material: IndirectPhongMaterial { diffuse: rgb(1.0, 1.0, 1.0) specular: rgb(0.0, 0.0, 0.0) exponent: 1.0 ambient: rgb(0.0, 0.0, 0.0) samples: 1 } }
+        { bounds: Plane { point: (0, 6, 0) normal: (0, -1.0, 0) }
+          material: IndirectPhongMaterial { diffuse: rgb(1.0, 1.0, 1.0) specular: rgb(0.0, 0.0, 0.0) exponent: 1.0 ambient: rgb(0.0, 0.0, 0.0) samples: 1 } }
+        { bounds: Plane { point: (-3, 0, 0) normal: (1, 0, 0) }
+          material: IndirectPhongMaterial { diffuse: rgb(1.0, 0.0, 0.0) specular: rgb(0.0, 0.0, 0.0) exponent: 1.0 ambient: rgb(0.0, 0.0, 0.0) samples: 1 } }
+        { bounds: Plane { point: (3, 0, 0) normal: (-1, 0, 0) }
+          material: IndirectPhongMaterial { diffuse: rgb(0.0, 1.0, 0.0) specular: rgb(0.0, 0.0, 0.0) exponent: 1.0 ambient: rgb(0.0, 0.0, 0.0) samples: 1 } }
+        { bounds: Sphere { center: (0, 1.5, 0) radius: 1.5 }
+          material: IndirectPhongMaterial { diffuse: rgb(1.0, 1.0, 1.0) specular: rgb(0.0, 0.0, 0.0) exponent: 1.0 ambient: rgb(0.0, 0.0, 0.0) samples: 1 } }
+        { bounds: Sphere { center: (0, 10.65, 0) radius: 5 }
+          material: IndirectPhongMaterial { diffuse: rgb(1.0, 1.0, 1.0) specular: rgb(0.0, 0.0, 0.0) exponent: 1.0 ambient: rgb(5.0, 5.0, 5.0) samples: 1 } }
+    ]
+    lights: [ ]
+    camera: SimplePerspectiveCamera new((0, 3, 17), (0, 0, -1), (0, 1, 0), 3.6)
+    background: SolidColorBackground { color: rgb(0.051, 0.051, 0.051) }
+    options: { width: 800 height: 800 antialias: 1024 }
+}
+"""
+# the same Cornell-box configuration as the upstream test_scene.txt (values restated, file not copied)
+
+
+def assert_parity(frame, ref, what, exact=False):
+    assert np.array_equal(frame.ids, ref["ids"]), "%s: primary hit ids differ in %d pixels" % (what, int((frame.ids != ref["ids"]).sum()))
+    a, b = frame.rows.astype(np.int16), ref["bgr"].astype(np.int16)
+    assert a.shape == b.shape
+    diff = np.abs(a - b)
+    assert diff.max() <= 1, "%s: a byte differs by %d LSB" % (what, int(diff.max()))
+    same = float((diff == 0).mean())
+    assert same >= 0.999, "%s: only %.5f of the bytes identical" % (what, same)
+    if exact:
+        assert same == 1.0, "%s: %d bytes differ" % (what, int((diff != 0).sum()))
+    assert frame.stats["rays_total"] == ref["stats"]["rays"], "%s: ray count %d vs oracle %d" % (what, frame.stats["rays_total"], ref["stats"]["rays"])
+    assert frame.stats["rays_shadow"] == ref["stats"]["shadow_rays"]
+    return same
+
+
+def test_quantiser(gpu, orc):
+    v, a = orc.srgb_tables()
+    rng = np.random.default_rng(1)
+    vals = np.concatenate([a, np.nextafter(a, -np.inf), np.nextafter(a, np.inf), v, rng.uniform(-0.1, 1.2, 50000),
+                           [0.0, -1.0, 0.051, 0.18, 0.5, 1.0, 5.0, np.nan, np.inf, -np.inf, -0.0]])
+    vals = np.resize(vals, (vals.size // 3) * 3).reshape(-1, 3)
+    assert np.array_equal(gpu.color.write_bgr(vals), orc.quantize_bgr(vals))
+
+
+def _random_rays(rng, n, extent, ymax):
+    o = np.stack([rng.uniform(-extent, extent, n), rng.uniform(0.1, ymax, n), rng.uniform(-extent, extent, n)], axis=1)
+    d = rng.normal(size=(n, 3))
+    d[: n // 2] /= np.linalg.norm(d[: n // 2], axis=1, keepdims=True)  # half unit, half un-normalised directions
+    return np.concatenate([o, d], axis=1)
+
+
+@pytest.mark.parametrize("accel", ["linear", "bvh"])
+@pytest.mark.parametrize("fp_mode", ["strict", "fast"])
+def test_intersect_random_rays(gpu, orc, scenes, accel, fp_mode):
+    desc = scenes.random_spheres(3000, 77, 30.0, 64, 64)
+    sc = gpu.Scene(desc)
+    rays = _random_rays(np.random.default_rng(5), 200_000, 35.0, 9.0)
+    # rays leaving sphere surfaces (secondary-ray geometry) and rays from inside spheres
+    data = desc["objects"][1]["data"]
+    inside = np.concatenate([data[:2000, :3], np.random.default_rng(6).normal(size=(2000, 3))], axis=1)
+    rays = np.concatenate([rays, inside])
+    ids, t, nrm = gpu.raytrace.intersect(sc, rays, accel=gpu.ACCEL_BVH if accel == "bvh" else gpu.ACCEL_LINEAR,
+                                         fp_mode=gpu.FP_FAST if fp_mode == "fast" else gpu.FP_STRICT)
+    rid, rt_, rn = orc.OracleScene(desc).trace_rays(rays)
+    if fp_mode == "strict":
+        assert np.array_equal(ids, rid)
+        assert np.array_equal(t, rt_), "hit distances must be bit-identical in strict mode"
+        assert np.array_equal(nrm, rn)
+    else:
+        assert (ids != rid).mean() < 1e-5
+        ok = ids == rid
+        assert np.allclose(t[ok], rt_[ok], rtol=1e-9, atol=0)
+
+
+def test_intersect_edge_cases(gpu, orc):
+    S = gpu.scene
+    b = S.SceneBuilder()
+    m = b.add_material(S.PhongMaterial((0.5, 0.5, 0.5), (0, 0, 0), 1.0, (0, 0, 0)))
+    b.add_object(S.Plane((0, 0, -3), (0, 0, 1)), m)       # 0
+    b.add_object(S.Sphere((0, 1.5, 0), 1.5), m)           # 1
+    b.add_object(S.Sphere((0, 1.5, 0), 1.5), m)           # 2 coincident with 1 -> lower index wins
+    b.add_object(S.Plane((0, -1, 0), (0, 1, 0)), m)       # 3
+    b.add_object(S.Sphere((5, 5, 5), 1.0), m)             # 4
+    b.camera = S.SimplePerspectiveCamera.new((0, 3, 17), (0, 0, -1), (0, 1, 0), 3.6)
+    b.background = S.SolidColorBackground((0, 0, 0))
+    b.options = S.Options(8, 8, 1)
+    desc = b.build()
+    rays = np.array([
+        [0, 3, 17, 0, 0, -1],        # exactly tangent to sphere 1 (disc == 0 -> miss), hits plane 0 at t = 20
+        [0, 1.5, 17, 0, 0, -1],      # through the centre of spheres 1/2 -> id 1
+        [0, 1.5, 0, 0, 0, 1],        # from inside the spheres -> far root
+        [0, 1.5, 0, 0, 0, -2.5],     # inside, un-normalised direction
+        [0, 5, 5, 1, 0, 0],          # parallel to plane 3 with positive numerator?  n.(p-o) = -6 -> -inf -> rejected
+        [0, -5, 5, 1, 0, 0],         # parallel, numerator +4 -> t = +inf accepted unless something closer (sphere 4? no)
+        [0, -1, 5, 1, 0, 0],         # in plane 3: 0/0 = NaN -> plane 3 wins whatever else is hit
+        [5, -1, 5, 0, 0.0, 0.0],     # zero direction
+        [5, 20, 5, 0, -1, 0],        # straight down through sphere 4 then plane 3
+        [np.nan, 0, 0, 0, 0, -1],
+        [0, 1, 30, 0, 0, -1e-3],     # tiny direction length
+    ], dtype=np.float64)
+    ref = orc.OracleScene(desc).trace_rays(rays)
+    for accel in (gpu.ACCEL_LINEAR, gpu.ACCEL_BVH):
+        ids, t, nrm = gpu.raytrace.intersect(gpu.Scene(desc), rays, accel=accel)
+        assert np.array_equal(ids, ref[0]), (accel, ids, ref[0])
+        assert np.array_equal(t, ref[1], equal_nan=True), (accel, t, ref[1])
+        assert np.array_equal(nrm, ref[2], equal_nan=True)
+    assert ref[0][0] == 0 and ref[1][0] == 20.0 and ref[0][1] == 1 and ref[0][6] == 3 and np.isnan(ref[1][6])
+
+
+def test_project(gpu, orc):
+    S = gpu.scene
+    rng = np.random.default_rng(3)
+    pos = rng.uniform(-1.5, 1.5, size=(5000, 2))
+    cam = S.SimplePerspectiveCamera.look_at((0.3, 1.0, -2.0), (0.2, -0.3, -1.0), (0.0, 1.0, 0.1), np.deg2rad(40.0), 2.5)
+    for dof in (None, dict(focus=7.5, aperture=0.2, samples=3)):
+        b = S.SceneBuilder()
+        b.camera = dict(cam, dof=dof) if dof else cam
+        b.background = S.SolidColorBackground((0, 0, 0))
+        b.options = S.Options(4, 4, 1)
+        desc = b.build()
+        got = gpu.raytrace.project(gpu.Scene(desc), pos, seed=9)
+        ref = orc.OracleScene(desc).project(pos, seed=9)
+        if dof is None:
+            assert np.array_equal(got, ref)
+        else:
+            assert np.allclose(got, ref, rtol=1e-12, atol=1e-13)  # sin/cos: CUDA libm vs glibc, <= 2 ulp
+
+
+def test_render_cornell_text(gpu, orc):
+    from oracle import scene_text
+    desc = scene_text.deserialize(REF_TEXT_SCENE)
+    sc = gpu.serialize.deserialize(REF_TEXT_SCENE)
+    assert sc.options() == (800, 800, 1024)
+    kw = dict(width=240, height=200, antialias=3, seed=21)
+    ref = orc.OracleScene(desc).render(**kw)
+    fr = gpu.raytrace.render(sc, **kw)
+    assert_parity(fr, ref, "cornell")
+    assert fr.stats["accel_used"] == gpu.ACCEL_LINEAR
+
+
+@pytest.mark.parametrize("accel", ["linear", "bvh"])
+@pytest.mark.parametrize("fp_mode", ["strict", "fast"])
+def test_render_all_materials(gpu, orc, scenes, accel, fp_mode):
+    desc = scenes.materials_showcase(256, 192, 2)
+    ref = orc.OracleScene(desc).render(max_depth=5, seed=4)
+    fr = gpu.raytrace.render(gpu.Scene(desc), max_depth=5, seed=4, accel=gpu.ACCEL_BVH if accel == "bvh" else gpu.ACCEL_LINEAR,
+                             fp_mode=gpu.FP_FAST if fp_mode == "fast" else gpu.FP_STRICT)
+    if fp_mode == "strict":
+        assert_parity(fr, ref, "showcase/%s/%s" % (accel, fp_mode))
+    else:  # contraction can move a near-threshold significance test: ray counts may differ by a hair
+        assert np.array_equal(fr.ids, ref["ids"])
+        diff = np.abs(fr.rows.astype(np.int16) - ref["bgr"].astype(np.int16))
+        assert diff.max() <= 1 and (diff == 0).mean() >= 0.999
+        assert abs(fr.stats["rays_total"] - ref["stats"]["rays"]) <= 1e-4 * ref["stats"]["rays"]
+
+
+def test_render_spheres_bvh_depth8_text_and_builder(gpu, orc, scenes):
+    desc = scenes.random_spheres(4000, 0x5EED0003, 40.0, 320, 180)
+    ref = orc.OracleScene(desc).render(max_depth=8, seed=3)
+    fr_b = gpu.raytrace.render(gpu.Scene(desc), max_depth=8, seed=3, accel=gpu.ACCEL_BVH)
+    assert_parity(fr_b, ref, "spheres4000/builder")
+    fr_t = gpu.raytrace.render(gpu.serialize.deserialize(gpu.scene.to_text(desc)), max_depth=8, seed=3, accel=gpu.ACCEL_BVH)
+    assert np.array_equal(fr_t.rows, fr_b.rows) and np.array_equal(fr_t.ids, fr_b.ids), "text and builder scenes must render identically"
+    fr_l = gpu.raytrace.render(gpu.Scene(desc), max_depth=8, seed=3, accel=gpu.ACCEL_LINEAR)
+    assert np.array_equal(fr_l.ids, fr_b.ids)
+    assert fr_l.stats["rays_total"] == fr_b.stats["rays_total"]
+    assert (fr_l.rows != fr_b.rows).mean() < 1e-5  # same rays, only the accumulation order may differ
+
+
+def test_render_skybox_dof_area(gpu, orc, scenes):
+    S = gpu.scene
+    desc = scenes.random_spheres(200, 5, 10.0, 200, 144, antialias=2, reflective_only=True,
+                                 background=S.SkyboxBackground(*scenes.skybox_faces(64, 8)),
+                                 camera=S.DepthOfFieldCamera.new(S.SimplePerspectiveCamera.new((0, 4, 14), (0, -0.2, -1), (0, 1, 0), 2.0), 12.0, 0.15, 2))
+    desc["lights"].append(S.AreaLight((-3.0, 9.0, -3.0), (6.0, 0.0, 0.0), (0.0, 0.0, 6.0), (0.6, 0.6, 0.5)))
+    ref = orc.OracleScene(desc).render(max_depth=4, seed=8)
+    fr = gpu.raytrace.render(gpu.Scene(desc), max_depth=4, seed=8)
+    # depth-of-field rays go through sin/cos (libm differs by <= 2 ulp), so ids may differ on a handful of edge pixels
+    assert (fr.ids != ref["ids"]).mean() < 1e-4
+    diff = np.abs(fr.rows.astype(np.int16) - ref["bgr"].astype(np.int16))
+    assert (diff <= 1).mean() >= 0.9999 and (diff == 0).mean() >= 0.999
+
+
+def test_queue_slicing_is_invisible(gpu, scenes):
+    desc = scenes.materials_showcase(160, 120, 2)
+    sc = gpu.Scene(desc)
+    big = gpu.raytrace.render(sc, max_depth=6, seed=2)
+    small = gpu.raytrace.render(sc, max_depth=6, seed=2, max_rays_in_flight=4096)
+    assert np.array_equal(big.ids, small.ids)
+    assert big.stats["rays_total"] == small.stats["rays_total"]
+    assert (big.rows != small.rows).mean() < 1e-5
+    assert small.stats["kernel_launches"] > big.stats["kernel_launches"]
+
+
+def test_antialias_zero_is_nan_white(gpu, scenes):
+    fr = gpu.raytrace.render(gpu.Scene(scenes.materials_showcase(16, 12, 1)), antialias=0)
+    assert (fr.bgr == 255).all()  # 0/0 -> NaN -> code 255 (src/main.rs:56, src/color.rs:593-600)
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_row_band_shards_reassemble(gpu, scenes, world):
+    import torch
+    desc = scenes.random_spheres(500, 9, 15.0, 200, 150)  # 150 rows: not a multiple of band*world
+    sc = gpu.Scene(desc)
+    whole = gpu.raytrace.render(sc, max_depth=4, seed=6)
+    parts, ctxs = [], []
+    for r in range(world):
+        ctx = gpu.Context(sc, max_depth=4, seed=6, rank=r, world=world)
+        ctx.render()
+        ptr, nbytes = ctx.framebuffer_ptr()
+        rows, _, _ = ctx.download()
+        parts.append(torch.from_numpy(rows.reshape(-1)).cuda())
+        assert rows.size == nbytes
+        ctxs.append(ctx)
+    gathered = torch.cat(parts).contiguous()
+    out = torch.zeros(whole.rows.size, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    ctxs[0].untile(gathered.data_ptr(), out.data_ptr())
+    ctxs[0].synchronize()
+    got = out.cpu().numpy().reshape(whole.rows.shape)
+    assert (got != whole.rows).mean() < 1e-5
+    assert np.array_equal(got[:, 600:], whole.rows[:, 600:])  # row padding bytes
+
+
+def test_config2_cornell_4k_1spp(gpu, orc):
+    """BASELINE config 2: test scene at 3840x2160, 1 spp, full-frame pixel match against the CPU oracle."""
+    from oracle import scene_text
+    desc = scene_text.deserialize(REF_TEXT_SCENE)
+    kw = dict(width=3840, height=2160, antialias=1, seed=1)
+    ref = orc.OracleScene(desc).render(want_accum=False, **kw)
+    fr = gpu.raytrace.render(gpu.serialize.deserialize(REF_TEXT_SCENE), **kw)
+    same = assert_parity(fr, ref, "config2")
+    print("config2: identical bytes %.6f, rays %d, %.2f ms" % (same, fr.stats["rays_total"], fr.stats["render_ms"]))
