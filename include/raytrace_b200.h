@@ -141,6 +141,13 @@ typedef struct rt_stats {
     uint32_t local_rows;      /* rows this shard produces (padded to whole bands) */
     uint32_t bytewidth;       /* bytes per output row = (3*width + 3) & ~3 (src/bmp.rs:11) */
     int32_t accel_used, fp_mode_used;
+    /* BVH traversal work of the last render (device counters): 64-byte nodes fetched and exact sphere tests at leaves,
+     * [0] by the closest-hit kernel, [1] by the shadow kernel */
+    uint64_t bvh_nodes_visited[2], bvh_prims_tested[2];
+    /* per-kernel-class device time of the last render; filled only while rt_context_set_profiling(ctx, 1) is on
+     * (one CUDA event pair per launch).  Order: primary, closest, shade, shadow, resolve. */
+    double class_ms[5];
+    uint64_t class_launches[5];
 } rt_stats;
 
 /* One-call frame render: upload, (build BVH), trace, resolve, copy back.
@@ -166,6 +173,10 @@ RT_API int rt_context_download(rt_context*, uint8_t* bgr_rows, int32_t* primary_
  * writes the final bytewidth*height image in BMP row order into `out_dev`.  Runs on the context's device/stream. */
 RT_API int rt_context_untile(rt_context*, const void* gathered_dev, void* out_dev);
 RT_API int rt_context_synchronize(rt_context*);
+/* run on a caller-owned CUDA stream (a cudaStream_t / CUstream handle, e.g. torch's current stream) instead of the
+ * context's own; pass NULL to go back.  The caller keeps the stream alive for as long as it is set. */
+RT_API int rt_context_set_stream(rt_context*, void* cuda_stream);
+RT_API int rt_context_set_profiling(rt_context*, int on);
 
 /* Scene::intersect for a batch of rays (src/scene.rs:247-249): origin xyz + direction xyz per ray.
  * ids: object index or -1; t: hit distance (+inf on miss); normal: shape normal as upstream returns it. */

@@ -128,6 +128,13 @@ class Context:
     def synchronize(self):
         B.check(self._lib, self._lib.rt_context_synchronize(self._h))
 
+    def set_stream(self, cuda_stream):
+        """Run on a caller-owned stream (int handle, e.g. torch.cuda.current_stream().cuda_stream); None = own stream."""
+        B.check(self._lib, self._lib.rt_context_set_stream(self._h, C.c_void_p(cuda_stream or 0)))
+
+    def set_profiling(self, on=True):
+        B.check(self._lib, self._lib.rt_context_set_profiling(self._h, 1 if on else 0))
+
 
 class _Serialize:
     """`serialize` module (src/serialize.rs)."""

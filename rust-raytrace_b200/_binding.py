@@ -24,10 +24,18 @@ class Stats(C.Structure):
     _fields_ = [("rays_total", C.c_uint64), ("rays_primary", C.c_uint64), ("rays_secondary", C.c_uint64), ("rays_shadow", C.c_uint64),
                 ("paths", C.c_uint64), ("kernel_launches", C.c_uint64), ("render_ms", C.c_double), ("bvh_build_ms", C.c_double),
                 ("n_bvh_nodes", C.c_uint64), ("local_rows", C.c_uint32), ("bytewidth", C.c_uint32), ("accel_used", C.c_int32),
-                ("fp_mode_used", C.c_int32)]
+                ("fp_mode_used", C.c_int32), ("bvh_nodes_visited", C.c_uint64 * 2), ("bvh_prims_tested", C.c_uint64 * 2),
+                ("class_ms", C.c_double * 5), ("class_launches", C.c_uint64 * 5)]
+
+    CLASSES = ("primary", "closest", "shade", "shadow", "resolve")
 
     def as_dict(self):
-        return {k: getattr(self, k) for k, _ in self._fields_}
+        d = {k: getattr(self, k) for k, _ in self._fields_ if not k.startswith(("class_", "bvh_nodes_", "bvh_prims_"))}
+        d["bvh_nodes_visited"] = {"closest": int(self.bvh_nodes_visited[0]), "shadow": int(self.bvh_nodes_visited[1])}
+        d["bvh_prims_tested"] = {"closest": int(self.bvh_prims_tested[0]), "shadow": int(self.bvh_prims_tested[1])}
+        d["class_ms"] = dict(zip(self.CLASSES, [float(x) for x in self.class_ms]))
+        d["class_launches"] = dict(zip(self.CLASSES, [int(x) for x in self.class_launches]))
+        return d
 
 
 class SceneInfo(C.Structure):
@@ -91,6 +99,8 @@ API = {
     "rt_context_download": (C.c_int, [C.c_void_p, _u8p, _i32p, _dp]),
     "rt_context_untile": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "rt_context_synchronize": (C.c_int, [C.c_void_p]),
+    "rt_context_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "rt_context_set_profiling": (C.c_int, [C.c_void_p, C.c_int]),
     "rt_trace_rays": (C.c_int, [C.c_void_p, C.POINTER(RenderOpts), C.c_uint64, _dp, _i32p, _dp, _dp]),
     "rt_project": (C.c_int, [C.c_void_p, C.POINTER(RenderOpts), C.c_uint64, _dp, _dp]),
     "rt_quantize_bgr": (C.c_int, [_dp, C.c_uint64, _u8p, C.c_int]),

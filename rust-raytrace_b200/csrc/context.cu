@@ -182,6 +182,23 @@ struct rt_context {
     uint64_t total_paths = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     rt_stats stats{};
+    cudaStream_t own_stream = nullptr;
+    bool profiling = false;
+    std::vector<cudaEvent_t> prof_events;       // pool, two per timed launch
+    std::vector<int> prof_class;                // class of launch i (events 2i, 2i+1)
+
+    // brackets one kernel-class launch with an event pair while profiling is on
+    void prof_begin(int cls) {
+        if (!profiling) return;
+        const size_t i = prof_class.size();
+        while (prof_events.size() < 2 * (i + 1)) { cudaEvent_t e; cudaEventCreate(&e); prof_events.push_back(e); }
+        prof_class.push_back(cls);
+        cudaEventRecord(prof_events[2 * i], stream);
+    }
+    void prof_end() {
+        if (!profiling) return;
+        cudaEventRecord(prof_events[2 * (prof_class.size() - 1) + 1], stream);
+    }
 
     ~rt_context() {
         cudaSetDevice(device);
@@ -189,8 +206,9 @@ struct rt_context {
         if (counters_host) cudaFreeHost(counters_host);
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
+        for (cudaEvent_t e : prof_events) cudaEventDestroy(e);
         scene.release();
-        if (stream) cudaStreamDestroy(stream);
+        if (own_stream) cudaStreamDestroy(own_stream);
     }
 };
 
@@ -210,12 +228,16 @@ int process_level(rt_context* c, uint32_t d, uint32_t n) {
     uint32_t* next_count = &c->counters->level_count[last ? 63 : d + 1];
     for (uint32_t first = 0; first < n; first += c->slice) {
         const uint32_t cnt = std::min(c->slice, n - first);
-        c->k->closest(c->stream, c->scene.ds, c->scene.use_bvh, in, first, cnt, &c->counters->cursor, c->sm_count);
+        c->prof_begin(1);
+        c->k->closest(c->stream, c->scene.ds, c->scene.use_bvh, in, first, cnt, c->counters, c->sm_count);
+        c->prof_end();
         CUDA_TRY(cudaMemsetAsync(next_count, 0, sizeof(uint32_t), c->stream));
         CUDA_TRY(cudaMemsetAsync(&c->counters->shadow_count, 0, sizeof(uint32_t), c->stream));
+        c->prof_begin(2);
         c->k->shade(c->stream, c->scene.ds, c->fp, in, first, cnt, out, next_count, c->shadowq, &c->counters->shadow_count, &c->counters->overflow,
                     c->accum, c->ids);
-        c->stats.kernel_launches += 2 + (c->scene.use_bvh ? 0 : 0);
+        c->prof_end();
+        c->stats.kernel_launches += 2;
         int rc = ctx_fetch_counters(c);
         if (rc != RT_OK) return rc;
         const uint32_t n_shadow = c->counters_host->shadow_count;
@@ -223,7 +245,9 @@ int process_level(rt_context* c, uint32_t d, uint32_t n) {
         if (d == 0) c->stats.rays_primary += cnt; else c->stats.rays_secondary += cnt;
         c->stats.rays_shadow += n_shadow;
         if (n_shadow) {
-            c->k->shadow(c->stream, c->scene.ds, c->scene.use_bvh, c->shadowq, n_shadow, c->accum, &c->counters->cursor, c->sm_count);
+            c->prof_begin(3);
+            c->k->shadow(c->stream, c->scene.ds, c->scene.use_bvh, c->shadowq, n_shadow, c->accum, c->counters, c->sm_count);
+            c->prof_end();
             c->stats.kernel_launches += 1;
         }
         if (n_next) {
@@ -253,7 +277,8 @@ int rt_context_create(const rt_scene* s, const rt_render_opts* o, rt_context** o
     c->opts = *o;
     auto fail = [&](int rc) { delete c; return rc; };
     if (cudaSetDevice(o->device) != cudaSuccess) { set_error("cudaSetDevice failed"); return fail(RT_ERR_CUDA); }
-    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { set_error("cudaStreamCreate failed"); return fail(RT_ERR_CUDA); }
+    if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess) { set_error("cudaStreamCreate failed"); return fail(RT_ERR_CUDA); }
+    c->stream = c->own_stream;
     cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, o->device);
     c->k = o->fp_mode == RT_FP_FAST ? kernels_fast() : kernels_strict();
     int rc = c->scene.init(s, o->accel, c->stream);
@@ -314,6 +339,7 @@ int rt_context_render(rt_context* c, rt_stats* stats) {
     c->stats.rays_total = c->stats.rays_primary = c->stats.rays_secondary = c->stats.rays_shadow = 0;
     c->stats.kernel_launches = 0;
     c->stats.paths = 0;
+    c->prof_class.clear();
     CUDA_TRY(cudaEventRecord(c->ev0, c->stream));
     CUDA_TRY(cudaMemsetAsync(c->accum, 0, npix * 3 * sizeof(double), c->stream));
     CUDA_TRY(cudaMemsetAsync(c->ids, 0xFF, npix * sizeof(int32_t), c->stream));
@@ -322,7 +348,9 @@ int rt_context_render(rt_context* c, rt_stats* stats) {
     for (uint64_t base = 0; base < c->total_paths; base += batch) {
         const uint32_t n = (uint32_t)std::min<uint64_t>(batch, c->total_paths - base);
         CUDA_TRY(cudaMemsetAsync(&c->counters->level_count[0], 0, sizeof(uint32_t), c->stream));
+        c->prof_begin(0);
         c->k->primary(c->stream, c->scene.ds, fp, c->levels[0], &c->counters->level_count[0], &c->counters->overflow, base, n);
+        c->prof_end();
         c->stats.kernel_launches += 1;
         int rc = ctx_fetch_counters(c);
         if (rc != RT_OK) return rc;
@@ -333,10 +361,25 @@ int rt_context_render(rt_context* c, rt_stats* stats) {
             if (rc != RT_OK) return rc;
         }
     }
+    c->prof_begin(4);
     c->k->resolve(c->stream, c->scene.ds, fp, c->accum, c->framebuffer, c->bytewidth);
+    c->prof_end();
     c->stats.kernel_launches += 1;
+    CUDA_TRY(cudaMemcpyAsync(c->counters_host, c->counters, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
     CUDA_TRY(cudaEventRecord(c->ev1, c->stream));
     CUDA_TRY(cudaEventSynchronize(c->ev1));
+    for (int k = 0; k < 2; k++) {
+        c->stats.bvh_nodes_visited[k] = c->counters_host->bvh_nodes[k];
+        c->stats.bvh_prims_tested[k] = c->counters_host->bvh_prims[k];
+    }
+    for (int k = 0; k < 5; k++) { c->stats.class_ms[k] = 0.0; c->stats.class_launches[k] = 0; }
+    for (size_t i = 0; i < c->prof_class.size(); i++) {
+        float pm = 0;
+        if (cudaEventElapsedTime(&pm, c->prof_events[2 * i], c->prof_events[2 * i + 1]) == cudaSuccess) {
+            c->stats.class_ms[c->prof_class[i]] += pm;
+            c->stats.class_launches[c->prof_class[i]] += 1;
+        }
+    }
     CUDA_TRY(cudaGetLastError());
     float ms = 0;
     CUDA_TRY(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
@@ -372,6 +415,20 @@ int rt_context_untile(rt_context* c, const void* gathered_dev, void* out_dev) {
     launch_untile(c->stream, (const uint32_t*)gathered_dev, (uint32_t*)out_dev, c->fp.height, c->bytewidth / 4, c->fp.band_rows, c->fp.world,
                   c->fp.local_rows);
     CUDA_TRY(cudaGetLastError());
+    return RT_OK;
+}
+
+int rt_context_set_stream(rt_context* c, void* cuda_stream) {
+    if (!c) { set_error("null context"); return RT_ERR_INVALID; }
+    CUDA_TRY(cudaSetDevice(c->device));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
+    return RT_OK;
+}
+
+int rt_context_set_profiling(rt_context* c, int on) {
+    if (!c) { set_error("null context"); return RT_ERR_INVALID; }
+    c->profiling = on != 0;
     return RT_OK;
 }
 
@@ -430,7 +487,7 @@ int rt_trace_rays(const rt_scene* s, const rt_render_opts* o, uint64_t n, const 
         std::vector<void*> allocs;
         RayQueue q{};
         double *d_t = nullptr, *d_n = nullptr;
-        uint32_t* cursor = nullptr;
+        Counters* cursor = nullptr;
         if (rc == RT_OK) rc = alloc_ray_queue(&q, (uint32_t)n, &allocs, false);
         if (rc == RT_OK) rc = dev_alloc(&d_t, n);
         if (rc == RT_OK) rc = dev_alloc(&d_n, 3 * n);
@@ -440,6 +497,7 @@ int rt_trace_rays(const rt_scene* s, const rt_render_opts* o, uint64_t n, const 
             for (uint64_t i = 0; i < n; i++)
                 for (int k = 0; k < 6; k++) soa[(size_t)k * n + i] = origin_dir[6 * i + k];
             cudaError_t e = cudaMemcpyAsync(q.ox, soa.data(), sizeof(double) * 6 * n, cudaMemcpyHostToDevice, st);
+            if (e == cudaSuccess) e = cudaMemsetAsync(cursor, 0, sizeof(Counters), st);
             if (e == cudaSuccess) e = cudaStreamSynchronize(st);
             const KernelTable* k = o->fp_mode == RT_FP_FAST ? kernels_fast() : kernels_strict();
             if (e == cudaSuccess) {

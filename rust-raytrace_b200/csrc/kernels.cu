@@ -218,8 +218,23 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_shadow_scan(const __grid_const
 // ---------------------------------------------------------------------------------------------------------
 // BVH traversal: persistent warps, each pulling 32 rays at a time off a global cursor
 // ---------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_constant__ DeviceScene sc, RayQueue q, uint32_t first, uint32_t n, uint32_t* cursor) {
+__device__ __forceinline__ void flush_traverse_count(const TraverseCount& tc, Counters* counters, int cls) {
+    unsigned long long nodes = tc.nodes, prims = tc.prims;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        nodes += __shfl_xor_sync(0xFFFFFFFFu, nodes, o);
+        prims += __shfl_xor_sync(0xFFFFFFFFu, prims, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&counters->bvh_nodes[cls], nodes);
+        atomicAdd(&counters->bvh_prims[cls], prims);
+    }
+}
+
+__global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_constant__ DeviceScene sc, RayQueue q, uint32_t first, uint32_t n, Counters* counters) {
     const int lane = threadIdx.x & 31;
+    uint32_t* cursor = &counters->cursor;
+    TraverseCount tc; tc.nodes = 0; tc.prims = 0;
     while (true) {
         uint32_t base = 0;
         if (lane == 0) base = atomicAdd(cursor, 32u);
@@ -231,15 +246,18 @@ __global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_consta
             RayQ r = make_rayq(v3(q.ox[i], q.oy[i], q.oz[i]), v3(q.dx[i], q.dy[i], q.dz[i]));
             int32_t id;
             double t;
-            closest_bvh(sc, r, id, t);
+            closest_bvh(sc, r, id, t, tc);
             q.hit_id[i] = id;
             q.hit_t[i] = t;
         }
     }
+    flush_traverse_count(tc, counters, 0);
 }
 
-__global__ void __launch_bounds__(BVH_THREADS) k_shadow_bvh(const __grid_constant__ DeviceScene sc, ShadowQueue sq, uint32_t n, double* accum, uint32_t* cursor) {
+__global__ void __launch_bounds__(BVH_THREADS) k_shadow_bvh(const __grid_constant__ DeviceScene sc, ShadowQueue sq, uint32_t n, double* accum, Counters* counters) {
     const int lane = threadIdx.x & 31;
+    uint32_t* cursor = &counters->cursor;
+    TraverseCount tc; tc.nodes = 0; tc.prims = 0;
     while (true) {
         uint32_t base = 0;
         if (lane == 0) base = atomicAdd(cursor, 32u);
@@ -248,9 +266,10 @@ __global__ void __launch_bounds__(BVH_THREADS) k_shadow_bvh(const __grid_constan
         const uint32_t i = base + lane;
         if (i < n) {
             RayQ r = make_rayq(v3(sq.ox[i], sq.oy[i], sq.oz[i]), v3(sq.dx[i], sq.dy[i], sq.dz[i]));
-            if (!shadow_bvh(sc, r, sq.r2[i])) accum_add(accum, sq.pixel[i], c3(sq.cr[i], sq.cg[i], sq.cb[i]));
+            if (!shadow_bvh(sc, r, sq.r2[i], tc)) accum_add(accum, sq.pixel[i], c3(sq.cr[i], sq.cg[i], sq.cb[i]));
         }
     }
+    flush_traverse_count(tc, counters, 1);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -402,13 +421,13 @@ static void scan_attr_once() {
     }
 }
 
-static void l_closest(cudaStream_t st, const DeviceScene& sc, bool bvh, RayQueue q, uint32_t first, uint32_t n, uint32_t* cursor, int sm_count) {
+static void l_closest(cudaStream_t st, const DeviceScene& sc, bool bvh, RayQueue q, uint32_t first, uint32_t n, Counters* counters, int sm_count) {
     if (!n) return;
     if (bvh) {
-        cudaMemsetAsync(cursor, 0, sizeof(uint32_t), st);
+        cudaMemsetAsync(&counters->cursor, 0, sizeof(uint32_t), st);
         uint32_t want = div_up(n, BVH_THREADS);
         uint32_t grid = (uint32_t)sm_count * 8u;  // 8 resident CTAs of 128 threads per SM
-        k_closest_bvh<<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, q, first, n, cursor);
+        k_closest_bvh<<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, q, first, n, counters);
     } else {
         scan_attr_once();
         k_closest_scan<<<div_up(n, SCAN_THREADS), SCAN_THREADS, sizeof(ScanSmem), st>>>(sc, q, first, n);
@@ -421,13 +440,13 @@ static void l_shade(cudaStream_t st, const DeviceScene& sc, const FrameParams& f
     k_shade<<<div_up(n, SHADE_THREADS), SHADE_THREADS, 0, st>>>(sc, fp, in, first, n, out, out_count, sq, sq_count, overflow, accum, ids);
 }
 
-static void l_shadow(cudaStream_t st, const DeviceScene& sc, bool bvh, ShadowQueue sq, uint32_t n, double* accum, uint32_t* cursor, int sm_count) {
+static void l_shadow(cudaStream_t st, const DeviceScene& sc, bool bvh, ShadowQueue sq, uint32_t n, double* accum, Counters* counters, int sm_count) {
     if (!n) return;
     if (bvh) {
-        cudaMemsetAsync(cursor, 0, sizeof(uint32_t), st);
+        cudaMemsetAsync(&counters->cursor, 0, sizeof(uint32_t), st);
         uint32_t want = div_up(n, BVH_THREADS);
         uint32_t grid = (uint32_t)sm_count * 8u;
-        k_shadow_bvh<<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, cursor);
+        k_shadow_bvh<<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters);
     } else {
         scan_attr_once();
         k_shadow_scan<<<div_up(n, SCAN_THREADS), SCAN_THREADS, sizeof(ScanSmem), st>>>(sc, sq, n, accum);

@@ -13,6 +13,8 @@ struct Counters {
     uint32_t shadow_count;  // shadow queue length
     uint32_t cursor;        // persistent-thread work cursor (reset before each persistent launch)
     uint32_t _pad;
+    unsigned long long bvh_nodes[2];  // 64-byte BVH nodes fetched: [0] closest-hit kernel, [1] shadow kernel (whole render)
+    unsigned long long bvh_prims[2];  // exact sphere tests done at BVH leaves
     uint32_t level_count[64];  // ray-queue length per wavefront level
 };
 
@@ -21,12 +23,12 @@ struct KernelTable {
     void (*primary)(cudaStream_t, const DeviceScene&, const FrameParams&, RayQueue q, uint32_t* q_count, uint32_t* overflow, uint64_t path_base,
                     uint32_t n_paths);
     // Scene::intersect for rays [first, first+n) of q; fills hit_id / hit_t
-    void (*closest)(cudaStream_t, const DeviceScene&, bool bvh, RayQueue q, uint32_t first, uint32_t n, uint32_t* cursor, int sm_count);
+    void (*closest)(cudaStream_t, const DeviceScene&, bool bvh, RayQueue q, uint32_t first, uint32_t n, Counters* counters, int sm_count);
     // material evaluation: pixel accumulation, shadow-ray and child-ray emission with warp-aggregated appends
     void (*shade)(cudaStream_t, const DeviceScene&, const FrameParams&, RayQueue in, uint32_t first, uint32_t n, RayQueue out, uint32_t* out_count,
                   ShadowQueue sq, uint32_t* sq_count, uint32_t* overflow, double* accum, int32_t* ids);
     // shadow queries; unoccluded rays add their pending contribution to the pixel
-    void (*shadow)(cudaStream_t, const DeviceScene&, bool bvh, ShadowQueue sq, uint32_t n, double* accum, uint32_t* cursor, int sm_count);
+    void (*shadow)(cudaStream_t, const DeviceScene&, bool bvh, ShadowQueue sq, uint32_t n, double* accum, Counters* counters, int sm_count);
     // average, quantise (threshold table) and pack BGR rows with padding; 128-bit stores
     void (*resolve)(cudaStream_t, const DeviceScene&, const FrameParams&, const double* accum, uint8_t* out, uint32_t bytewidth);
     // test hooks

@@ -273,8 +273,12 @@ RT_HD float f64_to_f32_down(double x) {
 
 // SHADOW = false: closest hit among spheres merged into `best` (which already holds the plane result).
 // SHADOW = true : sets s.any as soon as one sphere hit counts for the range.
+struct TraverseCount {
+    uint32_t nodes, prims;  // 64-byte nodes fetched, exact sphere tests done
+};
+
 template <bool SHADOW>
-RT_HD void bvh_traverse(const DeviceScene& sc, const RayQ& r, Closest& best, double range2, Shadow& s) {
+RT_HD void bvh_traverse(const DeviceScene& sc, const RayQ& r, Closest& best, double range2, Shadow& s, TraverseCount& tc) {
     if (sc.n_spheres == 0) return;
     BoxRay br = make_boxray(sc, r.o, r.d);
     if (!br.finite) return;
@@ -287,12 +291,14 @@ RT_HD void bvh_traverse(const DeviceScene& sc, const RayQ& r, Closest& best, dou
     else bound = best.t * RT_BVH_TSLACK;  // NaN best never reaches here (caller skips), inf stays inf
     while (true) {
         BvhNode n = load_node(sc.bvh_nodes + node);
+        tc.nodes++;
         double t0 = box_entry(br, n.lo0, n.hi0, bound);
         double t1 = box_entry(br, n.lo1, n.hi1, bound);
         if (t0 >= 0.0 && n.c0 < 0) {
             int32_t k = ~n.c0;
             const SphereRec* sp_ = sc.bvh_sph + k;
             double t;
+            tc.prims++;
             if (sphere_hit(r, RT_LDG(&sp_->cx), RT_LDG(&sp_->cy), RT_LDG(&sp_->cz), RT_LDG(&sp_->r2), t)) {
                 if (SHADOW) {
                     if (shadow_hit_counts(t, range2)) { s.any = true; return; }
@@ -308,6 +314,7 @@ RT_HD void bvh_traverse(const DeviceScene& sc, const RayQ& r, Closest& best, dou
                 int32_t k = ~n.c1;
                 const SphereRec* sp_ = sc.bvh_sph + k;
                 double t;
+                tc.prims++;
                 if (sphere_hit(r, RT_LDG(&sp_->cx), RT_LDG(&sp_->cy), RT_LDG(&sp_->cz), RT_LDG(&sp_->r2), t)) {
                     if (SHADOW) {
                         if (shadow_hit_counts(t, range2)) { s.any = true; return; }
@@ -341,22 +348,22 @@ RT_HD void bvh_traverse(const DeviceScene& sc, const RayQ& r, Closest& best, dou
 }
 
 // Scene::intersect through the BVH
-RT_HD void closest_bvh(const DeviceScene& sc, const RayQ& r, int32_t& id, double& t) {
+RT_HD void closest_bvh(const DeviceScene& sc, const RayQ& r, int32_t& id, double& t, TraverseCount& tc) {
     Closest best = closest_none();
     planes_closest(sc, r, best);
     if (!best.nan) {
         Shadow dummy; dummy.nan = false; dummy.any = false;
-        bvh_traverse<false>(sc, r, best, -1.0, dummy);
+        bvh_traverse<false>(sc, r, best, -1.0, dummy, tc);
     }
     id = closest_id(best);
     t = best.t;
 }
-RT_HD bool shadow_bvh(const DeviceScene& sc, const RayQ& r, double range2) {
+RT_HD bool shadow_bvh(const DeviceScene& sc, const RayQ& r, double range2, TraverseCount& tc) {
     Shadow s; s.nan = false; s.any = false;
     planes_shadow(sc, r, range2, s);
     if (!s.nan && !s.any) {
         Closest dummy = closest_none();
-        bvh_traverse<true>(sc, r, dummy, range2, s);
+        bvh_traverse<true>(sc, r, dummy, range2, s, tc);
     }
     return shadow_result(s, range2);
 }

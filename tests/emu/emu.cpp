@@ -125,6 +125,8 @@ int make_scene(const rt_scene* s, int accel, EmuScene* e) {
     return RT_OK;
 }
 
+TraverseCount g_tc{0, 0};
+
 struct QRay {
     V3 o, d;
     C3 T;
@@ -184,7 +186,7 @@ RT_API int emu_render_shard(const rt_scene* s, const rt_render_opts* o, uint8_t*
             for (const QRay& r : cur) {
                 RayQ rq = make_rayq(r.o, r.d);
                 int32_t id; double t;
-                if (e.use_bvh) closest_bvh(e.ds, rq, id, t); else closest_linear(e.ds, rq, id, t);
+                if (e.use_bvh) closest_bvh(e.ds, rq, id, t, g_tc); else closest_linear(e.ds, rq, id, t);
                 if (r.meta & META_RECORD_ID) idbuf[r.pixel] = id;
                 ShadeCtx sc;
                 C3 a = shade_begin(e.ds, fp, r.o, r.d, r.T, r.sig, r.key, r.meta & META_DEPTH_MASK, id, t, sc);
@@ -206,7 +208,7 @@ RT_API int emu_render_shard(const rt_scene* s, const rt_render_opts* o, uint8_t*
             st.rays_shadow += shadows.size();
             for (const SRay& sr : shadows) {
                 RayQ rq = make_rayq(sr.r.o, sr.r.d);
-                const bool occ = e.use_bvh ? shadow_bvh(e.ds, rq, sr.r.range2) : shadow_linear(e.ds, rq, sr.r.range2);
+                const bool occ = e.use_bvh ? shadow_bvh(e.ds, rq, sr.r.range2, g_tc) : shadow_linear(e.ds, rq, sr.r.range2);
                 if (!occ) add(sr.pixel, sr.r.c);
             }
             cur.swap(next);
@@ -239,7 +241,7 @@ RT_API int emu_trace_rays(const rt_scene* s, const rt_render_opts* o, uint64_t n
         V3 org = v3(od + 6 * i), dir = v3(od + 6 * i + 3);
         RayQ rq = make_rayq(org, dir);
         int32_t id; double t;
-        if (e.use_bvh) closest_bvh(e.ds, rq, id, t); else closest_linear(e.ds, rq, id, t);
+        if (e.use_bvh) closest_bvh(e.ds, rq, id, t, g_tc); else closest_linear(e.ds, rq, id, t);
         ids[i] = id;
         if (t_out) t_out[i] = id >= 0 ? t : (double)INFINITY;
         if (normal) {
@@ -257,7 +259,7 @@ RT_API int emu_shadow_rays(const rt_scene* s, const rt_render_opts* o, uint64_t 
     if (rc != RT_OK) return rc;
     for (uint64_t i = 0; i < n; i++) {
         RayQ rq = make_rayq(v3(od + 6 * i), v3(od + 6 * i + 3));
-        occluded[i] = (e.use_bvh ? shadow_bvh(e.ds, rq, r2[i]) : shadow_linear(e.ds, rq, r2[i])) ? 1 : 0;
+        occluded[i] = (e.use_bvh ? shadow_bvh(e.ds, rq, r2[i], g_tc) : shadow_linear(e.ds, rq, r2[i])) ? 1 : 0;
     }
     return RT_OK;
 }
