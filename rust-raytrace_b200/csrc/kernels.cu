@@ -231,42 +231,128 @@ __device__ __forceinline__ void flush_traverse_count(const TraverseCount& tc, Co
     }
 }
 
-__global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_constant__ DeviceScene sc, RayQueue q, uint32_t first, uint32_t n, Counters* counters) {
+// Warp-aggregated refill: every idle lane takes the next ray index off the cursor (one atomicAdd per warp).
+// Must be called by all 32 lanes.  Returns the ray index for lanes that were idle (may be >= n: nothing left).
+__device__ __forceinline__ uint32_t warp_fetch(unsigned idle_mask, uint32_t* cursor) {
     const int lane = threadIdx.x & 31;
+    const int leader = __ffs(idle_mask) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(cursor, (uint32_t)__popc(idle_mask));
+    base = __shfl_sync(0xFFFFFFFFu, base, leader);
+    return base + (uint32_t)__popc(idle_mask & ((1u << lane) - 1u));
+}
+
+constexpr int FETCH_MIN_IDLE = 8;  // refill when at least this many lanes of the warp have finished their ray
+
+// Persistent "while-while" traversal.  Each lane owns one ray at a time; the warp alternates between
+//   phase 1  every lane walks internal nodes (f32 box filter) until its next job is a leaf test or it is done,
+//   phase 2  every lane with a pending leaf runs the exact f64 sphere test,
+// and lanes whose ray has finished are refilled from the global cursor instead of idling until the slowest lane of
+// a fixed 32-ray batch is done.
+__global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_constant__ DeviceScene sc, RayQueue q, uint32_t first, uint32_t n, Counters* counters) {
     uint32_t* cursor = &counters->cursor;
     TraverseCount tc; tc.nodes = 0; tc.prims = 0;
+    TravStack st; st.sp = 0;
+    RayQ r; BoxRay32 br; Closest best;
+    r = make_rayq(v3(0, 0, 0), v3(0, 0, 0)); best = closest_none();
+    br.ix = br.iy = br.iz = br.px = br.py = br.pz = br.mx = br.my = br.mz = 0.0f; br.finite = false;
+    int32_t cur = TRAV_EMPTY;
+    float bound = 0.0f;
+    uint32_t ray = 0;
+    bool active = false, exhausted = false;
     while (true) {
-        uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(cursor, 32u);
-        base = __shfl_sync(0xFFFFFFFFu, base, 0);
-        if (base >= n) break;
-        const uint32_t li = base + lane;
-        if (li < n) {
-            const uint32_t i = first + li;
-            RayQ r = make_rayq(v3(q.ox[i], q.oy[i], q.oz[i]), v3(q.dx[i], q.dy[i], q.dz[i]));
-            int32_t id;
-            double t;
-            closest_bvh(sc, r, id, t, tc);
-            q.hit_id[i] = id;
-            q.hit_t[i] = t;
+        const unsigned idle = __ballot_sync(0xFFFFFFFFu, !active);
+        if (idle != 0u && !exhausted && (__popc(idle) >= FETCH_MIN_IDLE || idle == 0xFFFFFFFFu)) {
+            const uint32_t li = warp_fetch(idle, cursor);
+            if (!active) {
+                if (li < n) {
+                    ray = first + li;
+                    r = make_rayq(v3(q.ox[ray], q.oy[ray], q.oz[ray]), v3(q.dx[ray], q.dy[ray], q.dz[ray]));
+                    best = closest_none();
+                    planes_closest(sc, r, best);
+                    st.sp = 0;
+                    cur = TRAV_EMPTY;
+                    if (!best.nan && sc.n_spheres > 0) {
+                        br = make_boxray32(sc, r.o, r.d);
+                        if (br.finite) { cur = 0; bound = closest_bound32(best); }
+                    }
+                    active = true;
+                }
+            }
+            // the cursor only grows: once any lane is handed an index past the end, the queue is drained
+            exhausted = __any_sync(0xFFFFFFFFu, li >= n && (idle >> (threadIdx.x & 31) & 1u));
+        }
+        if (__all_sync(0xFFFFFFFFu, !active)) {
+            if (exhausted) break;
+            continue;
+        }
+        if (active) cur = trav_descend(sc, br, cur, bound, st, tc);
+        __syncwarp();
+        if (active) {
+            if (cur == TRAV_EMPTY) {
+                q.hit_id[ray] = closest_id(best);
+                q.hit_t[ray] = best.t;
+                active = false;
+            } else {
+                leaf_closest(sc, r, ~cur, best, tc);
+                bound = closest_bound32(best);
+                cur = trav_pop(st, bound);
+            }
         }
     }
     flush_traverse_count(tc, counters, 0);
 }
 
 __global__ void __launch_bounds__(BVH_THREADS) k_shadow_bvh(const __grid_constant__ DeviceScene sc, ShadowQueue sq, uint32_t n, double* accum, Counters* counters) {
-    const int lane = threadIdx.x & 31;
     uint32_t* cursor = &counters->cursor;
     TraverseCount tc; tc.nodes = 0; tc.prims = 0;
+    TravStack st; st.sp = 0;
+    RayQ r; BoxRay32 br;
+    r = make_rayq(v3(0, 0, 0), v3(0, 0, 0));
+    br.ix = br.iy = br.iz = br.px = br.py = br.pz = br.mx = br.my = br.mz = 0.0f; br.finite = false;
+    int32_t cur = TRAV_EMPTY;
+    float bound = 0.0f;
+    double range2 = -1.0;
+    uint32_t ray = 0;
+    bool active = false, exhausted = false, occluded = false;
     while (true) {
-        uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(cursor, 32u);
-        base = __shfl_sync(0xFFFFFFFFu, base, 0);
-        if (base >= n) break;
-        const uint32_t i = base + lane;
-        if (i < n) {
-            RayQ r = make_rayq(v3(sq.ox[i], sq.oy[i], sq.oz[i]), v3(sq.dx[i], sq.dy[i], sq.dz[i]));
-            if (!shadow_bvh(sc, r, sq.r2[i], tc)) accum_add(accum, sq.pixel[i], c3(sq.cr[i], sq.cg[i], sq.cb[i]));
+        const unsigned idle = __ballot_sync(0xFFFFFFFFu, !active);
+        if (idle != 0u && !exhausted && (__popc(idle) >= FETCH_MIN_IDLE || idle == 0xFFFFFFFFu)) {
+            const uint32_t li = warp_fetch(idle, cursor);
+            if (!active) {
+                if (li < n) {
+                    ray = li;
+                    r = make_rayq(v3(sq.ox[ray], sq.oy[ray], sq.oz[ray]), v3(sq.dx[ray], sq.dy[ray], sq.dz[ray]));
+                    range2 = sq.r2[ray];
+                    Shadow s; s.nan = false; s.any = false;
+                    planes_shadow(sc, r, range2, s);
+                    st.sp = 0;
+                    cur = TRAV_EMPTY;
+                    occluded = shadow_result(s, range2);
+                    if (!s.nan && !s.any && sc.n_spheres > 0) {
+                        br = make_boxray32(sc, r.o, r.d);
+                        if (br.finite) { cur = 0; bound = shadow_bound32(range2); }
+                    }
+                    active = true;
+                }
+            }
+            exhausted = __any_sync(0xFFFFFFFFu, li >= n && (idle >> (threadIdx.x & 31) & 1u));
+        }
+        if (__all_sync(0xFFFFFFFFu, !active)) {
+            if (exhausted) break;
+            continue;
+        }
+        if (active) cur = trav_descend(sc, br, cur, bound, st, tc);
+        __syncwarp();
+        if (active) {
+            if (cur != TRAV_EMPTY) {
+                if (leaf_shadow(sc, r, ~cur, range2, tc)) { occluded = true; cur = TRAV_EMPTY; }
+                else cur = trav_pop(st, bound);
+            }
+            if (cur == TRAV_EMPTY) {
+                if (!occluded) accum_add(accum, sq.pixel[ray], c3(sq.cr[ray], sq.cg[ray], sq.cb[ray]));
+                active = false;
+            }
         }
     }
     flush_traverse_count(tc, counters, 1);

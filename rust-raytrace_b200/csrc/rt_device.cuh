@@ -209,46 +209,79 @@ RT_HD void planes_shadow(const DeviceScene& sc, const RayQ& r, double range2, Sh
 RT_HD bool shadow_result(const Shadow& s, double range2) { return s.nan ? (range2 < 0.0) : s.any; }
 
 // ---------------------------------------------------------------------------------------------------------
-// BVH traversal.  The box test is a conservative filter (f32 boxes rounded outward at build time, widened per
-// ray by `pad`); the leaf test is the same f64 expression as the linear scan, so the result is the scan's.
+// BVH traversal.
+//
+// The box test is only a conservative FILTER: it may pass a box the ray misses, never reject a box whose sphere
+// the exact test would hit.  It runs in f32 (native FFMA/FMNMX: a third of the instructions of an f64 slab test,
+// whose min/max are emulated) on the f32 boxes that the build rounded outward.  The leaf test is the same f64
+// expression as the linear scan (sphere_hit), so the hit, its t and the tie-break are the scan's, bit for bit.
+//
+// Conservativeness of the f32 filter (DESIGN.md "BVH == linear scan"):
+//   additive errors  -- rounding the ray origin to f32 (<= 2^-24 |o|), the rounding of (o +- pad)*inv, and the
+//                       rounding error of the exact test's discriminant (which makes the scan "hit" spheres inflated
+//                       by up to min(E/2r_min, sqrt(E)), E = 64 eps S^2) -- are covered by widening every box by `pad`;
+//   relative errors  -- inv = fl32(1/d) and the FFMA rounding scale each slab distance by (1 +- 2^-23) -- are covered
+//                       by shrinking the entry distance and growing the exit distance by 2^-21.
 // ---------------------------------------------------------------------------------------------------------
 constexpr int BVH_STACK = 96;          // >= 63 Morton bits + 32 tie-break bits
-#define RT_BVH_TSLACK 1.000000000001   // relative slack on t comparisons of the filter
+#define RT_BVH_TSLACK 1.000000000001   // relative slack when a t of the exact test bounds the filter
+constexpr int32_t TRAV_EMPTY = (int32_t)0x80000000;  // "no node left"; never a valid ~leaf (n_spheres < 2^31 - 16)
 
-struct BoxRay {
-    double ix, iy, iz;     // clamped reciprocal direction
-    double px, py, pz;     // (o + pad) * inv
-    double mx, my, mz;     // (o - pad) * inv
+struct TraverseCount {
+    uint32_t nodes, prims;  // 64-byte nodes fetched, exact sphere tests done
+};
+
+struct BoxRay32 {
+    float ix, iy, iz;  // clamped reciprocal direction
+    float px, py, pz;  // (o + pad) * inv
+    float mx, my, mz;  // (o - pad) * inv
     bool finite;
 };
 
-RT_HD double safe_inv(double d) {
-    return fabs(d) < 1e-150 ? copysign(1e150, d) : 1.0 / d;
+RT_HD float safe_inv32(double d) {
+    if (fabs(d) < 1e-30) return (float)copysign(1e30, d);
+    return (float)(1.0 / d);
 }
 
-RT_HD BoxRay make_boxray(const DeviceScene& sc, V3 o, V3 d) {
-    BoxRay b;
+#if defined(__CUDA_ARCH__)
+RT_HD float f64_to_f32_down(double x) { return __double2float_rd(x); }
+RT_HD float f64_to_f32_up(double x) { return __double2float_ru(x); }
+#else
+RT_HD float f64_to_f32_down(double x) {
+    float f = (float)x;
+    return ((double)f > x) ? nextafterf(f, -INFINITY) : f;
+}
+RT_HD float f64_to_f32_up(double x) {
+    float f = (float)x;
+    return ((double)f < x) ? nextafterf(f, INFINITY) : f;
+}
+#endif
+
+RT_HD BoxRay32 make_boxray32(const DeviceScene& sc, V3 o, V3 d) {
+    BoxRay32 b;
     double s = fmax(fmax(fabs(o.x), fabs(o.y)), fabs(o.z));
     double dm = fmax(fmax(fabs(d.x), fabs(d.y)), fabs(d.z));
     // any non-finite origin/direction makes every sphere discriminant NaN (=> miss); skip the tree
-    b.finite = (s < 1e150) && (dm < 1e150) && (o.x == o.x) && (o.y == o.y) && (o.z == o.z) && (d.x == d.x) && (d.y == d.y) && (d.z == d.z);
+    b.finite = (s < 1e30) && (dm < 1e30) && (o.x == o.x) && (o.y == o.y) && (o.z == o.z) && (d.x == d.x) && (d.y == d.y) && (d.z == d.z);
     double S = s + sc.bvh_cmax;
     double E = 64.0 * 2.220446049250313e-16 * S * S;  // bound on the rounding error of the discriminant, in r^2 units
-    double pad = S * 0x1.0p-40 + fmin(E / (2.0 * sc.bvh_rmin), sqrt(E));
-    b.ix = safe_inv(d.x); b.iy = safe_inv(d.y); b.iz = safe_inv(d.z);
-    b.px = (o.x + pad) * b.ix; b.py = (o.y + pad) * b.iy; b.pz = (o.z + pad) * b.iz;
-    b.mx = (o.x - pad) * b.ix; b.my = (o.y - pad) * b.iy; b.mz = (o.z - pad) * b.iz;
+    double pad = S * 0x1.0p-20 + fmin(E / (2.0 * sc.bvh_rmin), sqrt(E));
+    b.ix = safe_inv32(d.x); b.iy = safe_inv32(d.y); b.iz = safe_inv32(d.z);
+    b.px = (float)((o.x + pad) * (double)b.ix); b.py = (float)((o.y + pad) * (double)b.iy); b.pz = (float)((o.z + pad) * (double)b.iz);
+    b.mx = (float)((o.x - pad) * (double)b.ix); b.my = (float)((o.y - pad) * (double)b.iy); b.mz = (float)((o.z - pad) * (double)b.iz);
     return b;
 }
 
-// returns entry distance (clamped at 0) if the padded box is hit within [0, bound], else -1
-RT_HD double box_entry(const BoxRay& b, const float* lo, const float* hi, double bound) {
-    double ax = fma((double)lo[0], b.ix, -b.px), bx = fma((double)hi[0], b.ix, -b.mx);
-    double ay = fma((double)lo[1], b.iy, -b.py), by = fma((double)hi[1], b.iy, -b.my);
-    double az = fma((double)lo[2], b.iz, -b.pz), bz = fma((double)hi[2], b.iz, -b.mz);
-    double tn = fmax(fmax(fmin(ax, bx), fmin(ay, by)), fmax(fmin(az, bz), 0.0));
-    double tf = fmin(fmin(fmax(ax, bx), fmax(ay, by)), fmax(az, bz));
-    return (tn <= tf * RT_BVH_TSLACK && tn <= bound) ? tn : -1.0;
+// conservative entry distance (>= 0) of the padded box if it can be hit within [0, bound], else -1
+RT_HD float box_entry32(const BoxRay32& b, const float* lo, const float* hi, float bound) {
+    float ax = fmaf(lo[0], b.ix, -b.px), bx = fmaf(hi[0], b.ix, -b.mx);
+    float ay = fmaf(lo[1], b.iy, -b.py), by = fmaf(hi[1], b.iy, -b.my);
+    float az = fmaf(lo[2], b.iz, -b.pz), bz = fmaf(hi[2], b.iz, -b.mz);
+    float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
+    float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
+    tn *= (1.0f - 0x1.0p-21f);
+    tf *= (1.0f + 0x1.0p-21f);
+    return (tn <= tf && tn <= bound) ? tn : -1.0f;
 }
 
 #if defined(__CUDA_ARCH__)
@@ -262,98 +295,86 @@ RT_HD BvhNode load_node(const BvhNode* p) {
     n.c0 = __float_as_int(d.x); n.c1 = __float_as_int(d.y);
     return n;
 }
-RT_HD float f64_to_f32_down(double x) { return __double2float_rd(x); }
 #else
 RT_HD BvhNode load_node(const BvhNode* p) { return *p; }
-RT_HD float f64_to_f32_down(double x) {
-    float f = (float)x;
-    return ((double)f > x) ? nextafterf(f, -INFINITY) : f;
-}
 #endif
 
-// SHADOW = false: closest hit among spheres merged into `best` (which already holds the plane result).
-// SHADOW = true : sets s.any as soon as one sphere hit counts for the range.
-struct TraverseCount {
-    uint32_t nodes, prims;  // 64-byte nodes fetched, exact sphere tests done
+// traversal stack: internal nodes (>= 0) and leaves (~slot < 0) alike, each with its conservative entry distance
+struct TravStack {
+    int32_t node[BVH_STACK];
+    float t[BVH_STACK];
+    int sp;
 };
 
-template <bool SHADOW>
-RT_HD void bvh_traverse(const DeviceScene& sc, const RayQ& r, Closest& best, double range2, Shadow& s, TraverseCount& tc) {
-    if (sc.n_spheres == 0) return;
-    BoxRay br = make_boxray(sc, r.o, r.d);
-    if (!br.finite) return;
-    int32_t stack_node[BVH_STACK];
-    float stack_t[BVH_STACK];
-    int sp = 0;
-    int32_t node = 0;
-    double bound;
-    if (SHADOW) bound = range2 < 0.0 ? (double)INFINITY : sqrt(range2) * RT_BVH_TSLACK;
-    else bound = best.t * RT_BVH_TSLACK;  // NaN best never reaches here (caller skips), inf stays inf
-    while (true) {
-        BvhNode n = load_node(sc.bvh_nodes + node);
-        tc.nodes++;
-        double t0 = box_entry(br, n.lo0, n.hi0, bound);
-        double t1 = box_entry(br, n.lo1, n.hi1, bound);
-        if (t0 >= 0.0 && n.c0 < 0) {
-            int32_t k = ~n.c0;
-            const SphereRec* sp_ = sc.bvh_sph + k;
-            double t;
-            tc.prims++;
-            if (sphere_hit(r, RT_LDG(&sp_->cx), RT_LDG(&sp_->cy), RT_LDG(&sp_->cz), RT_LDG(&sp_->r2), t)) {
-                if (SHADOW) {
-                    if (shadow_hit_counts(t, range2)) { s.any = true; return; }
-                } else {
-                    closest_update(best, t, RT_LDG(sc.bvh_obj + k));
-                    bound = best.t * RT_BVH_TSLACK;
-                }
-            }
-            t0 = -1.0;
-        }
-        if (t1 >= 0.0 && n.c1 < 0) {
-            if (t1 <= bound) {
-                int32_t k = ~n.c1;
-                const SphereRec* sp_ = sc.bvh_sph + k;
-                double t;
-                tc.prims++;
-                if (sphere_hit(r, RT_LDG(&sp_->cx), RT_LDG(&sp_->cy), RT_LDG(&sp_->cz), RT_LDG(&sp_->r2), t)) {
-                    if (SHADOW) {
-                        if (shadow_hit_counts(t, range2)) { s.any = true; return; }
-                    } else {
-                        closest_update(best, t, RT_LDG(sc.bvh_obj + k));
-                        bound = best.t * RT_BVH_TSLACK;
-                    }
-                }
-            }
-            t1 = -1.0;
-        }
-        if (t0 >= 0.0 && t0 > bound) t0 = -1.0;
-        if (t1 >= 0.0 && t1 > bound) t1 = -1.0;
-        if (t0 >= 0.0 && t1 >= 0.0) {
-            int32_t nearc = n.c0, farc = n.c1;
-            double tfar = t1;
-            if (t1 < t0) { nearc = n.c1; farc = n.c0; tfar = t0; }
-            if (sp < BVH_STACK) { stack_node[sp] = farc; stack_t[sp] = f64_to_f32_down(tfar); sp++; }
-            node = nearc;
-            continue;
-        }
-        if (t0 >= 0.0) { node = n.c0; continue; }
-        if (t1 >= 0.0) { node = n.c1; continue; }
-        bool found = false;
-        while (sp > 0) {
-            --sp;
-            if ((double)stack_t[sp] <= bound) { node = stack_node[sp]; found = true; break; }
-        }
-        if (!found) return;
+RT_HD int32_t trav_pop(TravStack& st, float bound) {
+    while (st.sp > 0) {
+        --st.sp;
+        if (st.t[st.sp] <= bound) return st.node[st.sp];
     }
+    return TRAV_EMPTY;
 }
 
-// Scene::intersect through the BVH
+// Walk internal nodes from `cur` (near child first, far child pushed) until the next thing to do is a leaf test
+// (returns ~slot < 0) or nothing is left (TRAV_EMPTY).  Leaves are NOT tested here: postponing them keeps the lanes
+// of a warp in the same code (box tests together, sphere tests together).
+RT_HD int32_t trav_descend(const DeviceScene& sc, const BoxRay32& br, int32_t cur, float bound, TravStack& st, TraverseCount& tc) {
+    while (cur >= 0) {
+        const BvhNode n = load_node(sc.bvh_nodes + cur);
+        tc.nodes++;
+        const float t0 = box_entry32(br, n.lo0, n.hi0, bound);
+        const float t1 = box_entry32(br, n.lo1, n.hi1, bound);
+        if (t0 >= 0.0f && t1 >= 0.0f) {
+            const bool swap = t1 < t0;
+            const int32_t farc = swap ? n.c0 : n.c1;
+            if (st.sp < BVH_STACK) { st.node[st.sp] = farc; st.t[st.sp] = swap ? t0 : t1; st.sp++; }
+            cur = swap ? n.c1 : n.c0;
+        } else if (t0 >= 0.0f) {
+            cur = n.c0;
+        } else if (t1 >= 0.0f) {
+            cur = n.c1;
+        } else {
+            cur = trav_pop(st, bound);
+        }
+    }
+    return cur;
+}
+
+RT_HD float closest_bound32(const Closest& best) { return f64_to_f32_up(best.t * RT_BVH_TSLACK); }
+RT_HD float shadow_bound32(double range2) { return range2 < 0.0 ? INFINITY : f64_to_f32_up(sqrt(range2) * RT_BVH_TSLACK); }
+
+// exact test of Morton-slot k against the running closest hit; returns the new filter bound
+RT_HD void leaf_closest(const DeviceScene& sc, const RayQ& r, int32_t k, Closest& best, TraverseCount& tc) {
+    const SphereRec* s = sc.bvh_sph + k;
+    double t;
+    tc.prims++;
+    if (sphere_hit(r, RT_LDG(&s->cx), RT_LDG(&s->cy), RT_LDG(&s->cz), RT_LDG(&s->r2), t)) closest_update(best, t, RT_LDG(sc.bvh_obj + k));
+}
+RT_HD bool leaf_shadow(const DeviceScene& sc, const RayQ& r, int32_t k, double range2, TraverseCount& tc) {
+    const SphereRec* s = sc.bvh_sph + k;
+    double t;
+    tc.prims++;
+    return sphere_hit(r, RT_LDG(&s->cx), RT_LDG(&s->cy), RT_LDG(&s->cz), RT_LDG(&s->r2), t) && shadow_hit_counts(t, range2);
+}
+
+// Scene::intersect through the BVH (one ray, start to finish; the kernels run the same pieces lane by lane)
 RT_HD void closest_bvh(const DeviceScene& sc, const RayQ& r, int32_t& id, double& t, TraverseCount& tc) {
     Closest best = closest_none();
     planes_closest(sc, r, best);
-    if (!best.nan) {
-        Shadow dummy; dummy.nan = false; dummy.any = false;
-        bvh_traverse<false>(sc, r, best, -1.0, dummy, tc);
+    if (!best.nan && sc.n_spheres > 0) {
+        const BoxRay32 br = make_boxray32(sc, r.o, r.d);
+        if (br.finite) {
+            TravStack st;
+            st.sp = 0;
+            int32_t cur = 0;
+            float bound = closest_bound32(best);
+            while (true) {
+                cur = trav_descend(sc, br, cur, bound, st, tc);
+                if (cur == TRAV_EMPTY) break;
+                leaf_closest(sc, r, ~cur, best, tc);
+                bound = closest_bound32(best);
+                cur = trav_pop(st, bound);
+            }
+        }
     }
     id = closest_id(best);
     t = best.t;
@@ -361,9 +382,20 @@ RT_HD void closest_bvh(const DeviceScene& sc, const RayQ& r, int32_t& id, double
 RT_HD bool shadow_bvh(const DeviceScene& sc, const RayQ& r, double range2, TraverseCount& tc) {
     Shadow s; s.nan = false; s.any = false;
     planes_shadow(sc, r, range2, s);
-    if (!s.nan && !s.any) {
-        Closest dummy = closest_none();
-        bvh_traverse<true>(sc, r, dummy, range2, s, tc);
+    if (!s.nan && !s.any && sc.n_spheres > 0) {
+        const BoxRay32 br = make_boxray32(sc, r.o, r.d);
+        if (br.finite) {
+            TravStack st;
+            st.sp = 0;
+            int32_t cur = 0;
+            const float bound = shadow_bound32(range2);
+            while (true) {
+                cur = trav_descend(sc, br, cur, bound, st, tc);
+                if (cur == TRAV_EMPTY) break;
+                if (leaf_shadow(sc, r, ~cur, range2, tc)) { s.any = true; break; }
+                cur = trav_pop(st, bound);
+            }
+        }
     }
     return shadow_result(s, range2);
 }
