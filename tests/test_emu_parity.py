@@ -1,0 +1,161 @@
+"""CPU-side parity of the product's per-ray arithmetic (rust-raytrace_b200/csrc/rt_device.cuh) against the oracle.
+
+tests/emu compiles the product header with g++ and drives it with a serial loop shaped like the GPU wavefront
+(tests/emu/README.md).  It is a test of the header, not a fallback: what is parallel (kernels, atomics, TMA staging,
+the device BVH build) is only covered by `pytest -m gpu`.
+
+Bars as on the GPU: primary hit ids bit-exact, bytes within +-1 LSB and >= 99.9 % identical, ray counts equal; in
+strict arithmetic the intersection results (t, normal) are bit-identical.
+"""
+import numpy as np
+import pytest
+
+import emu
+from test_gpu_parity import REF_TEXT_SCENE
+
+
+def check(got, ref, what):
+    assert np.array_equal(got["ids"], ref["ids"]), "%s: primary ids differ in %d pixels" % (what, int((got["ids"] != ref["ids"]).sum()))
+    diff = np.abs(got["bgr"].astype(np.int16) - ref["bgr"].astype(np.int16))
+    assert diff.max() <= 1, "%s: %d LSB" % (what, int(diff.max()))
+    same = float((diff == 0).mean())
+    assert same >= 0.999, "%s: %.5f identical" % (what, same)
+    assert got["stats"]["rays_total"] == ref["stats"]["rays"], (what, got["stats"]["rays_total"], ref["stats"]["rays"])
+    assert got["stats"]["rays_shadow"] == ref["stats"]["shadow_rays"]
+    return same
+
+
+def _rays(rng, n, extent, ymax):
+    o = np.stack([rng.uniform(-extent, extent, n), rng.uniform(0.1, ymax, n), rng.uniform(-extent, extent, n)], axis=1)
+    d = rng.normal(size=(n, 3))
+    d[: n // 2] /= np.linalg.norm(d[: n // 2], axis=1, keepdims=True)
+    return np.concatenate([o, d], axis=1)
+
+
+def test_quantiser(orc):
+    v, a = orc.srgb_tables()
+    vals = np.concatenate([a, np.nextafter(a, -np.inf), np.nextafter(a, np.inf), v, np.random.default_rng(1).uniform(-0.1, 1.2, 20001),
+                           [0.0, -1.0, 1.0, 5.0, np.nan, np.inf, -np.inf, -0.0]])
+    vals = np.resize(vals, (vals.size // 3) * 3).reshape(-1, 3)
+    assert np.array_equal(emu.quantize_bgr(vals), orc.quantize_bgr(vals))
+
+
+@pytest.mark.parametrize("accel", ["linear", "bvh"])
+def test_intersect_is_bit_identical(rt, orc, scenes, accel):
+    desc = scenes.random_spheres(2000, 77, 25.0, 8, 8)
+    rays = _rays(np.random.default_rng(5), 30000, 30.0, 9.0)
+    data = desc["objects"][1]["data"]
+    inside = np.concatenate([data[:1000, :3], np.random.default_rng(6).normal(size=(1000, 3))], axis=1)  # rays starting inside spheres
+    surf = data[1000:2000, :3] + data[1000:2000, 3:4] * np.array([0.0, 1.0, 0.0])                         # rays leaving sphere tops
+    leaving = np.concatenate([surf, np.random.default_rng(8).normal(size=(1000, 3))], axis=1)
+    rays = np.concatenate([rays, inside, leaving])
+    ids, t, nrm = emu.trace_rays(emu.Scene(desc), rays, accel=rt.ACCEL_BVH if accel == "bvh" else rt.ACCEL_LINEAR)
+    rid, rt_, rn = orc.OracleScene(desc).trace_rays(rays)
+    assert np.array_equal(ids, rid) and np.array_equal(t, rt_) and np.array_equal(nrm, rn)
+    assert (ids >= 0).mean() > 0.3
+
+
+def test_bvh_equals_linear_scan_on_degenerate_input(rt, orc):
+    """ties, duplicates, nested and huge/tiny spheres, NaN/inf/zero rays: the BVH must return the scan's object index"""
+    S = rt.scene
+    b = S.SceneBuilder()
+    m = b.add_material(S.PhongMaterial((0.5, 0.5, 0.5), (0, 0, 0), 1.0, (0, 0, 0)))
+    b.add_object(S.Plane((0, -1, 0), (0, 1, 0)), m)
+    rng = np.random.default_rng(11)
+    c = rng.uniform(-5, 5, size=(60, 3))
+    r = rng.uniform(0.05, 1.5, size=60)
+    data = np.concatenate([np.c_[c, r], np.c_[c, r],                        # every sphere twice (coincident: lower index wins)
+                           np.c_[c[:20], r[:20] * 0.5],                      # nested
+                           [[0, 0, 0, 40.0], [0, 0, 0, 1e-6], [1e6, 0, 0, 1.0]]])
+    b.add_spheres(data, np.zeros(len(data), dtype=np.uint32))
+    b.camera = S.SimplePerspectiveCamera.new((0, 0, 20), (0, 0, -1), (0, 1, 0), 2.0)
+    b.background = S.SolidColorBackground((0, 0, 0))
+    b.options = S.Options(8, 8, 1)
+    desc = b.build()
+    rays = _rays(rng, 20000, 8.0, 6.0)
+    rays[:5000, :3] = c[rng.integers(0, 60, 5000)]                           # from sphere centres
+    special = np.array([[0, 0, 0, 0, 0, 0], [np.nan, 0, 0, 0, 0, 1], [0, 0, 0, np.nan, 0, 1], [0, 0, 0, np.inf, 0, 0],
+                        [0, 0, 100, 0, 0, -1e-300], [0, 0, 100, 0, 0, -1e300], [1e300, 0, 0, -1, 0, 0], [0, -1, 5, 1, 0, 0]])
+    rays = np.concatenate([rays, special])
+    a = emu.trace_rays(emu.Scene(desc), rays, accel=rt.ACCEL_LINEAR)
+    bb = emu.trace_rays(emu.Scene(desc), rays, accel=rt.ACCEL_BVH)
+    ref = orc.OracleScene(desc).trace_rays(rays)
+    for got in (a, bb):
+        assert np.array_equal(got[0], ref[0])
+        assert np.array_equal(got[1], ref[1], equal_nan=True)
+        assert np.array_equal(got[2], ref[2], equal_nan=True)
+    n_nodes, depth = emu.bvh_stats(emu.Scene(desc))
+    assert n_nodes == len(data) - 1 and depth < 96
+
+
+@pytest.mark.parametrize("accel", ["linear", "bvh"])
+def test_shadow_any_hit_equals_closest_hit_rule(rt, orc, scenes, accel):
+    """src/raytrace.rs:43-50: occluded iff the CLOSEST hit exists and (no range or t*t < r2); the kernels use any-hit"""
+    desc = scenes.random_spheres(800, 5, 12.0, 8, 8)
+    rng = np.random.default_rng(2)
+    rays = _rays(rng, 20000, 14.0, 8.0)
+    r2 = np.where(rng.uniform(size=20000) < 0.3, -1.0, rng.uniform(0.0, 30.0, 20000) ** 2)
+    occ = emu.shadow_rays(emu.Scene(desc), rays, r2, accel=rt.ACCEL_BVH if accel == "bvh" else rt.ACCEL_LINEAR)
+    ids, t, _ = orc.OracleScene(desc).trace_rays(rays)
+    with np.errstate(invalid="ignore"):
+        want = (ids >= 0) & ((r2 < 0) | (t * t < r2))
+    assert np.array_equal(occ, want)
+    assert 0.1 < want.mean() < 0.9
+
+
+def test_render_cornell_text(rt, orc):
+    from oracle import scene_text
+    desc = scene_text.deserialize(REF_TEXT_SCENE)
+    kw = dict(width=120, height=100, antialias=3, seed=21)
+    check(emu.render(emu.Scene.parse(REF_TEXT_SCENE), **kw), orc.OracleScene(desc).render(**kw), "cornell")
+
+
+@pytest.mark.parametrize("accel", ["linear", "bvh"])
+def test_render_all_materials(rt, orc, scenes, accel):
+    desc = scenes.materials_showcase(128, 96, 2)
+    ref = orc.OracleScene(desc).render(max_depth=5, seed=4)
+    got = emu.render(emu.Scene(desc), max_depth=5, seed=4, accel=rt.ACCEL_BVH if accel == "bvh" else rt.ACCEL_LINEAR)
+    same = check(got, ref, "showcase/" + accel)
+    # the accumulators themselves agree to re-association error (path-throughput form vs recursion)
+    ok = np.isfinite(ref["accum"])
+    assert np.allclose(got["accum"][ok] / 2.0, ref["accum"][ok], rtol=1e-11, atol=1e-13)  # product keeps the SUM over the 2 aa samples
+    assert same > 0.9999
+
+
+def test_render_spheres_depth8(rt, orc, scenes):
+    desc = scenes.random_spheres(1500, 0x5EED0003, 25.0, 160, 90)
+    ref = orc.OracleScene(desc).render(max_depth=8, seed=3)
+    check(emu.render(emu.Scene(desc), max_depth=8, seed=3, accel=rt.ACCEL_BVH), ref, "spheres1500")
+    assert ref["stats"]["rays"] > 5 * 160 * 90
+
+
+def test_render_skybox_dof_area(rt, orc, scenes):
+    S = rt.scene
+    cam = S.DepthOfFieldCamera.new(S.SimplePerspectiveCamera.new((0, 4, 14), (0, -0.2, -1), (0, 1, 0), 2.0), 12.0, 0.15, 2)
+    desc = scenes.random_spheres(120, 5, 10.0, 100, 72, antialias=2, reflective_only=True, background=S.SkyboxBackground(*scenes.skybox_faces(64, 8)), camera=cam)
+    desc["lights"].append(S.AreaLight((-3.0, 9.0, -3.0), (6.0, 0.0, 0.0), (0.0, 0.0, 6.0), (0.6, 0.6, 0.5)))
+    ref = orc.OracleScene(desc).render(max_depth=4, seed=8)
+    got = emu.render(emu.Scene(desc), max_depth=4, seed=8)
+    check(got, ref, "skybox/dof/area")  # same libm on both sides here, so this is exact on the CPU
+
+
+def test_depth_and_significance_edges(rt, orc, scenes):
+    desc = scenes.materials_showcase(48, 36, 1)
+    for md, ms in [(0, 1 / 512), (1, 1 / 512), (12, 1 / 512), (6, 0.0), (6, 0.2)]:
+        ref = orc.OracleScene(desc).render(max_depth=md, min_significance=ms, seed=1)
+        check(emu.render(emu.Scene(desc), max_depth=md, min_significance=ms, seed=1), ref, "md%d ms%g" % (md, ms))
+
+
+def test_antialias_zero_and_empty_scene(rt, orc):
+    S = rt.scene
+    b = S.SceneBuilder()
+    b.camera = S.SimplePerspectiveCamera.new((0, 0, 0), (0, 0, -1), (0, 1, 0), 1.0)
+    b.background = S.SolidColorBackground((0.051, 0.18, 0.5))
+    b.options = S.Options(5, 3, 1)   # width 5: bytewidth 16, one padding byte per row
+    desc = b.build()
+    got = emu.render(emu.Scene(desc))
+    ref = orc.OracleScene(desc).render()
+    check(got, ref, "empty scene")
+    assert (got["ids"] == -1).all() and got["bgr"][0, :15].tolist() == [188, 118, 64] * 5 and got["bgr"][0, 15] == 0
+    z = emu.render(emu.Scene(desc), antialias=0)
+    assert (z["bgr"][:, :15] == 255).all()

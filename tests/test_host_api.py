@@ -1,0 +1,222 @@
+"""Host side of the drop-in boundary, no GPU needed: the C-ABI library loads and exports every symbol the header
+declares, the scene model / scene-text reader (serialize::deserialize, src/serialize.rs) / BMP sink (src/bmp.rs) behave
+like the reference, and every compute entry point fails loudly (RT_ERR_CUDA) instead of falling back to a CPU path.
+"""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from test_gpu_parity import REF_TEXT_SCENE
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "raytrace_b200.h")
+
+
+def header_symbols():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"RT_API\s+[^;(]*?\b(rt_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol(rt):
+    syms = header_symbols()
+    assert len(syms) >= 45, syms
+    L = C.CDLL(rt.LIB_PATH)
+    for s in syms:
+        assert hasattr(L, s), "libraytrace_b200.so does not export %s" % s
+    B = __import__("importlib").import_module("rust-raytrace_b200._binding")
+    assert sorted(B.API) == syms, "binding table and header disagree: %s" % (set(B.API) ^ set(syms))
+    # nothing but the C ABI is visible (-fvisibility=hidden): no C++ or oracle symbols leak
+    out = subprocess.run(["nm", "-D", "--defined-only", rt.LIB_PATH], capture_output=True, text=True).stdout
+    exported = [ln.split()[-1] for ln in out.splitlines() if " T " in ln]
+    assert sorted(exported) == syms, set(exported) ^ set(syms)
+    assert not any("orc_" in ln or "emu_" in ln for ln in out.splitlines())
+
+
+def test_product_does_not_reference_the_oracle():
+    pkg = os.path.join(ROOT, "rust-raytrace_b200")
+    for dirpath, _, files in os.walk(pkg):
+        if os.path.basename(dirpath) in ("build", "lib", "__pycache__"):
+            continue
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                if f.endswith(".py"):
+                    bad = re.search(r"^\s*(import|from)\s+(oracle|tests|emu)\b|liboracle|libemu", src, flags=re.M)
+                else:  # comments may mention the test harness; includes / dlopen may not
+                    bad = re.search(r"#\s*include[^\n]*(oracle|emu)|dlopen|liboracle|libemu", src)
+                assert not bad, "%s refers to test infrastructure" % f
+
+
+def test_version_and_defaults(rt):
+    assert rt.version().startswith("raytrace_b200") and "sm_100a" in rt.version()
+    B = __import__("importlib").import_module("rust-raytrace_b200._binding")
+    o = B.make_opts(rt.lib())
+    assert o.max_depth == 4 and o.min_significance == 1.0 / 512.0  # src/raytrace.rs:17-18
+    assert o.antialias == 0xFFFFFFFF and o.width == 0 and o.height == 0
+    assert o.world == 1 and o.rank == 0 and o.accel == rt.ACCEL_AUTO and o.fp_mode == rt.FP_STRICT
+
+
+def test_no_cpu_fallback(rt, scenes):
+    if rt.device_count() > 0:
+        pytest.skip("a GPU is visible: the failure path cannot be observed")
+    sc = rt.Scene(scenes.materials_showcase(16, 12, 1))
+    for call in (lambda: rt.raytrace.render(sc), lambda: rt.Context(sc), lambda: rt.raytrace.intersect(sc, np.zeros((1, 6))),
+                 lambda: rt.raytrace.project(sc, np.zeros((1, 2))), lambda: rt.color.write_bgr(np.zeros((1, 3)))):
+        with pytest.raises(rt.RtError) as e:
+            call()
+        assert e.value.code == -4 and "no CPU fallback" in e.value.message
+
+
+# ---- serialize::deserialize -------------------------------------------------------------------------------
+def test_parse_reference_scene(rt):
+    sc = rt.serialize.deserialize(REF_TEXT_SCENE)
+    assert sc.options() == (800, 800, 1024)
+    info = sc.info()
+    assert info["n_objects"] == 7 and info["n_planes"] == 5 and info["n_spheres"] == 2 and info["n_lights"] == 0
+    assert info["camera_kind"] == 0 and info["background_kind"] == 0
+    pos, m = sc.camera()
+    assert pos.tolist() == [0, 3, 17] and np.array_equal(m, [[1, 0, 0], [0, 1, 0], [0, 0, -3.6]])
+
+
+def test_text_and_builder_scenes_are_identical(rt, scenes):
+    for desc in (scenes.materials_showcase(64, 48, 2), scenes.random_spheres(200, 3, 9.0, 32, 32)):
+        a = rt.Scene(desc).dump()
+        b = rt.serialize.deserialize(rt.scene.to_text(desc)).dump()
+        assert a == b
+        assert len(a) > 500
+
+
+def test_parser_agrees_with_python_restatement(rt, scenes, orc):
+    """oracle/scene_text.py restates src/serialize.rs independently; both readers must build the same scene."""
+    from oracle import scene_text
+    text = rt.scene.to_text(scenes.materials_showcase(40, 30, 3))
+    text = "# leading comment\n" + text.replace("objects:", "/* block\n comment */ objects:").replace("lights:", "// line comment\n lights:")
+    desc = scene_text.deserialize(text)
+    assert rt.Scene(desc).dump() == rt.serialize.deserialize(text).dump()
+    # camera matrix computed by the host library == the oracle's (src/camera.rs:51-63)
+    pos, m = rt.serialize.deserialize(text).camera()
+    opos, om = orc.OracleScene(desc).camera()
+    assert np.array_equal(pos, opos) and np.array_equal(m, om)
+
+
+BAD_SCENES = [
+    "", "{", "}", "{ objects: [ } ", "{ objects: [] lights: [] }", "{ objects: [], }", "[", "{ objects: 5 }",
+    "{ objects: [ { bounds: Cube { } } ] }",
+    "{ objects: [ { bounds: Sphere { center: (0, 0) radius: 1 } } ] }",
+    "{ objects: [ { bounds: Sphere { center: (0, 0, 0) radius: abc } material: PhongMaterial {} } ] }",
+    "{ objects: [ { bounds: Sphere { radius: 1 center: (0, 0, 0) } } ] }",
+    '{ objects: [] lights: [] camera: SimplePerspectiveCamera new((0,0,0),(0,0,-1),(0,1,0)) }',
+    '{ objects: [] lights: [] camera: SimplePerspectiveCamera look_at((0,0,0),(0,0,-1),(0,1,0), 45 furlongs, 1) }',
+    '{ objects: [] lights: [] camera: Pinhole new() }',
+    '{ objects: [] lights: [ { model: SpotLight { } color: rgb(1,1,1) } ] }',
+    '{ objects: [] lights: [] camera: SimplePerspectiveCamera new((0,0,0),(0,0,-1),(0,1,0),1) background: SolidColorBackground { color: rgb(1,1) } }',
+    '{ objects: [] lights: [] camera: SimplePerspectiveCamera new((0,0,0),(0,0,-1),(0,1,0),1) background: SolidColorBackground { color: rgb(1,1,1) } options: { width: -3 height: 2 antialias: 1 } }',
+    '{ objects: [] lights: [] camera: SimplePerspectiveCamera new((0,0,0),(0,0,-1),(0,1,0),1) background: SolidColorBackground { color: rgb(1,1,1) } options: { width: 3 height: 2 antialias: 1 } } trailing',
+    '{ objects: [ "unterminated ] }', "{ objects: [ /* unterminated ] }", '{ objects: [ "bad \\q escape" ] }', "{ objects: @ }", "{ objects: [ 1e400 ] }",
+]
+
+
+@pytest.mark.parametrize("i", range(len(BAD_SCENES)))
+def test_syntax_errors_match_reference_format(rt, i):
+    """error text is upstream's `row:col: message` (src/serialize.rs:244-272); compared with the Python restatement"""
+    from oracle import scene_text
+    text = BAD_SCENES[i]
+    want = None
+    try:
+        scene_text.deserialize(text)
+    except scene_text.SyntaxError_ as e:
+        want = str(e)
+    if want is None:
+        rt.serialize.deserialize(text)  # both accept
+        return
+    with pytest.raises(rt.serialize.SyntaxError) as e:
+        rt.serialize.deserialize(text)
+    assert e.value.code == -2
+    assert e.value.message == want
+    assert re.match(r"^\d+:\d+: ", e.value.message)
+
+
+def test_parse_warnings_and_units(rt):
+    from oracle import scene_text
+    base = ('{ objects: [] lights: [] camera: SimplePerspectiveCamera look_at((0,1,0),(0,0,-1),(0,1,0), %s, 2.0) '
+            'background: SolidColorBackground { color: rgb(0,0,0) } options: { width: 4.0 height: 3.7 antialias: 1 } }')
+    a = rt.serialize.deserialize(base % "90 deg")
+    b = rt.serialize.deserialize(base % ("%r rad" % (np.pi / 2)))
+    assert np.allclose(a.camera()[1], b.camera()[1], rtol=0, atol=1e-15)
+    d, warns = scene_text.deserialize(base % "90 deg", return_warnings=True)
+    assert a.options() == (d["options"]["width"], d["options"]["height"], d["options"]["antialias"])
+    assert a.warnings().strip().splitlines() == [w.strip() for w in warns]
+
+
+def test_parse_file_and_missing_file(rt, tmp_path):
+    p = tmp_path / "scene.txt"
+    p.write_text(REF_TEXT_SCENE)
+    L = rt.lib()
+    out = C.c_void_p()
+    err = C.create_string_buffer(256)
+    assert L.rt_scene_parse_file(os.fsencode(str(p)), C.byref(out), err, 256) == 0
+    L.rt_scene_free(out)
+    assert L.rt_scene_parse_file(os.fsencode(str(tmp_path / "nope.txt")), C.byref(out), err, 256) == -3
+
+
+def test_builder_validation(rt):
+    L = rt.lib()
+    B = __import__("importlib").import_module("rust-raytrace_b200._binding")
+    h = C.c_void_p(L.rt_scene_new())
+    one = np.array([[0.0, 0.0, 0.0, 1.0]])
+    mat = np.array([3], dtype=np.uint32)
+    assert L.rt_scene_add_spheres(h, 1, B.ptr(one, C.c_double), B.ptr(mat, C.c_uint32)) == -1  # material index out of range
+    assert b"material" in L.rt_last_error()
+    assert L.rt_scene_add_plane(h, B.d3((0, 0, 0)), B.d3((0, 1, 0)), 0) == -1
+    assert L.rt_scene_set_camera_dof(h, 1.0, 0.1, 2) == -1                                          # no perspective camera yet
+    assert L.rt_scene_set_skybox_face(h, 6, 2, 2, None) == -1
+    assert L.rt_scene_add_material_phong(h, B.d3((1, 1, 1)), B.d3((0, 0, 0)), 1.0, B.d3((0, 0, 0))) == 0
+    mat[0] = 0
+    assert L.rt_scene_add_spheres(h, 1, B.ptr(one, C.c_double), B.ptr(mat, C.c_uint32)) == 0
+    L.rt_scene_free(h)
+
+
+# ---- skybox textures (src/texture.rs:34-37 for the formats decodable without the `image` crate) --------------
+def test_skybox_face_loaders(rt, scenes, tmp_path):
+    faces = scenes.skybox_faces(16, 4)
+    S = rt.scene
+    desc = scenes.random_spheres(5, 1, 3.0, 8, 8, background=S.SkyboxBackground(*faces))
+    paths = []
+    for i, f in enumerate(faces):
+        if i % 2 == 0:  # binary PPM
+            p = tmp_path / ("f%d.ppm" % i)
+            p.write_bytes(b"P6\n# c\n16 16\n255\n" + f.tobytes())
+        else:           # 24-bit BMP, bottom-up BGR rows
+            p = tmp_path / ("f%d.bmp" % i)
+            rows = np.zeros((16, rt.bmp.bytewidth(16)), dtype=np.uint8)
+            rows[:, :48] = f[::-1, :, ::-1].reshape(16, 48)
+            rt.bmp.write(str(p), 16, 16, rows)
+        paths.append(str(p))
+    from_text = rt.serialize.deserialize(S.to_text(desc, texture_paths=paths))
+    assert from_text.dump() == rt.Scene(desc).dump()
+    assert from_text.info()["background_kind"] == 1
+    with pytest.raises(rt.RtError):
+        rt.serialize.deserialize(S.to_text(desc, texture_paths=[str(tmp_path / "missing.ppm")] * 6))
+
+
+# ---- bmp (src/bmp.rs:10-61) -------------------------------------------------------------------------------
+def test_bmp_header_and_file(rt, orc, tmp_path):
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "outbmp_block_means.npz"))
+    assert rt.bmp.header(800, 800) == g["header"].tobytes()
+    for w, h in [(1, 1), (2, 3), (3, 2), (5, 5), (800, 800), (3840, 2160), (7680, 4320), (1023, 7)]:
+        assert rt.bmp.header(w, h) == orc.bmp_header(w, h)
+        assert rt.bmp.bytewidth(w) == orc.bytewidth(w) == (3 * w + 3) // 4 * 4
+    rows = np.random.default_rng(0).integers(0, 256, size=(7, rt.bmp.bytewidth(5)), dtype=np.uint8)
+    p = tmp_path / "o.bmp"
+    rt.bmp.write(str(p), 5, 7, rows)
+    raw = p.read_bytes()
+    assert raw[:122] == orc.bmp_header(5, 7) and raw[122:] == rows.tobytes() and len(raw) == 122 + 16 * 7
+    with pytest.raises(ValueError):
+        rt.bmp.write(str(p), 5, 7, rows[:, :15])
+    with pytest.raises(rt.RtError):
+        rt.bmp.write(str(tmp_path / "no_such_dir" / "o.bmp"), 5, 7, rows)
