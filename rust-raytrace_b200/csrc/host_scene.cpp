@@ -142,8 +142,9 @@ int flatten_scene(const rt_scene* s, FlatScene* f) {
     f->obj_shape.assign(s->objects.size(), 0u);
     f->obj_material.assign(s->objects.size(), 0u);
     f->sph.reserve(s->n_spheres); f->sph_obj.reserve(s->n_spheres);
-    for (int a = 0; a < 3; a++) { f->centroid_lo[a] = INFINITY; f->centroid_hi[a] = -INFINITY; }
+    for (int a = 0; a < 3; a++) { f->centroid_lo[a] = INFINITY; f->centroid_hi[a] = -INFINITY; f->box_lo[a] = INFINITY; f->box_hi[a] = -INFINITY; }
     double cmax = 0.0, rmin = INFINITY;
+    bool finite = true;
     for (size_t i = 0; i < s->objects.size(); i++) {
         const HostObject& o = s->objects[i];
         f->obj_material[i] = o.material;
@@ -167,10 +168,15 @@ int flatten_scene(const rt_scene* s, FlatScene* f) {
                 if (o.p[a] > f->centroid_hi[a]) f->centroid_hi[a] = o.p[a];
                 const double m = std::fabs(o.p[a]) + ar;
                 if (m > cmax) cmax = m;
+                if (o.p[a] - ar < f->box_lo[a]) f->box_lo[a] = o.p[a] - ar;
+                if (o.p[a] + ar > f->box_hi[a]) f->box_hi[a] = o.p[a] + ar;
+                if (!std::isfinite(m)) finite = false;
             }
             if (ar < rmin) rmin = ar;
         }
     }
+    if (!finite || f->sph.empty())  // no usable bounds: rays are never advanced (t0 = 0)
+        for (int a = 0; a < 3; a++) { f->box_lo[a] = -INFINITY; f->box_hi[a] = INFINITY; }
     f->cmax = cmax;
     f->rmin = (rmin > 0.0 && std::isfinite(rmin)) ? rmin : 1e-300;
     int mc = 0;
@@ -198,6 +204,7 @@ void fill_scene_header(const rt_scene* s, const FlatScene& f, DeviceScene* ds) {
     ds->max_children = f.max_children;
     ds->bvh_cmax = f.cmax;
     ds->bvh_rmin = f.rmin;
+    for (int a = 0; a < 3; a++) { ds->bvh_lo[a] = f.box_lo[a]; ds->bvh_hi[a] = f.box_hi[a]; }
 }
 
 bool accel_uses_bvh(int accel, uint32_t n_spheres) {

@@ -68,6 +68,7 @@ struct FlatScene {
     std::vector<PlaneRec> planes;
     std::vector<uint32_t> obj_shape, obj_material;
     double centroid_lo[3], centroid_hi[3];
+    double box_lo[3], box_hi[3];  // bounds of the sphere boxes (c -+ |r|); -+inf when unusable
     double cmax, rmin;
     int32_t max_children;
 };

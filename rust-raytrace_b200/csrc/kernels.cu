@@ -255,7 +255,7 @@ __global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_consta
     TravStack st; st.sp = 0;
     RayQ r; BoxRay32 br; Closest best;
     r = make_rayq(v3(0, 0, 0), v3(0, 0, 0)); best = closest_none();
-    br.ix = br.iy = br.iz = br.px = br.py = br.pz = br.mx = br.my = br.mz = 0.0f; br.finite = false;
+    br.ix = br.iy = br.iz = br.px = br.py = br.pz = br.mx = br.my = br.mz = 0.0f; br.t0 = 0.0; br.enter = false;
     int32_t cur = TRAV_EMPTY;
     float bound = 0.0f;
     uint32_t ray = 0;
@@ -274,7 +274,7 @@ __global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_consta
                     cur = TRAV_EMPTY;
                     if (!best.nan && sc.n_spheres > 0) {
                         br = make_boxray32(sc, r.o, r.d);
-                        if (br.finite) { cur = 0; bound = closest_bound32(best); }
+                        if (br.enter) { cur = 0; bound = closest_bound32(best.t, br.t0); }
                     }
                     active = true;
                 }
@@ -295,7 +295,7 @@ __global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_consta
                 active = false;
             } else {
                 leaf_closest(sc, r, ~cur, best, tc);
-                bound = closest_bound32(best);
+                bound = closest_bound32(best.t, br.t0);
                 cur = trav_pop(st, bound);
             }
         }
@@ -309,7 +309,7 @@ __global__ void __launch_bounds__(BVH_THREADS) k_shadow_bvh(const __grid_constan
     TravStack st; st.sp = 0;
     RayQ r; BoxRay32 br;
     r = make_rayq(v3(0, 0, 0), v3(0, 0, 0));
-    br.ix = br.iy = br.iz = br.px = br.py = br.pz = br.mx = br.my = br.mz = 0.0f; br.finite = false;
+    br.ix = br.iy = br.iz = br.px = br.py = br.pz = br.mx = br.my = br.mz = 0.0f; br.t0 = 0.0; br.enter = false;
     int32_t cur = TRAV_EMPTY;
     float bound = 0.0f;
     double range2 = -1.0;
@@ -331,7 +331,7 @@ __global__ void __launch_bounds__(BVH_THREADS) k_shadow_bvh(const __grid_constan
                     occluded = shadow_result(s, range2);
                     if (!s.nan && !s.any && sc.n_spheres > 0) {
                         br = make_boxray32(sc, r.o, r.d);
-                        if (br.finite) { cur = 0; bound = shadow_bound32(range2); }
+                        if (br.enter) { cur = 0; bound = shadow_bound32(range2, br.t0); }
                     }
                     active = true;
                 }

@@ -212,19 +212,24 @@ RT_HD bool shadow_result(const Shadow& s, double range2) { return s.nan ? (range
 // BVH traversal.
 //
 // The box test is only a conservative FILTER: it may pass a box the ray misses, never reject a box whose sphere
-// the exact test would hit.  It runs in f32 (native FFMA/FMNMX: a third of the instructions of an f64 slab test,
-// whose min/max are emulated) on the f32 boxes that the build rounded outward.  The leaf test is the same f64
-// expression as the linear scan (sphere_hit), so the hit, its t and the tie-break are the scan's, bit for bit.
+// the exact test would hit.  It runs in f32 (native FFMA/FMNMX) on the f32 boxes that the build rounded outward.
+// The leaf test is the same f64 expression as the linear scan (sphere_hit), so the hit, its t and the tie-break
+// are the scan's, bit for bit.
 //
 // Conservativeness of the f32 filter (DESIGN.md "BVH == linear scan"):
-//   additive errors  -- rounding the ray origin to f32 (<= 2^-24 |o|), the rounding of (o +- pad)*inv, and the
-//                       rounding error of the exact test's discriminant (which makes the scan "hit" spheres inflated
-//                       by up to min(E/2r_min, sqrt(E)), E = 64 eps S^2) -- are covered by widening every box by `pad`;
+//   advance          -- the ray is first advanced (in f64) to where it enters the bounds of all sphere boxes, so the
+//                       filter works on an origin of scene magnitude however far away the ray started (ground-plane
+//                       hits near the horizon are 10^6..10^9 units out); filter distances are t - t0;
+//   additive errors  -- rounding the advanced origin to f32, the rounding of (o +- pad)*inv, the error of the advance
+//                       itself, and the rounding error of the exact test's discriminant (which makes the scan "hit"
+//                       spheres inflated by up to min(E/2r_min, sqrt(E)), E = 64 eps S^2, S the magnitude of the
+//                       ORIGINAL origin) -- are covered by widening every box by `pad`;
 //   relative errors  -- inv = fl32(1/d) and the FFMA rounding scale each slab distance by (1 +- 2^-23) -- are covered
 //                       by shrinking the entry distance and growing the exit distance by 2^-21.
 // ---------------------------------------------------------------------------------------------------------
-constexpr int BVH_STACK = 96;          // >= 63 Morton bits + 32 tie-break bits
 #define RT_BVH_TSLACK 1.000000000001   // relative slack when a t of the exact test bounds the filter
+
+constexpr int BVH_STACK = 96;          // >= 63 Morton bits + 32 tie-break bits
 constexpr int32_t TRAV_EMPTY = (int32_t)0x80000000;  // "no node left"; never a valid ~leaf (n_spheres < 2^31 - 16)
 
 struct TraverseCount {
@@ -233,9 +238,10 @@ struct TraverseCount {
 
 struct BoxRay32 {
     float ix, iy, iz;  // clamped reciprocal direction
-    float px, py, pz;  // (o + pad) * inv
-    float mx, my, mz;  // (o - pad) * inv
-    bool finite;
+    float px, py, pz;  // (o' + pad) * inv
+    float mx, my, mz;  // (o' - pad) * inv
+    double t0;         // ray parameter of the advanced origin o' = o + d * t0 (0 when o is inside the sphere bounds)
+    bool enter;        // false: no sphere can be hit (non-finite ray, or the ray misses the bounds) -> skip the tree
 };
 
 RT_HD float safe_inv32(double d) {
@@ -259,20 +265,50 @@ RT_HD float f64_to_f32_up(double x) {
 
 RT_HD BoxRay32 make_boxray32(const DeviceScene& sc, V3 o, V3 d) {
     BoxRay32 b;
-    double s = fmax(fmax(fabs(o.x), fabs(o.y)), fabs(o.z));
-    double dm = fmax(fmax(fabs(d.x), fabs(d.y)), fabs(d.z));
+    const double s = fmax(fmax(fabs(o.x), fabs(o.y)), fabs(o.z));
+    const double dm = fmax(fmax(fabs(d.x), fabs(d.y)), fabs(d.z));
     // any non-finite origin/direction makes every sphere discriminant NaN (=> miss); skip the tree
-    b.finite = (s < 1e30) && (dm < 1e30) && (o.x == o.x) && (o.y == o.y) && (o.z == o.z) && (d.x == d.x) && (d.y == d.y) && (d.z == d.z);
-    double S = s + sc.bvh_cmax;
-    double E = 64.0 * 2.220446049250313e-16 * S * S;  // bound on the rounding error of the discriminant, in r^2 units
-    double pad = S * 0x1.0p-20 + fmin(E / (2.0 * sc.bvh_rmin), sqrt(E));
+    b.enter = (s < 1e30) && (dm < 1e30) && (o.x == o.x) && (o.y == o.y) && (o.z == o.z) && (d.x == d.x) && (d.y == d.y) && (d.z == d.z);
+    b.t0 = 0.0;
+    const double St = s + sc.bvh_cmax;
+    const double E = 64.0 * 2.220446049250313e-16 * St * St;  // bound on the rounding error of the discriminant, in r^2 units
+    const double infl = fmin(E / (2.0 * sc.bvh_rmin), sqrt(E));
+    V3 oo = o;
+    if (b.enter) {
+        // f64 slab test against the sphere bounds grown by the inflation: where does the ray enter them?
+        const double m = infl + St * 0x1.0p-40;
+        const double oa[3] = {o.x, o.y, o.z}, da[3] = {d.x, d.y, d.z};
+        double te = 0.0, tx = (double)INFINITY;
+        bool miss = false;
+        for (int a = 0; a < 3; a++) {
+            const double lo = sc.bvh_lo[a] - m, hi = sc.bvh_hi[a] + m;
+            if (fabs(da[a]) < 1e-300) {
+                if (oa[a] < lo || oa[a] > hi) miss = true;
+            } else {
+                double t1 = (lo - oa[a]) / da[a], t2 = (hi - oa[a]) / da[a];
+                if (t1 > t2) { const double w = t1; t1 = t2; t2 = w; }
+                if (t1 > te) te = t1;
+                if (t2 < tx) tx = t2;
+            }
+        }
+        if (miss || te * (1.0 - 0x1.0p-40) > tx * (1.0 + 0x1.0p-40)) {
+            b.enter = false;
+        } else if (te > 0.0) {
+            b.t0 = te * (1.0 - 0x1.0p-40);
+            oo = v3(o.x + d.x * b.t0, o.y + d.y * b.t0, o.z + d.z * b.t0);
+        }
+    }
+    const double s2 = fmax(fmax(fabs(oo.x), fabs(oo.y)), fabs(oo.z));
+    const double S = s2 + sc.bvh_cmax;
+    const double pad = S * 0x1.0p-20 + infl + (s + dm * b.t0) * 0x1.0p-50;
     b.ix = safe_inv32(d.x); b.iy = safe_inv32(d.y); b.iz = safe_inv32(d.z);
-    b.px = (float)((o.x + pad) * (double)b.ix); b.py = (float)((o.y + pad) * (double)b.iy); b.pz = (float)((o.z + pad) * (double)b.iz);
-    b.mx = (float)((o.x - pad) * (double)b.ix); b.my = (float)((o.y - pad) * (double)b.iy); b.mz = (float)((o.z - pad) * (double)b.iz);
+    b.px = (float)((oo.x + pad) * (double)b.ix); b.py = (float)((oo.y + pad) * (double)b.iy); b.pz = (float)((oo.z + pad) * (double)b.iz);
+    b.mx = (float)((oo.x - pad) * (double)b.ix); b.my = (float)((oo.y - pad) * (double)b.iy); b.mz = (float)((oo.z - pad) * (double)b.iz);
     return b;
 }
 
-// conservative entry distance (>= 0) of the padded box if it can be hit within [0, bound], else -1
+// conservative entry distance (>= 0, measured from the advanced origin) of the padded box if it can be hit within
+// [0, bound], else -1
 RT_HD float box_entry32(const BoxRay32& b, const float* lo, const float* hi, float bound) {
     float ax = fmaf(lo[0], b.ix, -b.px), bx = fmaf(hi[0], b.ix, -b.mx);
     float ay = fmaf(lo[1], b.iy, -b.py), by = fmaf(hi[1], b.iy, -b.my);
@@ -339,8 +375,14 @@ RT_HD int32_t trav_descend(const DeviceScene& sc, const BoxRay32& br, int32_t cu
     return cur;
 }
 
-RT_HD float closest_bound32(const Closest& best) { return f64_to_f32_up(best.t * RT_BVH_TSLACK); }
-RT_HD float shadow_bound32(double range2) { return range2 < 0.0 ? INFINITY : f64_to_f32_up(sqrt(range2) * RT_BVH_TSLACK); }
+// filter bound (distance from the advanced origin) that no hit closer than `t` of the exact test can exceed
+RT_HD float closest_bound32(double t, double t0) { return f64_to_f32_up((t - t0) * RT_BVH_TSLACK + (fabs(t) + t0) * 1e-12); }
+RT_HD float shadow_bound32(double range2, double t0) {
+    if (range2 < 0.0) return INFINITY;
+    const double r = sqrt(range2);
+    return f64_to_f32_up((r - t0) * RT_BVH_TSLACK + (r + t0) * 1e-12);
+}
+
 
 // exact test of Morton-slot k against the running closest hit; returns the new filter bound
 RT_HD void leaf_closest(const DeviceScene& sc, const RayQ& r, int32_t k, Closest& best, TraverseCount& tc) {
@@ -362,16 +404,16 @@ RT_HD void closest_bvh(const DeviceScene& sc, const RayQ& r, int32_t& id, double
     planes_closest(sc, r, best);
     if (!best.nan && sc.n_spheres > 0) {
         const BoxRay32 br = make_boxray32(sc, r.o, r.d);
-        if (br.finite) {
+        if (br.enter) {
             TravStack st;
             st.sp = 0;
             int32_t cur = 0;
-            float bound = closest_bound32(best);
+            float bound = closest_bound32(best.t, br.t0);
             while (true) {
                 cur = trav_descend(sc, br, cur, bound, st, tc);
                 if (cur == TRAV_EMPTY) break;
                 leaf_closest(sc, r, ~cur, best, tc);
-                bound = closest_bound32(best);
+                bound = closest_bound32(best.t, br.t0);
                 cur = trav_pop(st, bound);
             }
         }
@@ -384,11 +426,11 @@ RT_HD bool shadow_bvh(const DeviceScene& sc, const RayQ& r, double range2, Trave
     planes_shadow(sc, r, range2, s);
     if (!s.nan && !s.any && sc.n_spheres > 0) {
         const BoxRay32 br = make_boxray32(sc, r.o, r.d);
-        if (br.finite) {
+        if (br.enter) {
             TravStack st;
             st.sp = 0;
             int32_t cur = 0;
-            const float bound = shadow_bound32(range2);
+            const float bound = shadow_bound32(range2, br.t0);
             while (true) {
                 cur = trav_descend(sc, br, cur, bound, st, tc);
                 if (cur == TRAV_EMPTY) break;

@@ -95,6 +95,7 @@ struct DeviceScene {
     uint32_t _pad0;
     double bvh_cmax;  // max over spheres of (|c|_inf + r): scale term of the per-ray box padding
     double bvh_rmin;  // min radius
+    double bvh_lo[3], bvh_hi[3];  // bounds of all sphere boxes (f64): rays are advanced to this box before the f32 filter
 };
 
 // Ray queue of one wavefront level, structure of arrays (one allocation, capacity `cap`)

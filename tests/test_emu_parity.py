@@ -159,3 +159,29 @@ def test_antialias_zero_and_empty_scene(rt, orc):
     assert (got["ids"] == -1).all() and got["bgr"][0, :15].tolist() == [188, 118, 64] * 5 and got["bgr"][0, 15] == 0
     z = emu.render(emu.Scene(desc), antialias=0)
     assert (z["bgr"][:, :15] == 255).all()
+
+
+@pytest.mark.parametrize("accel", ["linear", "bvh"])
+def test_far_origins_advance_to_the_scene(rt, orc, scenes, accel):
+    """rays that start 1e3 .. 1e9 units away (ground-plane hits near the horizon): the BVH filter advances them to the
+    sphere bounds first; results must still be the scan's, bit for bit, including the scan's own rounding artefacts"""
+    desc = scenes.random_spheres(600, 21, 15.0, 8, 8)
+    rng = np.random.default_rng(4)
+    n = 6000
+    target = np.stack([rng.uniform(-15, 15, n), rng.uniform(0.0, 6.0, n), rng.uniform(-15, 15, n)], 1)
+    dirs = rng.normal(size=(n, 3))
+    dirs /= np.linalg.norm(dirs, axis=1, keepdims=True)
+    dist = 10.0 ** rng.uniform(3, 9, n)
+    o = target - dirs * dist[:, None]
+    o[:, 1] = np.abs(o[:, 1])                       # keep the origins above the ground plane
+    d = target - o
+    d[: n // 2] /= np.linalg.norm(d[: n // 2], axis=1, keepdims=True)   # half unit, half un-normalised (|d| up to 1e9)
+    away = np.concatenate([o[:500], -d[:500]], 1)   # pointing away from the scene: must miss everything but the plane
+    rays = np.concatenate([np.concatenate([o, d], 1), away])
+    ids, t, nrm = emu.trace_rays(emu.Scene(desc), rays, accel=rt.ACCEL_BVH if accel == "bvh" else rt.ACCEL_LINEAR)
+    rid, rt_, rn = orc.OracleScene(desc).trace_rays(rays)
+    assert np.array_equal(ids, rid) and np.array_equal(t, rt_) and np.array_equal(nrm, rn)
+    assert (rid[:n] > 0).mean() > 0.2               # a good share of them does hit spheres
+    r2 = np.where(rng.uniform(size=len(rays)) < 0.5, -1.0, (dist.max() * 2) ** 2)
+    occ = emu.shadow_rays(emu.Scene(desc), rays, r2, accel=rt.ACCEL_BVH if accel == "bvh" else rt.ACCEL_LINEAR)
+    assert np.array_equal(occ, rid >= 0)

@@ -90,6 +90,28 @@ def test_intersect_random_rays(gpu, orc, scenes, accel, fp_mode):
         assert np.allclose(t[ok], rt_[ok], rtol=1e-9, atol=0)
 
 
+@pytest.mark.parametrize("accel", ["linear", "bvh"])
+def test_intersect_far_origins(gpu, orc, scenes, accel):
+    """origins 1e3 .. 1e9 units out (horizon hits of the ground plane): the BVH advances the ray to the sphere bounds
+    before the f32 filter and must still return the scan's result bit for bit"""
+    desc = scenes.random_spheres(3000, 21, 30.0, 8, 8)
+    rng = np.random.default_rng(4)
+    n = 100_000
+    target = np.stack([rng.uniform(-30, 30, n), rng.uniform(0.0, 6.0, n), rng.uniform(-30, 30, n)], 1)
+    dirs = rng.normal(size=(n, 3))
+    dirs /= np.linalg.norm(dirs, axis=1, keepdims=True)
+    dist = 10.0 ** rng.uniform(3, 9, n)
+    o = target - dirs * dist[:, None]
+    o[:, 1] = np.abs(o[:, 1])
+    d = target - o
+    d[: n // 2] /= np.linalg.norm(d[: n // 2], axis=1, keepdims=True)
+    rays = np.concatenate([np.concatenate([o, d], 1), np.concatenate([o[:5000], -d[:5000]], 1)])
+    ids, t, nrm = gpu.raytrace.intersect(gpu.Scene(desc), rays, accel=gpu.ACCEL_BVH if accel == "bvh" else gpu.ACCEL_LINEAR)
+    rid, rt_, rn = orc.OracleScene(desc).trace_rays(rays)
+    assert np.array_equal(ids, rid) and np.array_equal(t, rt_) and np.array_equal(nrm, rn)
+    assert (rid[:n] > 0).mean() > 0.2
+
+
 def test_intersect_edge_cases(gpu, orc):
     S = gpu.scene
     b = S.SceneBuilder()
