@@ -337,7 +337,7 @@ def run_e2e(R, steps):
     rt, torch, dist = R["rt"], R["torch"], R["dist"]
     world, rank = R["world"], R["rank"]
     h, bytewidth = R["h"], R["bytewidth"]
-    host = torch.empty(h * bytewidth, dtype=torch.uint8).pin_memory()
+    host = torch.empty(max(h * bytewidth, R["ctx"].framebuffer_ptr()[1]), dtype=torch.uint8).pin_memory()
     rays = 0
 
     def one():
@@ -357,8 +357,7 @@ def run_e2e(R, steps):
             if rank == 0:
                 host.copy_(R["final"])
         else:
-            rows, _, _ = ctx.download()
-            host.numpy()[:] = rows.reshape(-1)[: h * bytewidth]
+            ctx.download_rows_to(host.data_ptr())  # pinned host memory; local_rows == padded height at world 1
         torch.cuda.synchronize()
         ctx.close()
         return st["rays_total"]

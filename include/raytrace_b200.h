@@ -46,6 +46,9 @@ RT_API const char* rt_last_error(void);
 RT_API const char* rt_version(void);
 /* number of visible CUDA devices (0 when there is none; never an error) */
 RT_API int rt_device_count(void);
+/* Device blocks released by destroyed contexts are cached per device and reused by the next context (rt_render builds
+ * one per frame); this returns the cached blocks to the driver. */
+RT_API void rt_release_cached_memory(void);
 
 /* ---------------------------------------------------------------------------------------------------------
  * scene construction  (replaces the `pub` structs of src/scene.rs:32-212, src/shapes.rs:43-98)

@@ -25,7 +25,7 @@ from ._binding import (ACCEL_AUTO, ACCEL_BVH, ACCEL_LINEAR, FP_FAST, FP_STRICT, 
                        SyntaxError_)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libraytrace_b200.so")
+LIB_PATH = os.environ.get("RAYTRACE_B200_LIB") or os.path.join(_HERE, "lib", "libraytrace_b200.so")  # env: development builds only
 
 _lib = None
 
@@ -43,6 +43,11 @@ def lib():
 
 def device_count():
     return int(lib().rt_device_count())
+
+
+def release_cached_memory():
+    """Returns the device blocks cached from destroyed contexts to the driver (rt_release_cached_memory)."""
+    lib().rt_release_cached_memory()
 
 
 def version():
@@ -121,6 +126,10 @@ class Context:
         acc = np.zeros((self.local_rows, self.width, 3), dtype=np.float64) if want_accum else None
         B.check(self._lib, self._lib.rt_context_download(self._h, B.ptr(rows, C.c_uint8), B.ptr(ids, C.c_int32), B.ptr(acc, C.c_double)))
         return rows, ids, acc
+
+    def download_rows_to(self, host_ptr):
+        """Copies the local framebuffer (local_rows * bytewidth bytes) to caller-owned host memory (e.g. a pinned buffer)."""
+        B.check(self._lib, self._lib.rt_context_download(self._h, C.cast(C.c_void_p(host_ptr), C.POINTER(C.c_uint8)), None, None))
 
     def untile(self, gathered_ptr, out_ptr):
         B.check(self._lib, self._lib.rt_context_untile(self._h, C.c_void_p(gathered_ptr), C.c_void_p(out_ptr)))

@@ -63,6 +63,7 @@ API = {
     "rt_last_error": (C.c_char_p, []),
     "rt_version": (C.c_char_p, []),
     "rt_device_count": (C.c_int, []),
+    "rt_release_cached_memory": (None, []),
     "rt_scene_new": (C.c_void_p, []),
     "rt_scene_free": (None, [C.c_void_p]),
     "rt_scene_parse": (C.c_int, [C.c_char_p, C.c_size_t, C.POINTER(C.c_void_p), C.c_char_p, C.c_size_t]),

@@ -13,7 +13,10 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <map>
+#include <mutex>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "../../include/raytrace_b200.h"
@@ -33,11 +36,74 @@ using namespace rt;
 
 namespace {
 
+// Process-wide cache of device allocations.  The one-call entry point rt_render builds a context per frame (upload, BVH,
+// ray queues of several GB); paying cudaMalloc/cudaFree for those every frame costs more than the trace itself, so blocks
+// released by a context are kept (per device, by size) and handed to the next one.  rt_release_cached_memory() returns
+// them to the driver.
+class DeviceCache {
+public:
+    cudaError_t alloc(void** p, size_t bytes) {
+        *p = nullptr;
+        int dev = 0;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e != cudaSuccess) return e;
+        const size_t sz = (bytes + kGranule - 1) / kGranule * kGranule;
+        {
+            std::lock_guard<std::mutex> g(m_);
+            auto it = free_.find({dev, sz});
+            if (it != free_.end()) {
+                *p = it->second;
+                free_.erase(it);
+                cached_ -= sz;
+                live_[*p] = {dev, sz};
+                return cudaSuccess;
+            }
+        }
+        e = cudaMalloc(p, sz);
+        if (e != cudaSuccess) {  // out of memory with blocks parked in the cache: give them back and retry once
+            cudaGetLastError();
+            trim();
+            e = cudaMalloc(p, sz);
+            if (e != cudaSuccess) return e;
+        }
+        std::lock_guard<std::mutex> g(m_);
+        live_[*p] = {dev, sz};
+        return cudaSuccess;
+    }
+    void release(void* p) {
+        if (!p) return;
+        std::lock_guard<std::mutex> g(m_);
+        auto it = live_.find(p);
+        if (it == live_.end()) { cudaFree(p); return; }
+        free_.insert({{it->second.first, it->second.second}, p});
+        cached_ += it->second.second;
+        live_.erase(it);
+    }
+    void trim() {
+        std::lock_guard<std::mutex> g(m_);
+        int cur = 0;
+        cudaGetDevice(&cur);
+        for (auto& kv : free_) { cudaSetDevice(kv.first.first); cudaFree(kv.second); }
+        cudaSetDevice(cur);
+        free_.clear();
+        cached_ = 0;
+    }
+    size_t cached_bytes() { std::lock_guard<std::mutex> g(m_); return cached_; }
+
+private:
+    static constexpr size_t kGranule = 1u << 16;
+    std::mutex m_;
+    std::multimap<std::pair<int, size_t>, void*> free_;
+    std::unordered_map<void*, std::pair<int, size_t>> live_;
+    size_t cached_ = 0;
+};
+DeviceCache g_cache;
+
 template <typename T>
 int dev_alloc(T** p, size_t count) {
     *p = nullptr;
     if (count == 0) return RT_OK;
-    CUDA_TRY(cudaMalloc((void**)p, count * sizeof(T)));
+    CUDA_TRY(g_cache.alloc((void**)p, count * sizeof(T)));
     return RT_OK;
 }
 template <typename T>
@@ -59,7 +125,7 @@ struct DeviceSceneHolder {
 
     ~DeviceSceneHolder() { release(); }
     void release() {
-        for (void* p : allocs) cudaFree(p);
+        for (void* p : allocs) g_cache.release(p);
         allocs.clear();
         bvh_free(&bvh);
     }
@@ -125,7 +191,7 @@ int alloc_ray_queue(RayQueue* q, uint32_t cap, std::vector<void*>* allocs, bool 
     const size_t n_d = full ? 11 : 7;  // doubles per ray: o, d, (T, sig), hit_t
     const size_t bytes = c * (n_d * 8 + (full ? 8 + 4 + 4 : 0) + 4);
     unsigned char* base = nullptr;
-    CUDA_TRY(cudaMalloc((void**)&base, bytes));
+    CUDA_TRY(g_cache.alloc((void**)&base, bytes));
     allocs->push_back(base);
     double* d = (double*)base;
     q->ox = d; q->oy = d + c; q->oz = d + 2 * c; q->dx = d + 3 * c; q->dy = d + 4 * c; q->dz = d + 5 * c;
@@ -148,7 +214,7 @@ int alloc_shadow_queue(ShadowQueue* q, uint32_t cap, std::vector<void*>* allocs)
     if (cap == 0) return RT_OK;
     const size_t c = cap;
     unsigned char* base = nullptr;
-    CUDA_TRY(cudaMalloc((void**)&base, c * (10 * 8 + 4)));
+    CUDA_TRY(g_cache.alloc((void**)&base, c * (10 * 8 + 4)));
     allocs->push_back(base);
     double* d = (double*)base;
     q->ox = d; q->oy = d + c; q->oz = d + 2 * c; q->dx = d + 3 * c; q->dy = d + 4 * c; q->dz = d + 5 * c;
@@ -202,7 +268,8 @@ struct rt_context {
 
     ~rt_context() {
         cudaSetDevice(device);
-        for (void* p : allocs) cudaFree(p);
+        if (stream) cudaStreamSynchronize(stream);  // blocks go back to the cache: nothing may still be using them
+        for (void* p : allocs) g_cache.release(p);
         if (counters_host) cudaFreeHost(counters_host);
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
@@ -261,6 +328,8 @@ int process_level(rt_context* c, uint32_t d, uint32_t n) {
 }  // namespace
 
 extern "C" {
+
+void rt_release_cached_memory(void) { g_cache.trim(); }
 
 int rt_device_count(void) {
     int n = 0;
@@ -511,8 +580,8 @@ int rt_trace_rays(const rt_scene* s, const rt_render_opts* o, uint64_t n, const 
             if (e == cudaSuccess) e = cudaGetLastError();
             if (e != cudaSuccess) { set_error(std::string("rt_trace_rays: ") + cudaGetErrorString(e)); rc = RT_ERR_CUDA; }
         }
-        for (void* p : allocs) cudaFree(p);
-        cudaFree(d_t); cudaFree(d_n); cudaFree(cursor);
+        for (void* p : allocs) g_cache.release(p);
+        g_cache.release(d_t); g_cache.release(d_n); g_cache.release(cursor);
     }
     cudaStreamDestroy(st);
     return rc;

@@ -242,7 +242,13 @@ __device__ __forceinline__ uint32_t warp_fetch(unsigned idle_mask, uint32_t* cur
     return base + (uint32_t)__popc(idle_mask & ((1u << lane) - 1u));
 }
 
-constexpr int FETCH_MIN_IDLE = 8;  // refill when at least this many lanes of the warp have finished their ray
+#ifndef RT_FETCH_MIN_IDLE
+#define RT_FETCH_MIN_IDLE 8
+#endif
+#ifndef RT_DESCEND_STEPS
+#define RT_DESCEND_STEPS 16  // walk at most this many nodes before looking at the warp again (sweep: profiles/r01_v5_sweep.md)
+#endif
+constexpr int FETCH_MIN_IDLE = RT_FETCH_MIN_IDLE;  // refill when at least this many lanes of the warp have finished their ray
 
 // Persistent "while-while" traversal.  Each lane owns one ray at a time; the warp alternates between
 //   phase 1  every lane walks internal nodes (f32 box filter) until its next job is a leaf test or it is done,
@@ -286,14 +292,14 @@ __global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_consta
             if (exhausted) break;
             continue;
         }
-        if (active) cur = trav_descend(sc, br, cur, bound, st, tc);
+        if (active) cur = trav_descend(sc, br, cur, bound, st, tc, RT_DESCEND_STEPS);
         __syncwarp();
         if (active) {
             if (cur == TRAV_EMPTY) {
                 q.hit_id[ray] = closest_id(best);
                 q.hit_t[ray] = best.t;
                 active = false;
-            } else {
+            } else if (cur < 0) {
                 leaf_closest(sc, r, ~cur, best, tc);
                 bound = closest_bound32(best.t, br.t0);
                 cur = trav_pop(st, bound);
@@ -342,10 +348,10 @@ __global__ void __launch_bounds__(BVH_THREADS) k_shadow_bvh(const __grid_constan
             if (exhausted) break;
             continue;
         }
-        if (active) cur = trav_descend(sc, br, cur, bound, st, tc);
+        if (active) cur = trav_descend(sc, br, cur, bound, st, tc, RT_DESCEND_STEPS);
         __syncwarp();
         if (active) {
-            if (cur != TRAV_EMPTY) {
+            if (cur != TRAV_EMPTY && cur < 0) {
                 if (leaf_shadow(sc, r, ~cur, range2, tc)) { occluded = true; cur = TRAV_EMPTY; }
                 else cur = trav_pop(st, bound);
             }

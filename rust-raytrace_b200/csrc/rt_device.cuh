@@ -353,8 +353,10 @@ RT_HD int32_t trav_pop(TravStack& st, float bound) {
 // Walk internal nodes from `cur` (near child first, far child pushed) until the next thing to do is a leaf test
 // (returns ~slot < 0) or nothing is left (TRAV_EMPTY).  Leaves are NOT tested here: postponing them keeps the lanes
 // of a warp in the same code (box tests together, sphere tests together).
-RT_HD int32_t trav_descend(const DeviceScene& sc, const BoxRay32& br, int32_t cur, float bound, TravStack& st, TraverseCount& tc) {
-    while (cur >= 0) {
+// `max_steps` bounds the walk (the kernels come back to refill finished lanes; an unfinished walk returns cur >= 0).
+RT_HD int32_t trav_descend(const DeviceScene& sc, const BoxRay32& br, int32_t cur, float bound, TravStack& st, TraverseCount& tc,
+                           int max_steps = 0x7FFFFFFF) {
+    while (cur >= 0 && max_steps-- > 0) {
         const BvhNode n = load_node(sc.bvh_nodes + cur);
         tc.nodes++;
         const float t0 = box_entry32(br, n.lo0, n.hi0, bound);

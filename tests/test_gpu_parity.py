@@ -271,3 +271,59 @@ def test_config2_cornell_4k_1spp(gpu, orc):
     fr = gpu.raytrace.render(gpu.serialize.deserialize(REF_TEXT_SCENE), **kw)
     same = assert_parity(fr, ref, "config2")
     print("config2: identical bytes %.6f, rays %d, %.2f ms" % (same, fr.stats["rays_total"], fr.stats["render_ms"]))
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# BASELINE.json configurations at full size.  The CPU oracle is O(rays x objects), so full frames are checked against
+# the GPU's own f64 brute-force scan and a seed-determined sparse pixel set against the oracle.
+# ---------------------------------------------------------------------------------------------------------------------
+def _sparse_check(frame, osc, n_pixels, what, **kw):
+    h, w = frame.ids.shape
+    px = np.random.default_rng(2026).choice(w * h, size=n_pixels, replace=False).astype(np.uint32)
+    ref = osc.render_pixels(px, width=w, height=h, **kw)
+    ys, xs = px // w, px % w
+    assert np.array_equal(frame.ids[ys, xs], ref["ids"]), "%s: primary ids differ on the sparse pixel set" % what
+    diff = np.abs(frame.bgr[ys, xs].astype(np.int16) - ref["bgr"].astype(np.int16))
+    assert diff.max() <= 1, "%s: %d LSB" % (what, int(diff.max()))
+    same = float((diff == 0).mean())
+    assert same >= 0.999, "%s: %.5f identical" % (what, same)
+    return same
+
+
+def test_config3_spheres10k_4k_depth8(gpu, orc, scenes):
+    desc = scenes.spheres_10k()
+    sc = gpu.Scene(desc)
+    kw = dict(max_depth=8, seed=3)
+    bvh = gpu.raytrace.render(sc, accel=gpu.ACCEL_BVH, **kw)
+    lin = gpu.raytrace.render(sc, accel=gpu.ACCEL_LINEAR, **kw)            # ~1.6 s of f64 brute force: the full-frame oracle
+    assert np.array_equal(bvh.ids, lin.ids), "BVH and scan disagree on %d primary ids" % int((bvh.ids != lin.ids).sum())
+    assert bvh.stats["rays_total"] == lin.stats["rays_total"] and bvh.stats["rays_shadow"] == lin.stats["rays_shadow"]
+    assert (bvh.rows != lin.rows).mean() < 1e-5                            # identical rays; only the atomic accumulation order differs
+    same = _sparse_check(bvh, orc.OracleScene(desc), 4096, "config3", antialias=1, **kw)
+    print("config3: %d rays, bvh %.2f ms, scan %.1f ms, sparse identical %.5f" % (bvh.stats["rays_total"], bvh.stats["render_ms"], lin.stats["render_ms"], same))
+
+
+def test_config4_spheres1m_4k_depth8(gpu, orc, scenes):
+    """1M spheres through the device BVH (4K here; bench.py runs the 8K frame): all 8.3 M primary ids against the f64
+    brute-force scan, and final pixels of a sparse set against the CPU oracle"""
+    desc = scenes.spheres_1m(3840, 2160)
+    sc = gpu.Scene(desc)
+    kw = dict(max_depth=8, seed=4)
+    bvh = gpu.raytrace.render(sc, accel=gpu.ACCEL_BVH, **kw)
+    # (almost) primary rays only through the scan: max_depth 0 and an unreachable significance threshold leave only the
+    # refraction children of transparent hits (upstream spawns those without a significance test, src/raytrace.rs:214-223)
+    prim = gpu.raytrace.render(sc, accel=gpu.ACCEL_LINEAR, max_depth=0, min_significance=1e30, seed=4)
+    assert prim.stats["rays_primary"] == 3840 * 2160 and prim.stats["rays_shadow"] == 0
+    assert prim.stats["rays_secondary"] < 0.1 * prim.stats["rays_primary"]
+    assert np.array_equal(bvh.ids, prim.ids), "BVH and scan disagree on %d primary ids" % int((bvh.ids != prim.ids).sum())
+    same = _sparse_check(bvh, orc.OracleScene(desc), 1024, "config4", antialias=1, **kw)
+    print("config4@4K: %d rays, bvh %.1f ms (build %.1f ms, %d nodes), primary scan %.0f ms, sparse identical %.5f" % (
+        bvh.stats["rays_total"], bvh.stats["render_ms"], bvh.stats["bvh_build_ms"], bvh.stats["n_bvh_nodes"], prim.stats["render_ms"], same))
+
+
+def test_config5_skybox100k_4k(gpu, orc, scenes):
+    """textured configuration (the skybox is the only texture path upstream), 4 spp here (bench.py runs 16 spp)"""
+    desc = scenes.skybox_100k(3840, 2160, antialias=4, face_size=256)
+    fr = gpu.raytrace.render(gpu.Scene(desc), max_depth=4, seed=5)
+    same = _sparse_check(fr, orc.OracleScene(desc), 2048, "config5", antialias=4, max_depth=4, seed=5)
+    print("config5@4spp: %d rays, %.1f ms, sparse identical %.5f" % (fr.stats["rays_total"], fr.stats["render_ms"], same))
