@@ -151,6 +151,9 @@ typedef struct rt_stats {
      * (one CUDA event pair per launch).  Order: primary, closest, shade, shadow, resolve. */
     double class_ms[5];
     uint64_t class_launches[5];
+    /* rays the BVH traversal handed to the block-wide exact scan (runaway walks of rays that start 10^7+ units out):
+     * [0] closest-hit, [1] shadow */
+    uint64_t heavy_rays[2];
 } rt_stats;
 
 /* One-call frame render: upload, (build BVH), trace, resolve, copy back.

@@ -25,12 +25,13 @@ class Stats(C.Structure):
                 ("paths", C.c_uint64), ("kernel_launches", C.c_uint64), ("render_ms", C.c_double), ("bvh_build_ms", C.c_double),
                 ("n_bvh_nodes", C.c_uint64), ("local_rows", C.c_uint32), ("bytewidth", C.c_uint32), ("accel_used", C.c_int32),
                 ("fp_mode_used", C.c_int32), ("bvh_nodes_visited", C.c_uint64 * 2), ("bvh_prims_tested", C.c_uint64 * 2),
-                ("class_ms", C.c_double * 5), ("class_launches", C.c_uint64 * 5)]
+                ("class_ms", C.c_double * 5), ("class_launches", C.c_uint64 * 5), ("heavy_rays", C.c_uint64 * 2)]
 
     CLASSES = ("primary", "closest", "shade", "shadow", "resolve")
 
     def as_dict(self):
-        d = {k: getattr(self, k) for k, _ in self._fields_ if not k.startswith(("class_", "bvh_nodes_", "bvh_prims_"))}
+        d = {k: getattr(self, k) for k, _ in self._fields_ if not k.startswith(("class_", "bvh_nodes_", "bvh_prims_", "heavy_"))}
+        d["heavy_rays"] = {"closest": int(self.heavy_rays[0]), "shadow": int(self.heavy_rays[1])}
         d["bvh_nodes_visited"] = {"closest": int(self.bvh_nodes_visited[0]), "shadow": int(self.bvh_nodes_visited[1])}
         d["bvh_prims_tested"] = {"closest": int(self.bvh_prims_tested[0]), "shadow": int(self.bvh_prims_tested[1])}
         d["class_ms"] = dict(zip(self.CLASSES, [float(x) for x in self.class_ms]))

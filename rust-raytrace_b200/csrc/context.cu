@@ -139,6 +139,8 @@ struct DeviceSceneHolder {
         return RT_OK;
     }
 
+    uint32_t* heavy = nullptr;  // list of rays handed from the BVH traversal to the block-wide scan (kernels.h HEAVY_CAP)
+
     int init(const rt_scene* s, int accel, cudaStream_t st) {
         FlatScene f;
         int rc = flatten_scene(s, &f);
@@ -177,6 +179,8 @@ struct DeviceSceneHolder {
             bvh_ms = ms;
             cudaEventDestroy(e0); cudaEventDestroy(e1);
             ds.bvh_nodes = bvh.nodes; ds.bvh_sph = bvh.sph; ds.bvh_obj = bvh.obj; ds.n_bvh_nodes = bvh.n_nodes;
+            if ((rc = dev_alloc(&heavy, HEAVY_CAP)) != RT_OK) return rc;
+            allocs.push_back(heavy);
             build_launches = bvh.launches;
         }
         return RT_OK;
@@ -296,7 +300,7 @@ int process_level(rt_context* c, uint32_t d, uint32_t n) {
     for (uint32_t first = 0; first < n; first += c->slice) {
         const uint32_t cnt = std::min(c->slice, n - first);
         c->prof_begin(1);
-        c->k->closest(c->stream, c->scene.ds, c->scene.use_bvh, in, first, cnt, c->counters, c->sm_count);
+        c->k->closest(c->stream, c->scene.ds, c->scene.use_bvh, in, first, cnt, c->counters, c->sm_count, c->scene.heavy);
         c->prof_end();
         CUDA_TRY(cudaMemsetAsync(next_count, 0, sizeof(uint32_t), c->stream));
         CUDA_TRY(cudaMemsetAsync(&c->counters->shadow_count, 0, sizeof(uint32_t), c->stream));
@@ -304,7 +308,7 @@ int process_level(rt_context* c, uint32_t d, uint32_t n) {
         c->k->shade(c->stream, c->scene.ds, c->fp, in, first, cnt, out, next_count, c->shadowq, &c->counters->shadow_count, &c->counters->overflow,
                     c->accum, c->ids);
         c->prof_end();
-        c->stats.kernel_launches += 2;
+        c->stats.kernel_launches += c->scene.use_bvh ? 3 : 2;  // closest (+ heavy scan), shade
         int rc = ctx_fetch_counters(c);
         if (rc != RT_OK) return rc;
         const uint32_t n_shadow = c->counters_host->shadow_count;
@@ -313,9 +317,9 @@ int process_level(rt_context* c, uint32_t d, uint32_t n) {
         c->stats.rays_shadow += n_shadow;
         if (n_shadow) {
             c->prof_begin(3);
-            c->k->shadow(c->stream, c->scene.ds, c->scene.use_bvh, c->shadowq, n_shadow, c->accum, c->counters, c->sm_count);
+            c->k->shadow(c->stream, c->scene.ds, c->scene.use_bvh, c->shadowq, n_shadow, c->accum, c->counters, c->sm_count, c->scene.heavy);
             c->prof_end();
-            c->stats.kernel_launches += 1;
+            c->stats.kernel_launches += c->scene.use_bvh ? 2 : 1;  // shadow (+ heavy scan)
         }
         if (n_next) {
             rc = process_level(c, d + 1, n_next);
@@ -440,6 +444,7 @@ int rt_context_render(rt_context* c, rt_stats* stats) {
     for (int k = 0; k < 2; k++) {
         c->stats.bvh_nodes_visited[k] = c->counters_host->bvh_nodes[k];
         c->stats.bvh_prims_tested[k] = c->counters_host->bvh_prims[k];
+        c->stats.heavy_rays[k] = c->counters_host->heavy_rays[k];
     }
     for (int k = 0; k < 5; k++) { c->stats.class_ms[k] = 0.0; c->stats.class_launches[k] = 0; }
     for (size_t i = 0; i < c->prof_class.size(); i++) {
@@ -570,7 +575,7 @@ int rt_trace_rays(const rt_scene* s, const rt_render_opts* o, uint64_t n, const 
             if (e == cudaSuccess) e = cudaStreamSynchronize(st);
             const KernelTable* k = o->fp_mode == RT_FP_FAST ? kernels_fast() : kernels_strict();
             if (e == cudaSuccess) {
-                k->closest(st, holder.ds, holder.use_bvh, q, 0, (uint32_t)n, cursor, sm_count);
+                k->closest(st, holder.ds, holder.use_bvh, q, 0, (uint32_t)n, cursor, sm_count, holder.heavy);
                 k->hit_normals(st, holder.ds, q, (uint32_t)n, d_t, d_n);
                 e = cudaMemcpyAsync(ids, q.hit_id, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, st);
             }

@@ -255,8 +255,10 @@ constexpr int FETCH_MIN_IDLE = RT_FETCH_MIN_IDLE;  // refill when at least this 
 //   phase 2  every lane with a pending leaf runs the exact f64 sphere test,
 // and lanes whose ray has finished are refilled from the global cursor instead of idling until the slowest lane of
 // a fixed 32-ray batch is done.
-__global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_constant__ DeviceScene sc, RayQueue q, uint32_t first, uint32_t n, Counters* counters) {
+__global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_constant__ DeviceScene sc, RayQueue q, uint32_t first, uint32_t n, Counters* counters,
+                                                             uint32_t* heavy, uint32_t heavy_walks) {
     uint32_t* cursor = &counters->cursor;
+    uint32_t walks = 0;  // bounded walks spent on the current ray
     TraverseCount tc; tc.nodes = 0; tc.prims = 0;
     TravStack st; st.sp = 0;
     RayQ r; BoxRay32 br; Closest best;
@@ -276,6 +278,7 @@ __global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_consta
                     r = make_rayq(v3(q.ox[ray], q.oy[ray], q.oz[ray]), v3(q.dx[ray], q.dy[ray], q.dz[ray]));
                     best = closest_none();
                     planes_closest(sc, r, best);
+                    walks = 0;
                     st.sp = 0;
                     cur = TRAV_EMPTY;
                     if (!best.nan && sc.n_spheres > 0) {
@@ -304,13 +307,21 @@ __global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_consta
                 bound = closest_bound32(best.t, br.t0);
                 cur = trav_pop(st, bound);
             }
+            if (active && ++walks > heavy_walks) {
+                // runaway traversal: hand the ray to the block-wide scan (k_heavy_scan), which redoes it from scratch
+                const uint32_t slot = atomicAdd(&counters->heavy_count, 1u);
+                if (slot < HEAVY_CAP) { heavy[slot] = ray; active = false; }
+                else walks = 0;  // list full: keep traversing
+            }
         }
     }
     flush_traverse_count(tc, counters, 0);
 }
 
-__global__ void __launch_bounds__(BVH_THREADS) k_shadow_bvh(const __grid_constant__ DeviceScene sc, ShadowQueue sq, uint32_t n, double* accum, Counters* counters) {
+__global__ void __launch_bounds__(BVH_THREADS) k_shadow_bvh(const __grid_constant__ DeviceScene sc, ShadowQueue sq, uint32_t n, double* accum, Counters* counters,
+                                                            uint32_t* heavy, uint32_t heavy_walks) {
     uint32_t* cursor = &counters->cursor;
+    uint32_t walks = 0;
     TraverseCount tc; tc.nodes = 0; tc.prims = 0;
     TravStack st; st.sp = 0;
     RayQ r; BoxRay32 br;
@@ -332,6 +343,7 @@ __global__ void __launch_bounds__(BVH_THREADS) k_shadow_bvh(const __grid_constan
                     range2 = sq.r2[ray];
                     Shadow s; s.nan = false; s.any = false;
                     planes_shadow(sc, r, range2, s);
+                    walks = 0;
                     st.sp = 0;
                     cur = TRAV_EMPTY;
                     occluded = shadow_result(s, range2);
@@ -358,10 +370,92 @@ __global__ void __launch_bounds__(BVH_THREADS) k_shadow_bvh(const __grid_constan
             if (cur == TRAV_EMPTY) {
                 if (!occluded) accum_add(accum, sq.pixel[ray], c3(sq.cr[ray], sq.cg[ray], sq.cb[ray]));
                 active = false;
+            } else if (++walks > heavy_walks) {
+                const uint32_t slot = atomicAdd(&counters->heavy_count, 1u);
+                if (slot < HEAVY_CAP) { heavy[slot] = ray; active = false; }
+                else walks = 0;
             }
         }
     }
     flush_traverse_count(tc, counters, 1);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// k_heavy_scan: the rays a traversal kernel gave up on, one CTA per ray.  A ray that starts 10^7+ units from the scene
+// (a ground-plane hit near the horizon) makes the exact test's own rounding error large, so the conservative filter must
+// pad every box by many units and the walk touches a large part of the tree: milliseconds in ONE lane.  Here the 256
+// threads of a CTA stride over the sphere buffer with the scan's exact test and merge -- the same answer as the scan by
+// construction, in microseconds.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int HEAVY_THREADS = 256;
+
+__device__ __forceinline__ bool closest_before(const Closest& a, const Closest& b) {  // ordering of closest_update
+    if (a.nan != b.nan) return a.nan;
+    if (a.nan) return a.obj < b.obj;
+    return a.t < b.t || (a.t == b.t && a.obj < b.obj);
+}
+
+template <bool SHADOW>
+__global__ void __launch_bounds__(HEAVY_THREADS) k_heavy_scan(const __grid_constant__ DeviceScene sc, RayQueue q, ShadowQueue sq, uint32_t first,
+                                                              double* accum, Counters* counters, const uint32_t* heavy) {
+    __shared__ double s_t[HEAVY_THREADS / 32];
+    __shared__ int32_t s_obj[HEAVY_THREADS / 32];
+    __shared__ int s_nan[HEAVY_THREADS / 32];
+    const uint32_t count = counters->heavy_count < HEAVY_CAP ? counters->heavy_count : HEAVY_CAP;
+    for (uint32_t e = blockIdx.x; e < count; e += gridDim.x) {
+        const uint32_t ray = heavy[e];
+        const uint32_t i = ray;  // closest: already the absolute queue index (first + local)
+        const V3 o = SHADOW ? v3(sq.ox[i], sq.oy[i], sq.oz[i]) : v3(q.ox[i], q.oy[i], q.oz[i]);
+        const V3 d = SHADOW ? v3(sq.dx[i], sq.dy[i], sq.dz[i]) : v3(q.dx[i], q.dy[i], q.dz[i]);
+        const RayQ r = make_rayq(o, d);
+        if (SHADOW) {
+            const double range2 = sq.r2[i];
+            Shadow s; s.nan = false; s.any = false;
+            planes_shadow(sc, r, range2, s);
+            bool any = false;
+            if (!s.nan && !s.any)
+                for (uint32_t k = threadIdx.x; k < sc.n_spheres && !any; k += HEAVY_THREADS) {
+                    const double2 c01 = *reinterpret_cast<const double2*>(&sc.sph[k].cx), c23 = *reinterpret_cast<const double2*>(&sc.sph[k].cz);
+                    double th;
+                    if (sphere_hit(r, c01.x, c01.y, c23.x, c23.y, th) && shadow_hit_counts(th, range2)) any = true;
+                }
+            const int occluded_by_sphere = __syncthreads_or(any ? 1 : 0);
+            if (threadIdx.x == 0) {
+                s.any = s.any || occluded_by_sphere != 0;
+                if (!shadow_result(s, range2)) accum_add(accum, sq.pixel[i], c3(sq.cr[i], sq.cg[i], sq.cb[i]));
+                atomicAdd(&counters->heavy_rays[1], 1ull);
+            }
+        } else {
+            Closest best = closest_none();
+            if (threadIdx.x == 0) planes_closest(sc, r, best);
+            // a NaN plane hit wins whatever the spheres say (src/scene.rs:227-233); spheres never produce NaN
+            for (uint32_t k = threadIdx.x; k < sc.n_spheres; k += HEAVY_THREADS) {
+                const double2 c01 = *reinterpret_cast<const double2*>(&sc.sph[k].cx), c23 = *reinterpret_cast<const double2*>(&sc.sph[k].cz);
+                double th;
+                if (sphere_hit(r, c01.x, c01.y, c23.x, c23.y, th)) closest_update(best, th, __ldg(sc.sph_obj + k));
+            }
+#pragma unroll
+            for (int x = 16; x > 0; x >>= 1) {
+                Closest other;
+                other.t = __shfl_xor_sync(0xFFFFFFFFu, best.t, x);
+                other.obj = __shfl_xor_sync(0xFFFFFFFFu, best.obj, x);
+                other.nan = __shfl_xor_sync(0xFFFFFFFFu, best.nan ? 1 : 0, x) != 0;
+                if (closest_before(other, best)) best = other;
+            }
+            if ((threadIdx.x & 31) == 0) { s_t[threadIdx.x >> 5] = best.t; s_obj[threadIdx.x >> 5] = best.obj; s_nan[threadIdx.x >> 5] = best.nan ? 1 : 0; }
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                for (int w = 1; w < HEAVY_THREADS / 32; w++) {
+                    Closest other; other.t = s_t[w]; other.obj = s_obj[w]; other.nan = s_nan[w] != 0;
+                    if (closest_before(other, best)) best = other;
+                }
+                q.hit_id[i] = closest_id(best);
+                q.hit_t[i] = best.t;
+                atomicAdd(&counters->heavy_rays[0], 1ull);
+            }
+            __syncthreads();
+        }
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -513,13 +607,23 @@ static void scan_attr_once() {
     }
 }
 
-static void l_closest(cudaStream_t st, const DeviceScene& sc, bool bvh, RayQueue q, uint32_t first, uint32_t n, Counters* counters, int sm_count) {
+// a traversal that has looked at the warp this many times (16 nodes or one leaf each) is handed to k_heavy_scan:
+// about the point where a CTA-wide scan of the whole sphere buffer is the cheaper way to finish the ray
+static uint32_t heavy_walks(const DeviceScene& sc) {
+    const uint32_t w = sc.n_spheres / 256u;
+    return w < 256u ? 256u : (w > 8192u ? 8192u : w);
+}
+
+static void l_closest(cudaStream_t st, const DeviceScene& sc, bool bvh, RayQueue q, uint32_t first, uint32_t n, Counters* counters, int sm_count,
+                      uint32_t* heavy) {
     if (!n) return;
     if (bvh) {
-        cudaMemsetAsync(&counters->cursor, 0, sizeof(uint32_t), st);
+        cudaMemsetAsync(&counters->cursor, 0, 2 * sizeof(uint32_t), st);  // cursor + heavy_count
         uint32_t want = div_up(n, BVH_THREADS);
         uint32_t grid = (uint32_t)sm_count * 8u;  // 8 resident CTAs of 128 threads per SM
-        k_closest_bvh<<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, q, first, n, counters);
+        k_closest_bvh<<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, q, first, n, counters, heavy, heavy_walks(sc));
+        ShadowQueue none{};
+        k_heavy_scan<false><<<(uint32_t)sm_count * 4u, HEAVY_THREADS, 0, st>>>(sc, q, none, first, nullptr, counters, heavy);
     } else {
         scan_attr_once();
         k_closest_scan<<<div_up(n, SCAN_THREADS), SCAN_THREADS, sizeof(ScanSmem), st>>>(sc, q, first, n);
@@ -532,13 +636,16 @@ static void l_shade(cudaStream_t st, const DeviceScene& sc, const FrameParams& f
     k_shade<<<div_up(n, SHADE_THREADS), SHADE_THREADS, 0, st>>>(sc, fp, in, first, n, out, out_count, sq, sq_count, overflow, accum, ids);
 }
 
-static void l_shadow(cudaStream_t st, const DeviceScene& sc, bool bvh, ShadowQueue sq, uint32_t n, double* accum, Counters* counters, int sm_count) {
+static void l_shadow(cudaStream_t st, const DeviceScene& sc, bool bvh, ShadowQueue sq, uint32_t n, double* accum, Counters* counters, int sm_count,
+                     uint32_t* heavy) {
     if (!n) return;
     if (bvh) {
-        cudaMemsetAsync(&counters->cursor, 0, sizeof(uint32_t), st);
+        cudaMemsetAsync(&counters->cursor, 0, 2 * sizeof(uint32_t), st);
         uint32_t want = div_up(n, BVH_THREADS);
         uint32_t grid = (uint32_t)sm_count * 8u;
-        k_shadow_bvh<<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters);
+        k_shadow_bvh<<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters, heavy, heavy_walks(sc));
+        RayQueue none{};
+        k_heavy_scan<true><<<(uint32_t)sm_count * 4u, HEAVY_THREADS, 0, st>>>(sc, none, sq, 0u, accum, counters, heavy);
     } else {
         scan_attr_once();
         k_shadow_scan<<<div_up(n, SCAN_THREADS), SCAN_THREADS, sizeof(ScanSmem), st>>>(sc, sq, n, accum);

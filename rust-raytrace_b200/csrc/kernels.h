@@ -12,23 +12,29 @@ struct Counters {
     uint32_t overflow;      // a queue append was dropped (host sizing bug) -> render fails loudly
     uint32_t shadow_count;  // shadow queue length
     uint32_t cursor;        // persistent-thread work cursor (reset before each persistent launch)
-    uint32_t _pad;
+    uint32_t heavy_count;   // rays the traversal kernel handed to the block-wide scan (reset with the cursor)
     unsigned long long bvh_nodes[2];  // 64-byte BVH nodes fetched: [0] closest-hit kernel, [1] shadow kernel (whole render)
     unsigned long long bvh_prims[2];  // exact sphere tests done at BVH leaves
     uint32_t level_count[64];  // ray-queue length per wavefront level
+    unsigned long long heavy_rays[2];  // rays finished by the block-wide scan (whole render): [0] closest, [1] shadow
 };
+constexpr uint32_t HEAVY_CAP = 1u << 16;  // entries of the heavy-ray list (rays beyond it simply keep traversing)
 
 struct KernelTable {
     // camera.rs primary-ray generation: paths [path_base, path_base + n_paths) -> level-0 queue
     void (*primary)(cudaStream_t, const DeviceScene&, const FrameParams&, RayQueue q, uint32_t* q_count, uint32_t* overflow, uint64_t path_base,
                     uint32_t n_paths);
     // Scene::intersect for rays [first, first+n) of q; fills hit_id / hit_t
-    void (*closest)(cudaStream_t, const DeviceScene&, bool bvh, RayQueue q, uint32_t first, uint32_t n, Counters* counters, int sm_count);
+    // `heavy`: device scratch of HEAVY_CAP uint32 (BVH only): rays whose traversal runs away (huge filter padding for origins
+    // 10^7+ units out) are finished by a block-wide scan instead of holding one lane for milliseconds
+    void (*closest)(cudaStream_t, const DeviceScene&, bool bvh, RayQueue q, uint32_t first, uint32_t n, Counters* counters, int sm_count,
+                    uint32_t* heavy);
     // material evaluation: pixel accumulation, shadow-ray and child-ray emission with warp-aggregated appends
     void (*shade)(cudaStream_t, const DeviceScene&, const FrameParams&, RayQueue in, uint32_t first, uint32_t n, RayQueue out, uint32_t* out_count,
                   ShadowQueue sq, uint32_t* sq_count, uint32_t* overflow, double* accum, int32_t* ids);
     // shadow queries; unoccluded rays add their pending contribution to the pixel
-    void (*shadow)(cudaStream_t, const DeviceScene&, bool bvh, ShadowQueue sq, uint32_t n, double* accum, Counters* counters, int sm_count);
+    void (*shadow)(cudaStream_t, const DeviceScene&, bool bvh, ShadowQueue sq, uint32_t n, double* accum, Counters* counters, int sm_count,
+                   uint32_t* heavy);
     // average, quantise (threshold table) and pack BGR rows with padding; 128-bit stores
     void (*resolve)(cudaStream_t, const DeviceScene&, const FrameParams&, const double* accum, uint8_t* out, uint32_t bytewidth);
     // test hooks
