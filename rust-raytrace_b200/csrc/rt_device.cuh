@@ -321,14 +321,19 @@ RT_HD float box_entry32(const BoxRay32& b, const float* lo, const float* hi, flo
 }
 
 #if defined(__CUDA_ARCH__)
+// the 64-byte node in two 256-bit loads (sm_100 LDG.E.ENL2.256): a divergent node fetch costs the L1 data pipe one
+// wavefront per lane per load, so two loads instead of four halve the pipe's work
 RT_HD BvhNode load_node(const BvhNode* p) {
     BvhNode n;
-    const float4* q = reinterpret_cast<const float4*>(p);
-    float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), d = __ldg(q + 3);
-    n.lo0[0] = a.x; n.lo0[1] = a.y; n.lo0[2] = a.z; n.hi0[0] = a.w;
-    n.hi0[1] = b.x; n.hi0[2] = b.y; n.lo1[0] = b.z; n.lo1[1] = b.w;
-    n.lo1[2] = c.x; n.hi1[0] = c.y; n.hi1[1] = c.z; n.hi1[2] = c.w;
-    n.c0 = __float_as_int(d.x); n.c1 = __float_as_int(d.y);
+    float a0, a1, a2, a3, a4, a5, a6, a7, b0, b1, b2, b3, b4, b5, b6, b7;
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a0), "=f"(a1), "=f"(a2), "=f"(a3), "=f"(a4), "=f"(a5), "=f"(a6), "=f"(a7) : "l"(p));
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(b0), "=f"(b1), "=f"(b2), "=f"(b3), "=f"(b4), "=f"(b5), "=f"(b6), "=f"(b7) : "l"(reinterpret_cast<const char*>(p) + 32));
+    n.lo0[0] = a0; n.lo0[1] = a1; n.lo0[2] = a2; n.hi0[0] = a3;
+    n.hi0[1] = a4; n.hi0[2] = a5; n.lo1[0] = a6; n.lo1[1] = a7;
+    n.lo1[2] = b0; n.hi1[0] = b1; n.hi1[1] = b2; n.hi1[2] = b3;
+    n.c0 = __float_as_int(b4); n.c1 = __float_as_int(b5);
     return n;
 }
 #else
