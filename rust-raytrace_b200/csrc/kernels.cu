@@ -260,7 +260,7 @@ __global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_consta
     uint32_t* cursor = &counters->cursor;
     uint32_t walks = 0;  // bounded walks spent on the current ray
     TraverseCount tc; tc.nodes = 0; tc.prims = 0;
-    TravStack st; st.sp = 0;
+    TravStack st; int sp = 0;
     RayQ r; BoxRay32 br; Closest best;
     r = make_rayq(v3(0, 0, 0), v3(0, 0, 0)); best = closest_none();
     br.ix = br.iy = br.iz = br.px = br.py = br.pz = br.mx = br.my = br.mz = 0.0f; br.t0 = 0.0; br.enter = false;
@@ -279,7 +279,7 @@ __global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_consta
                     best = closest_none();
                     planes_closest(sc, r, best);
                     walks = 0;
-                    st.sp = 0;
+                    sp = 0;
                     cur = TRAV_EMPTY;
                     if (!best.nan && sc.n_spheres > 0) {
                         br = make_boxray32(sc, r.o, r.d);
@@ -295,7 +295,7 @@ __global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_consta
             if (exhausted) break;
             continue;
         }
-        if (active) cur = trav_descend(sc, br, cur, bound, st, tc, RT_DESCEND_STEPS);
+        if (active) cur = trav_descend(sc, br, cur, bound, st, sp, tc, RT_DESCEND_STEPS);
         __syncwarp();
         if (active) {
             if (cur == TRAV_EMPTY) {
@@ -305,7 +305,7 @@ __global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_consta
             } else if (cur < 0) {
                 leaf_closest(sc, r, ~cur, best, tc);
                 bound = closest_bound32(best.t, br.t0);
-                cur = trav_pop(st, bound);
+                cur = trav_pop(st, sp, bound);
             }
             if (active && ++walks > heavy_walks) {
                 // runaway traversal: hand the ray to the block-wide scan (k_heavy_scan), which redoes it from scratch
@@ -323,7 +323,7 @@ __global__ void __launch_bounds__(BVH_THREADS) k_shadow_bvh(const __grid_constan
     uint32_t* cursor = &counters->cursor;
     uint32_t walks = 0;
     TraverseCount tc; tc.nodes = 0; tc.prims = 0;
-    TravStack st; st.sp = 0;
+    TravStack st; int sp = 0;
     RayQ r; BoxRay32 br;
     r = make_rayq(v3(0, 0, 0), v3(0, 0, 0));
     br.ix = br.iy = br.iz = br.px = br.py = br.pz = br.mx = br.my = br.mz = 0.0f; br.t0 = 0.0; br.enter = false;
@@ -344,7 +344,7 @@ __global__ void __launch_bounds__(BVH_THREADS) k_shadow_bvh(const __grid_constan
                     Shadow s; s.nan = false; s.any = false;
                     planes_shadow(sc, r, range2, s);
                     walks = 0;
-                    st.sp = 0;
+                    sp = 0;
                     cur = TRAV_EMPTY;
                     occluded = shadow_result(s, range2);
                     if (!s.nan && !s.any && sc.n_spheres > 0) {
@@ -360,12 +360,12 @@ __global__ void __launch_bounds__(BVH_THREADS) k_shadow_bvh(const __grid_constan
             if (exhausted) break;
             continue;
         }
-        if (active) cur = trav_descend(sc, br, cur, bound, st, tc, RT_DESCEND_STEPS);
+        if (active) cur = trav_descend(sc, br, cur, bound, st, sp, tc, RT_DESCEND_STEPS);
         __syncwarp();
         if (active) {
             if (cur != TRAV_EMPTY && cur < 0) {
                 if (leaf_shadow(sc, r, ~cur, range2, tc)) { occluded = true; cur = TRAV_EMPTY; }
-                else cur = trav_pop(st, bound);
+                else cur = trav_pop(st, sp, bound);
             }
             if (cur == TRAV_EMPTY) {
                 if (!occluded) accum_add(accum, sq.pixel[ray], c3(sq.cr[ray], sq.cg[ray], sq.cb[ray]));

@@ -11,6 +11,7 @@
 #pragma once
 #include <math.h>
 #include <stdint.h>
+#include <string.h>
 
 #include "rt_types.h"
 
@@ -341,16 +342,25 @@ RT_HD BvhNode load_node(const BvhNode* p) { return *p; }
 #endif
 
 // traversal stack: internal nodes (>= 0) and leaves (~slot < 0) alike, each with its conservative entry distance
+// Postponed far children: (node, entry distance) packed in one 8-byte word so that a push is one store and a pop
+// one load.  The array is indexed dynamically and therefore lives in local memory; the depth `sp` is passed beside it
+// so that it stays in a register.
 struct TravStack {
-    int32_t node[BVH_STACK];
-    float t[BVH_STACK];
-    int sp;
+    unsigned long long e[BVH_STACK];
 };
+RT_HD unsigned long long trav_pack(int32_t node, float t) {
+    uint32_t tb;
+    memcpy(&tb, &t, 4);
+    return (unsigned long long)(uint32_t)node | ((unsigned long long)tb << 32);
+}
 
-RT_HD int32_t trav_pop(TravStack& st, float bound) {
-    while (st.sp > 0) {
-        --st.sp;
-        if (st.t[st.sp] <= bound) return st.node[st.sp];
+RT_HD int32_t trav_pop(const TravStack& st, int& sp, float bound) {
+    while (sp > 0) {
+        const unsigned long long e = st.e[--sp];
+        const uint32_t tb = (uint32_t)(e >> 32);
+        float t;
+        memcpy(&t, &tb, 4);
+        if (t <= bound) return (int32_t)(uint32_t)e;
     }
     return TRAV_EMPTY;
 }
@@ -359,7 +369,7 @@ RT_HD int32_t trav_pop(TravStack& st, float bound) {
 // (returns ~slot < 0) or nothing is left (TRAV_EMPTY).  Leaves are NOT tested here: postponing them keeps the lanes
 // of a warp in the same code (box tests together, sphere tests together).
 // `max_steps` bounds the walk (the kernels come back to refill finished lanes; an unfinished walk returns cur >= 0).
-RT_HD int32_t trav_descend(const DeviceScene& sc, const BoxRay32& br, int32_t cur, float bound, TravStack& st, TraverseCount& tc,
+RT_HD int32_t trav_descend(const DeviceScene& sc, const BoxRay32& br, int32_t cur, float bound, TravStack& st, int& sp, TraverseCount& tc,
                            int max_steps = 0x7FFFFFFF) {
     while (cur >= 0 && max_steps-- > 0) {
         const BvhNode n = load_node(sc.bvh_nodes + cur);
@@ -369,14 +379,14 @@ RT_HD int32_t trav_descend(const DeviceScene& sc, const BoxRay32& br, int32_t cu
         if (t0 >= 0.0f && t1 >= 0.0f) {
             const bool swap = t1 < t0;
             const int32_t farc = swap ? n.c0 : n.c1;
-            if (st.sp < BVH_STACK) { st.node[st.sp] = farc; st.t[st.sp] = swap ? t0 : t1; st.sp++; }
+            if (sp < BVH_STACK) st.e[sp++] = trav_pack(farc, swap ? t0 : t1);
             cur = swap ? n.c1 : n.c0;
         } else if (t0 >= 0.0f) {
             cur = n.c0;
         } else if (t1 >= 0.0f) {
             cur = n.c1;
         } else {
-            cur = trav_pop(st, bound);
+            cur = trav_pop(st, sp, bound);
         }
     }
     return cur;
@@ -413,15 +423,15 @@ RT_HD void closest_bvh(const DeviceScene& sc, const RayQ& r, int32_t& id, double
         const BoxRay32 br = make_boxray32(sc, r.o, r.d);
         if (br.enter) {
             TravStack st;
-            st.sp = 0;
+            int sp = 0;
             int32_t cur = 0;
             float bound = closest_bound32(best.t, br.t0);
             while (true) {
-                cur = trav_descend(sc, br, cur, bound, st, tc);
+                cur = trav_descend(sc, br, cur, bound, st, sp, tc);
                 if (cur == TRAV_EMPTY) break;
                 leaf_closest(sc, r, ~cur, best, tc);
                 bound = closest_bound32(best.t, br.t0);
-                cur = trav_pop(st, bound);
+                cur = trav_pop(st, sp, bound);
             }
         }
     }
@@ -435,14 +445,14 @@ RT_HD bool shadow_bvh(const DeviceScene& sc, const RayQ& r, double range2, Trave
         const BoxRay32 br = make_boxray32(sc, r.o, r.d);
         if (br.enter) {
             TravStack st;
-            st.sp = 0;
+            int sp = 0;
             int32_t cur = 0;
             const float bound = shadow_bound32(range2, br.t0);
             while (true) {
-                cur = trav_descend(sc, br, cur, bound, st, tc);
+                cur = trav_descend(sc, br, cur, bound, st, sp, tc);
                 if (cur == TRAV_EMPTY) break;
                 if (leaf_shadow(sc, r, ~cur, range2, tc)) { s.any = true; break; }
-                cur = trav_pop(st, bound);
+                cur = trav_pop(st, sp, bound);
             }
         }
     }
