@@ -154,6 +154,8 @@ typedef struct rt_stats {
     /* rays the BVH traversal handed to the block-wide exact scan (runaway walks of rays that start 10^7+ units out):
      * [0] closest-hit, [1] shadow */
     uint64_t heavy_rays[2];
+    /* bytes per BVH node in use: 32 (box planes on the scene's 16-bit grid), 64 (f32 planes; grid too coarse for the scene) or 0 */
+    uint64_t bvh_node_bytes;
 } rt_stats;
 
 /* One-call frame render: upload, (build BVH), trace, resolve, copy back.

@@ -25,7 +25,7 @@ class Stats(C.Structure):
                 ("paths", C.c_uint64), ("kernel_launches", C.c_uint64), ("render_ms", C.c_double), ("bvh_build_ms", C.c_double),
                 ("n_bvh_nodes", C.c_uint64), ("local_rows", C.c_uint32), ("bytewidth", C.c_uint32), ("accel_used", C.c_int32),
                 ("fp_mode_used", C.c_int32), ("bvh_nodes_visited", C.c_uint64 * 2), ("bvh_prims_tested", C.c_uint64 * 2),
-                ("class_ms", C.c_double * 5), ("class_launches", C.c_uint64 * 5), ("heavy_rays", C.c_uint64 * 2)]
+                ("class_ms", C.c_double * 5), ("class_launches", C.c_uint64 * 5), ("heavy_rays", C.c_uint64 * 2), ("bvh_node_bytes", C.c_uint64)]
 
     CLASSES = ("primary", "closest", "shade", "shadow", "resolve")
 

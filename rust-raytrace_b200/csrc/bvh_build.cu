@@ -156,6 +156,15 @@ __global__ void k_single_leaf(const SphereRec* sph, BvhNode* nodes) {
     nodes[0] = nd;
 }
 
+struct QuantGrid { double org[3], cell[3]; };
+__global__ void k_quantise(const BvhNode* nodes, uint32_t n_nodes, QuantGrid g, BvhQNode* out, uint32_t* off_grid) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_nodes) return;
+    bool ok = true;
+    out[i] = quantise_node(nodes[i], g.org, g.cell, ok);
+    if (!ok) atomicAdd(off_grid, 1u);
+}
+
 __global__ void k_untile(const uint32_t* gathered, uint32_t* out, uint32_t height, uint32_t words_per_row, uint32_t band_rows, uint32_t world,
                          uint32_t local_rows) {
     const uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -173,8 +182,8 @@ __global__ void k_untile(const uint32_t* gathered, uint32_t* out, uint32_t heigh
     } while (0)
 
 cudaError_t bvh_build(cudaStream_t st, const SphereRec* sph, const int32_t* sph_obj, uint32_t n, const double* clo, const double* chi,
-                      BvhBuildResult* out) {
-    out->nodes = nullptr; out->sph = nullptr; out->obj = nullptr; out->n_nodes = 0; out->launches = 0;
+                      const double* q_org, const double* q_cell, BvhBuildResult* out) {
+    out->nodes = nullptr; out->qnodes = nullptr; out->sph = nullptr; out->obj = nullptr; out->n_nodes = 0; out->launches = 0;
     uint64_t* keys = nullptr; uint32_t* idx = nullptr;
     int32_t *child0 = nullptr, *child1 = nullptr, *pint = nullptr, *pleaf = nullptr;
     uint32_t* flags = nullptr; Box* boxes = nullptr;
@@ -225,6 +234,21 @@ cudaError_t bvh_build(cudaStream_t st, const SphereRec* sph, const int32_t* sph_
         k_refit_pack<<<(n + T - 1) / T, T, 0, st>>>(out->sph, n, child0, child1, pint, pleaf, flags, boxes, out->nodes);
         out->launches += 2;
     }
+    if (q_org && q_cell) {
+        if (!flags) BVH_CHECK(cudaMalloc(&flags, sizeof(uint32_t)));
+        uint32_t* off_grid = flags;  // the refit is done with its arrival flags (stream order): word 0 becomes the counter
+        BVH_CHECK(cudaMalloc(&out->qnodes, sizeof(BvhQNode) * n_nodes));
+        BVH_CHECK(cudaMemsetAsync(off_grid, 0, sizeof(uint32_t), st));
+        QuantGrid g;
+        for (int a = 0; a < 3; a++) { g.org[a] = q_org[a]; g.cell[a] = q_cell[a]; }
+        k_quantise<<<(n_nodes + T - 1) / T, T, 0, st>>>(out->nodes, n_nodes, g, out->qnodes, off_grid);
+        out->launches++;
+        uint32_t bad = 0;
+        BVH_CHECK(cudaMemcpyAsync(&bad, off_grid, sizeof bad, cudaMemcpyDeviceToHost, st));
+        BVH_CHECK(cudaStreamSynchronize(st));
+        if (bad) { cudaFree(out->qnodes); out->qnodes = nullptr; }   // a box off the grid: keep the 64-byte nodes
+        else { cudaFree(out->nodes); out->nodes = nullptr; }
+    }
     BVH_CHECK(cudaStreamSynchronize(st));
     BVH_CHECK(cudaGetLastError());
     cudaFree(keys); cudaFree(idx); cudaFree(child0); cudaFree(child1); cudaFree(pint); cudaFree(pleaf); cudaFree(flags); cudaFree(boxes);
@@ -233,8 +257,8 @@ cudaError_t bvh_build(cudaStream_t st, const SphereRec* sph, const int32_t* sph_
 
 void bvh_free(BvhBuildResult* r) {
     if (!r) return;
-    cudaFree(r->nodes); cudaFree(r->sph); cudaFree(r->obj);
-    r->nodes = nullptr; r->sph = nullptr; r->obj = nullptr; r->n_nodes = 0;
+    cudaFree(r->nodes); cudaFree(r->qnodes); cudaFree(r->sph); cudaFree(r->obj);
+    r->nodes = nullptr; r->qnodes = nullptr; r->sph = nullptr; r->obj = nullptr; r->n_nodes = 0;
 }
 
 void launch_untile(cudaStream_t st, const uint32_t* gathered, uint32_t* out, uint32_t height, uint32_t words_per_row, uint32_t band_rows,

@@ -170,7 +170,7 @@ struct DeviceSceneHolder {
             CUDA_TRY(cudaEventCreate(&e0));
             CUDA_TRY(cudaEventCreate(&e1));
             CUDA_TRY(cudaEventRecord(e0, st));
-            cudaError_t e = bvh_build(st, ds.sph, ds.sph_obj, ds.n_spheres, clo, chi, &bvh);
+            cudaError_t e = bvh_build(st, ds.sph, ds.sph_obj, ds.n_spheres, clo, chi, f.quant ? f.q_org : nullptr, f.quant ? f.q_cell : nullptr, &bvh);
             if (e != cudaSuccess) { set_error(std::string("bvh_build: ") + cudaGetErrorString(e)); return RT_ERR_CUDA; }
             CUDA_TRY(cudaEventRecord(e1, st));
             CUDA_TRY(cudaEventSynchronize(e1));
@@ -178,7 +178,7 @@ struct DeviceSceneHolder {
             cudaEventElapsedTime(&ms, e0, e1);
             bvh_ms = ms;
             cudaEventDestroy(e0); cudaEventDestroy(e1);
-            ds.bvh_nodes = bvh.nodes; ds.bvh_sph = bvh.sph; ds.bvh_obj = bvh.obj; ds.n_bvh_nodes = bvh.n_nodes;
+            ds.bvh_nodes = bvh.nodes; ds.bvh_qnodes = bvh.qnodes; ds.bvh_sph = bvh.sph; ds.bvh_obj = bvh.obj; ds.n_bvh_nodes = bvh.n_nodes;
             if ((rc = dev_alloc(&heavy, HEAVY_CAP)) != RT_OK) return rc;
             allocs.push_back(heavy);
             build_launches = bvh.launches;
@@ -394,6 +394,7 @@ int rt_context_create(const rt_scene* s, const rt_render_opts* o, rt_context** o
     std::memset(&c->stats, 0, sizeof c->stats);
     c->stats.bvh_build_ms = c->scene.bvh_ms;
     c->stats.n_bvh_nodes = c->scene.ds.n_bvh_nodes;
+    c->stats.bvh_node_bytes = !c->scene.use_bvh ? 0 : (c->scene.ds.bvh_qnodes ? sizeof(BvhQNode) : sizeof(BvhNode));
     c->stats.local_rows = fp.local_rows;
     c->stats.bytewidth = c->bytewidth;
     c->stats.accel_used = c->scene.use_bvh ? RT_ACCEL_BVH : RT_ACCEL_LINEAR;

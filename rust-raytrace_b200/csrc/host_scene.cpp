@@ -5,6 +5,7 @@
 
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <fstream>
 #include <sstream>
@@ -132,6 +133,8 @@ bool load_texture_file(const std::string& path, HostTexture* out, std::string* e
     return false;
 }
 
+static void choose_quantisation(const rt_scene* s, FlatScene* f);
+
 int flatten_scene(const rt_scene* s, FlatScene* f) {
     if (!s->camera_set) { set_error("scene has no camera"); return RT_ERR_INVALID; }
     if (!s->background_set) { set_error("scene has no background"); return RT_ERR_INVALID; }
@@ -179,6 +182,7 @@ int flatten_scene(const rt_scene* s, FlatScene* f) {
         for (int a = 0; a < 3; a++) { f->box_lo[a] = -INFINITY; f->box_hi[a] = INFINITY; }
     f->cmax = cmax;
     f->rmin = (rmin > 0.0 && std::isfinite(rmin)) ? rmin : 1e-300;
+    choose_quantisation(s, f);
     int mc = 0;
     for (const MaterialRec& m : s->materials) {
         int c = m.kind == MAT_INDIRECT ? (int)m.samples : (m.kind == MAT_TRANSPARENT ? 2 : 1);
@@ -186,6 +190,40 @@ int flatten_scene(const rt_scene* s, FlatScene* f) {
     }
     f->max_children = mc;
     return RT_OK;
+}
+
+// The 32-byte nodes store box planes on a 65535-step grid over the sphere bounds.  A box grows by up to one cell from
+// the rounding and the filter pads it by another 1.25 cells (rt_device.cuh make_boxray32), so the grid is used only
+// when 2.25 cells stay under a quarter of the mean radius on every axis and the bounds are small enough for the f32
+// filter terms (2^23 * cell / |d|, |d| clamped at 1e-30) not to overflow.  RAYTRACE_B200_BVH_NODES=f32|q16 overrides the
+// size test (development / A-B measurements); unusable bounds always mean f32 nodes.
+static void choose_quantisation(const rt_scene* s, FlatScene* f) {
+    f->quant = false;
+    for (int a = 0; a < 3; a++) { f->q_org[a] = 0.0; f->q_cell[a] = 0.0; }
+    if (f->sph.empty()) return;
+    double rsum = 0.0;
+    for (const HostObject& o : s->objects)
+        if (!o.is_plane) rsum += std::fabs(o.radius);
+    const double rmean = rsum / (double)f->sph.size();
+    double cell_max = 0.0, ext_max = 0.0;
+    for (int a = 0; a < 3; a++) {
+        const double lo = f->box_lo[a], hi = f->box_hi[a];
+        if (!std::isfinite(lo) || !std::isfinite(hi) || !(hi >= lo)) return;
+        // the node boxes are the f64 bounds rounded outward to f32: leave room for that
+        const double m = (std::fabs(lo) + std::fabs(hi)) * 0x1.0p-21 + 1e-30;
+        f->q_org[a] = lo - m;
+        f->q_cell[a] = (hi + m - f->q_org[a]) / 65534.0;
+        if (!(f->q_cell[a] > 0.0) || !std::isfinite(f->q_cell[a])) return;
+        if (f->q_cell[a] > cell_max) cell_max = f->q_cell[a];
+        if (hi - lo > ext_max) ext_max = hi - lo;
+    }
+    if (!std::isfinite(rmean) || !(ext_max <= 1e6) || !(f->cmax <= 1e6)) return;
+    bool fine = 2.25 * cell_max <= 0.25 * rmean;
+    if (const char* e = std::getenv("RAYTRACE_B200_BVH_NODES")) {
+        if (!std::strcmp(e, "f32")) fine = false;
+        else if (!std::strcmp(e, "q16")) fine = true;
+    }
+    f->quant = fine;
 }
 
 void fill_scene_header(const rt_scene* s, const FlatScene& f, DeviceScene* ds) {
@@ -205,6 +243,8 @@ void fill_scene_header(const rt_scene* s, const FlatScene& f, DeviceScene* ds) {
     ds->bvh_cmax = f.cmax;
     ds->bvh_rmin = f.rmin;
     for (int a = 0; a < 3; a++) { ds->bvh_lo[a] = f.box_lo[a]; ds->bvh_hi[a] = f.box_hi[a]; }
+    ds->bvh_qnodes = nullptr;  // set by the owner of the device buffers when f.quant
+    for (int a = 0; a < 3; a++) { ds->q_org[a] = f.q_org[a]; ds->q_cell[a] = f.q_cell[a]; }
 }
 
 bool accel_uses_bvh(int accel, uint32_t n_spheres) {

@@ -71,6 +71,9 @@ struct FlatScene {
     double box_lo[3], box_hi[3];  // bounds of the sphere boxes (c -+ |r|); -+inf when unusable
     double cmax, rmin;
     int32_t max_children;
+    // 16-bit grid for the 32-byte BVH nodes (rt_types.h BvhQNode); quant == false: grid too coarse / unusable bounds
+    bool quant;
+    double q_org[3], q_cell[3];
 };
 // returns RT_OK or RT_ERR_INVALID (missing camera/background/skybox face)
 int flatten_scene(const rt_scene* s, FlatScene* out);

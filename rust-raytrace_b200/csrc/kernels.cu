@@ -255,6 +255,7 @@ constexpr int FETCH_MIN_IDLE = RT_FETCH_MIN_IDLE;  // refill when at least this 
 //   phase 2  every lane with a pending leaf runs the exact f64 sphere test,
 // and lanes whose ray has finished are refilled from the global cursor instead of idling until the slowest lane of
 // a fixed 32-ray batch is done.
+template <bool QNODES>
 __global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_constant__ DeviceScene sc, RayQueue q, uint32_t first, uint32_t n, Counters* counters,
                                                              uint32_t* heavy, uint32_t heavy_walks) {
     uint32_t* cursor = &counters->cursor;
@@ -282,7 +283,7 @@ __global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_consta
                     sp = 0;
                     cur = TRAV_EMPTY;
                     if (!best.nan && sc.n_spheres > 0) {
-                        br = make_boxray32(sc, r.o, r.d);
+                        br = make_boxray32_t<QNODES>(sc, r.o, r.d);
                         if (br.enter) { cur = 0; bound = closest_bound32(best.t, br.t0); }
                     }
                     active = true;
@@ -295,7 +296,7 @@ __global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_consta
             if (exhausted) break;
             continue;
         }
-        if (active) cur = trav_descend(sc, br, cur, bound, st, sp, tc, RT_DESCEND_STEPS);
+        if (active) cur = trav_descend<QNODES>(sc, br, cur, bound, st, sp, tc, RT_DESCEND_STEPS);
         __syncwarp();
         if (active) {
             if (cur == TRAV_EMPTY) {
@@ -318,6 +319,7 @@ __global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_consta
     flush_traverse_count(tc, counters, 0);
 }
 
+template <bool QNODES>
 __global__ void __launch_bounds__(BVH_THREADS) k_shadow_bvh(const __grid_constant__ DeviceScene sc, ShadowQueue sq, uint32_t n, double* accum, Counters* counters,
                                                             uint32_t* heavy, uint32_t heavy_walks) {
     uint32_t* cursor = &counters->cursor;
@@ -348,7 +350,7 @@ __global__ void __launch_bounds__(BVH_THREADS) k_shadow_bvh(const __grid_constan
                     cur = TRAV_EMPTY;
                     occluded = shadow_result(s, range2);
                     if (!s.nan && !s.any && sc.n_spheres > 0) {
-                        br = make_boxray32(sc, r.o, r.d);
+                        br = make_boxray32_t<QNODES>(sc, r.o, r.d);
                         if (br.enter) { cur = 0; bound = shadow_bound32(range2, br.t0); }
                     }
                     active = true;
@@ -360,7 +362,7 @@ __global__ void __launch_bounds__(BVH_THREADS) k_shadow_bvh(const __grid_constan
             if (exhausted) break;
             continue;
         }
-        if (active) cur = trav_descend(sc, br, cur, bound, st, sp, tc, RT_DESCEND_STEPS);
+        if (active) cur = trav_descend<QNODES>(sc, br, cur, bound, st, sp, tc, RT_DESCEND_STEPS);
         __syncwarp();
         if (active) {
             if (cur != TRAV_EMPTY && cur < 0) {
@@ -621,7 +623,8 @@ static void l_closest(cudaStream_t st, const DeviceScene& sc, bool bvh, RayQueue
         cudaMemsetAsync(&counters->cursor, 0, 2 * sizeof(uint32_t), st);  // cursor + heavy_count
         uint32_t want = div_up(n, BVH_THREADS);
         uint32_t grid = (uint32_t)sm_count * 8u;  // 8 resident CTAs of 128 threads per SM
-        k_closest_bvh<<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, q, first, n, counters, heavy, heavy_walks(sc));
+        if (sc.bvh_qnodes) k_closest_bvh<true><<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, q, first, n, counters, heavy, heavy_walks(sc));
+        else k_closest_bvh<false><<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, q, first, n, counters, heavy, heavy_walks(sc));
         ShadowQueue none{};
         k_heavy_scan<false><<<(uint32_t)sm_count * 4u, HEAVY_THREADS, 0, st>>>(sc, q, none, first, nullptr, counters, heavy);
     } else {
@@ -643,7 +646,8 @@ static void l_shadow(cudaStream_t st, const DeviceScene& sc, bool bvh, ShadowQue
         cudaMemsetAsync(&counters->cursor, 0, 2 * sizeof(uint32_t), st);
         uint32_t want = div_up(n, BVH_THREADS);
         uint32_t grid = (uint32_t)sm_count * 8u;
-        k_shadow_bvh<<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters, heavy, heavy_walks(sc));
+        if (sc.bvh_qnodes) k_shadow_bvh<true><<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters, heavy, heavy_walks(sc));
+        else k_shadow_bvh<false><<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters, heavy, heavy_walks(sc));
         RayQueue none{};
         k_heavy_scan<true><<<(uint32_t)sm_count * 4u, HEAVY_THREADS, 0, st>>>(sc, none, sq, 0u, accum, counters, heavy);
     } else {

@@ -48,7 +48,8 @@ const KernelTable* kernels_fast();
 
 // mode-independent kernels (bvh_build.cu)
 struct BvhBuildResult {
-    BvhNode* nodes;       // [n_nodes]
+    BvhNode* nodes;       // [n_nodes]; null when qnodes is set
+    BvhQNode* qnodes;     // [n_nodes] 32-byte grid form, when asked for and every box fits the grid
     SphereRec* sph;       // Morton order
     int32_t* obj;
     uint32_t n_nodes;
@@ -56,8 +57,9 @@ struct BvhBuildResult {
 };
 // Builds the LBVH over `n` spheres (scan-order records + object ids, device pointers).  Device-side throughout:
 // Morton codes -> bitonic sort -> Karras hierarchy -> bottom-up refit -> packed f32 child boxes.
+// q_org/q_cell non-null: also pack the nodes on that grid (rt_types.h BvhQNode) and drop the 64-byte form.
 cudaError_t bvh_build(cudaStream_t, const SphereRec* sph, const int32_t* sph_obj, uint32_t n, const double* centroid_lo, const double* centroid_hi,
-                      BvhBuildResult* out);
+                      const double* q_org, const double* q_cell, BvhBuildResult* out);
 void bvh_free(BvhBuildResult* r);
 
 // de-interleave row bands after the framebuffer all-gather (rank-major input)

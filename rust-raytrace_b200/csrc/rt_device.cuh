@@ -264,7 +264,8 @@ RT_HD float f64_to_f32_up(double x) {
 }
 #endif
 
-RT_HD BoxRay32 make_boxray32(const DeviceScene& sc, V3 o, V3 d) {
+template <bool QNODES>
+RT_HD BoxRay32 make_boxray32_t(const DeviceScene& sc, V3 o, V3 d) {
     BoxRay32 b;
     const double s = fmax(fmax(fabs(o.x), fabs(o.y)), fabs(o.z));
     const double dm = fmax(fmax(fabs(d.x), fabs(d.y)), fabs(d.z));
@@ -303,9 +304,30 @@ RT_HD BoxRay32 make_boxray32(const DeviceScene& sc, V3 o, V3 d) {
     const double S = s2 + sc.bvh_cmax;
     const double pad = S * 0x1.0p-20 + infl + (s + dm * b.t0) * 0x1.0p-50;
     b.ix = safe_inv32(d.x); b.iy = safe_inv32(d.y); b.iz = safe_inv32(d.z);
-    b.px = (float)((oo.x + pad) * (double)b.ix); b.py = (float)((oo.y + pad) * (double)b.iy); b.pz = (float)((oo.z + pad) * (double)b.iz);
-    b.mx = (float)((oo.x - pad) * (double)b.ix); b.my = (float)((oo.y - pad) * (double)b.iy); b.mz = (float)((oo.z - pad) * (double)b.iz);
+    if (!QNODES) {
+        b.px = (float)((oo.x + pad) * (double)b.ix); b.py = (float)((oo.y + pad) * (double)b.iy); b.pz = (float)((oo.z + pad) * (double)b.iz);
+        b.mx = (float)((oo.x - pad) * (double)b.ix); b.my = (float)((oo.y - pad) * (double)b.iy); b.mz = (float)((oo.z - pad) * (double)b.iz);
+    } else {
+        // grid form (see load_qnode).  Rounding a to f32 moves a plane by < 0.51 cells ((2^23 + q) * 2^-24), rounding P
+        // by < 0.51 cells (|P| < 2^24 a, o' being inside the bounds): 1.25 more cells of padding cover both.
+        const double oa[3] = {oo.x, oo.y, oo.z};
+        const float inv[3] = {b.ix, b.iy, b.iz};
+        float a32[3], pl[3], ph[3];
+        for (int a = 0; a < 3; a++) {
+            const double padq = pad + 1.25 * sc.q_cell[a];
+            a32[a] = (float)(sc.q_cell[a] * (double)inv[a]);
+            const double base = 8388608.0 * (double)a32[a];
+            pl[a] = (float)(base - (sc.q_org[a] - oa[a] - padq) * (double)inv[a]);
+            ph[a] = (float)(base - (sc.q_org[a] - oa[a] + padq) * (double)inv[a]);
+        }
+        b.ix = a32[0]; b.iy = a32[1]; b.iz = a32[2];
+        b.px = pl[0]; b.py = pl[1]; b.pz = pl[2];
+        b.mx = ph[0]; b.my = ph[1]; b.mz = ph[2];
+    }
     return b;
+}
+RT_HD BoxRay32 make_boxray32(const DeviceScene& sc, V3 o, V3 d) {
+    return sc.bvh_qnodes ? make_boxray32_t<true>(sc, o, d) : make_boxray32_t<false>(sc, o, d);
 }
 
 // conservative entry distance (>= 0, measured from the advanced origin) of the padded box if it can be hit within
@@ -320,6 +342,70 @@ RT_HD float box_entry32(const BoxRay32& b, const float* lo, const float* hi, flo
     tf *= (1.0f + 0x1.0p-21f);
     return (tn <= tf && tn <= bound) ? tn : -1.0f;
 }
+
+// ---- 32-byte nodes: box planes on the scene's 16-bit grid -------------------------------------------------
+// largest q with org + q*cell <= v (lower bounds) / smallest q with org + q*cell >= v (upper bounds), evaluated with
+// the same f64 expression the check uses; `ok` is cleared when v lies off the grid (the caller keeps the f32 nodes)
+RT_HD uint16_t quant_lo(float v, double org, double cell, bool& ok) {
+    double q = floor(((double)v - org) / cell);
+    if (!(q >= 0.0)) { q = 0.0; }
+    if (q > 65535.0) q = 65535.0;
+    while (q > 0.0 && org + q * cell > (double)v) q -= 1.0;
+    if (!(org + q * cell <= (double)v)) ok = false;
+    return (uint16_t)q;
+}
+RT_HD uint16_t quant_hi(float v, double org, double cell, bool& ok) {
+    double q = ceil(((double)v - org) / cell);
+    if (!(q >= 0.0)) { q = 0.0; }
+    if (q > 65535.0) q = 65535.0;
+    while (q < 65535.0 && org + q * cell < (double)v) q += 1.0;
+    if (!(org + q * cell >= (double)v)) ok = false;
+    return (uint16_t)q;
+}
+RT_HD BvhQNode quantise_node(const BvhNode& n, const double* org, const double* cell, bool& ok) {
+    BvhQNode o;
+    for (int a = 0; a < 3; a++) {
+        o.q[a] = quant_lo(n.lo0[a], org[a], cell[a], ok);
+        o.q[3 + a] = quant_hi(n.hi0[a], org[a], cell[a], ok);
+        o.q[6 + a] = quant_lo(n.lo1[a], org[a], cell[a], ok);
+        o.q[9 + a] = quant_hi(n.hi1[a], org[a], cell[a], ok);
+    }
+    o.c0 = n.c0; o.c1 = n.c1;
+    return o;
+}
+
+// The filter never decodes a grid coordinate: a plane at org + q*cell has slab distance
+//   ((org + q*cell) - (o' +- pad)) * inv  =  (2^23 + q) * (cell*inv)  +  ((org - (o' +- pad)) * inv - 2^23 * cell*inv),
+// so with the per-ray constants a = cell*inv and P = the last bracket it is one FFMA on the float 2^23 + q, whose
+// bit pattern is 0x4B000000 | q -- one byte permute per plane.  BoxRay32 holds (a, -P_lo, -P_hi) in place of
+// (inv, (o'+pad)*inv, (o'-pad)*inv) and box_entry32 is shared by both node formats.
+#if defined(__CUDA_ARCH__)
+RT_HD BvhNode load_qnode(const BvhQNode* p) {
+    uint32_t w0, w1, w2, w3, w4, w5, w6, w7;
+    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3), "=r"(w4), "=r"(w5), "=r"(w6), "=r"(w7) : "l"(p));
+    const uint32_t K = 0x4B000000u;
+    BvhNode n;
+    n.lo0[0] = __uint_as_float(__byte_perm(w0, K, 0x7610)); n.lo0[1] = __uint_as_float(__byte_perm(w0, K, 0x7632));
+    n.lo0[2] = __uint_as_float(__byte_perm(w1, K, 0x7610)); n.hi0[0] = __uint_as_float(__byte_perm(w1, K, 0x7632));
+    n.hi0[1] = __uint_as_float(__byte_perm(w2, K, 0x7610)); n.hi0[2] = __uint_as_float(__byte_perm(w2, K, 0x7632));
+    n.lo1[0] = __uint_as_float(__byte_perm(w3, K, 0x7610)); n.lo1[1] = __uint_as_float(__byte_perm(w3, K, 0x7632));
+    n.lo1[2] = __uint_as_float(__byte_perm(w4, K, 0x7610)); n.hi1[0] = __uint_as_float(__byte_perm(w4, K, 0x7632));
+    n.hi1[1] = __uint_as_float(__byte_perm(w5, K, 0x7610)); n.hi1[2] = __uint_as_float(__byte_perm(w5, K, 0x7632));
+    n.c0 = (int32_t)w6; n.c1 = (int32_t)w7;
+    return n;
+}
+#else
+RT_HD BvhNode load_qnode(const BvhQNode* p) {
+    BvhNode n;
+    for (int a = 0; a < 3; a++) {
+        n.lo0[a] = (float)(8388608u + p->q[a]); n.hi0[a] = (float)(8388608u + p->q[3 + a]);
+        n.lo1[a] = (float)(8388608u + p->q[6 + a]); n.hi1[a] = (float)(8388608u + p->q[9 + a]);
+    }
+    n.c0 = p->c0; n.c1 = p->c1;
+    return n;
+}
+#endif
 
 #if defined(__CUDA_ARCH__)
 // the 64-byte node in two 256-bit loads (sm_100 LDG.E.ENL2.256): a divergent node fetch costs the L1 data pipe one
@@ -369,10 +455,11 @@ RT_HD int32_t trav_pop(const TravStack& st, int& sp, float bound) {
 // (returns ~slot < 0) or nothing is left (TRAV_EMPTY).  Leaves are NOT tested here: postponing them keeps the lanes
 // of a warp in the same code (box tests together, sphere tests together).
 // `max_steps` bounds the walk (the kernels come back to refill finished lanes; an unfinished walk returns cur >= 0).
+template <bool QNODES>
 RT_HD int32_t trav_descend(const DeviceScene& sc, const BoxRay32& br, int32_t cur, float bound, TravStack& st, int& sp, TraverseCount& tc,
                            int max_steps = 0x7FFFFFFF) {
     while (cur >= 0 && max_steps-- > 0) {
-        const BvhNode n = load_node(sc.bvh_nodes + cur);
+        const BvhNode n = QNODES ? load_qnode(sc.bvh_qnodes + cur) : load_node(sc.bvh_nodes + cur);
         tc.nodes++;
         const float t0 = box_entry32(br, n.lo0, n.hi0, bound);
         const float t1 = box_entry32(br, n.lo1, n.hi1, bound);
@@ -427,7 +514,7 @@ RT_HD void closest_bvh(const DeviceScene& sc, const RayQ& r, int32_t& id, double
             int32_t cur = 0;
             float bound = closest_bound32(best.t, br.t0);
             while (true) {
-                cur = trav_descend(sc, br, cur, bound, st, sp, tc);
+                cur = sc.bvh_qnodes ? trav_descend<true>(sc, br, cur, bound, st, sp, tc) : trav_descend<false>(sc, br, cur, bound, st, sp, tc);
                 if (cur == TRAV_EMPTY) break;
                 leaf_closest(sc, r, ~cur, best, tc);
                 bound = closest_bound32(best.t, br.t0);
@@ -449,7 +536,7 @@ RT_HD bool shadow_bvh(const DeviceScene& sc, const RayQ& r, double range2, Trave
             int32_t cur = 0;
             const float bound = shadow_bound32(range2, br.t0);
             while (true) {
-                cur = trav_descend(sc, br, cur, bound, st, sp, tc);
+                cur = sc.bvh_qnodes ? trav_descend<true>(sc, br, cur, bound, st, sp, tc) : trav_descend<false>(sc, br, cur, bound, st, sp, tc);
                 if (cur == TRAV_EMPTY) break;
                 if (leaf_shadow(sc, r, ~cur, range2, tc)) { s.any = true; break; }
                 cur = trav_pop(st, sp, bound);

@@ -68,6 +68,14 @@ struct alignas(64) BvhNode {
     int32_t _pad[2];
 };
 
+// 32-byte BVH node: the same two child boxes on the scene's 16-bit grid (coordinate = q_org + q * q_cell per axis,
+// lower bounds rounded down, upper bounds rounded up) -- one 256-bit load per visit.  Used when the grid is fine
+// enough for the scene (host_scene.cpp choose_quantisation), else the 64-byte node above.
+struct alignas(32) BvhQNode {
+    uint16_t q[12];  // lo0[3], hi0[3], lo1[3], hi1[3]
+    int32_t c0, c1;
+};
+
 // Everything a kernel needs to know about the scene (passed by value as a __grid_constant__ parameter).
 struct DeviceScene {
     uint32_t n_objects, n_spheres, n_planes, n_lights;
@@ -96,6 +104,8 @@ struct DeviceScene {
     double bvh_cmax;  // max over spheres of (|c|_inf + r): scale term of the per-ray box padding
     double bvh_rmin;  // min radius
     double bvh_lo[3], bvh_hi[3];  // bounds of all sphere boxes (f64): rays are advanced to this box before the f32 filter
+    const BvhQNode* bvh_qnodes;   // non-null: traverse these instead of bvh_nodes
+    double q_org[3], q_cell[3];   // the grid of bvh_qnodes
 };
 
 // Ray queue of one wavefront level, structure of arrays (one allocation, capacity `cap`)

@@ -132,3 +132,10 @@ def bvh_stats(scene):
     n, d = C.c_uint64(), C.c_uint32()
     B.check(lib(), lib().emu_bvh_stats(scene.handle, C.byref(n), C.byref(d)))
     return n.value, d.value
+
+
+def bvh_node_bytes(scene):
+    """bytes per BVH node the product would use for this scene: 32 = grid form, 64 = f32 planes"""
+    b = C.c_uint32()
+    B.check(lib(), lib().emu_bvh_node_bytes(scene.handle, C.byref(b)))
+    return b.value

@@ -26,6 +26,7 @@ struct EmuScene {
     FlatScene flat;
     DeviceScene ds{};
     std::vector<BvhNode> nodes;
+    std::vector<BvhQNode> qnodes;  // grid form, when the scene's grid is fine enough (host_scene.cpp choose_quantisation)
     std::vector<SphereRec> bvh_sph;
     std::vector<int32_t> bvh_obj;
     bool use_bvh = false;
@@ -121,6 +122,12 @@ int make_scene(const rt_scene* s, int accel, EmuScene* e) {
         build_bvh(*e);
         e->ds.bvh_nodes = e->nodes.data(); e->ds.bvh_sph = e->bvh_sph.data(); e->ds.bvh_obj = e->bvh_obj.data();
         e->ds.n_bvh_nodes = (uint32_t)e->nodes.size();
+        if (e->flat.quant) {
+            bool ok = true;
+            e->qnodes.resize(e->nodes.size());
+            for (size_t i = 0; i < e->nodes.size(); i++) e->qnodes[i] = quantise_node(e->nodes[i], e->flat.q_org, e->flat.q_cell, ok);
+            if (ok) e->ds.bvh_qnodes = e->qnodes.data();
+        }
     }
     return RT_OK;
 }
@@ -218,6 +225,7 @@ RT_API int emu_render_shard(const rt_scene* s, const rt_render_opts* o, uint8_t*
     st.local_rows = fp.local_rows; st.bytewidth = bytewidth;
     st.accel_used = e.use_bvh ? RT_ACCEL_BVH : RT_ACCEL_LINEAR;
     st.n_bvh_nodes = e.nodes.size();
+    st.bvh_node_bytes = !e.use_bvh ? 0 : (e.ds.bvh_qnodes ? sizeof(BvhQNode) : sizeof(BvhNode));
     if (bgr_rows) {
         std::memset(bgr_rows, 0, (size_t)fp.local_rows * bytewidth);
         for (uint32_t y = 0; y < fp.local_rows; y++)
@@ -297,6 +305,14 @@ RT_API int emu_bvh_stats(const rt_scene* s, uint64_t* n_nodes, uint32_t* max_dep
         }
     }
     *max_depth = md;
+    return RT_OK;
+}
+
+RT_API int emu_bvh_node_bytes(const rt_scene* s, uint32_t* bytes) {
+    EmuScene e;
+    int rc = make_scene(s, RT_ACCEL_BVH, &e);
+    if (rc != RT_OK) return rc;
+    *bytes = !e.use_bvh ? 0u : (e.ds.bvh_qnodes ? (uint32_t)sizeof(BvhQNode) : (uint32_t)sizeof(BvhNode));
     return RT_OK;
 }
 

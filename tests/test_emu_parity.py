@@ -185,3 +185,47 @@ def test_far_origins_advance_to_the_scene(rt, orc, scenes, accel):
     r2 = np.where(rng.uniform(size=len(rays)) < 0.5, -1.0, (dist.max() * 2) ** 2)
     occ = emu.shadow_rays(emu.Scene(desc), rays, r2, accel=rt.ACCEL_BVH if accel == "bvh" else rt.ACCEL_LINEAR)
     assert np.array_equal(occ, rid >= 0)
+
+
+@pytest.mark.parametrize("nodes", ["q16", "f32"])
+def test_both_node_formats_equal_the_scan(rt, orc, scenes, nodes, monkeypatch):
+    """32-byte grid nodes (boxes rounded outward to a 16-bit grid, padded 1.25 cells) and 64-byte f32 nodes are both only
+    a conservative filter in front of the scan's exact test: ids, t and normals bit-identical with either"""
+    monkeypatch.setenv("RAYTRACE_B200_BVH_NODES", nodes)
+    desc = scenes.random_spheres(3000, 31, 40.0, 8, 8)
+    assert emu.bvh_node_bytes(emu.Scene(desc)) == (32 if nodes == "q16" else 64)
+    rng = np.random.default_rng(12)
+    rays = _rays(rng, 40000, 45.0, 8.0)
+    rays[:2000, 3:] = np.array([1.0, 0.0, 0.0]) * rng.choice([-1.0, 1.0], 2000)[:, None]   # axis-parallel: clamped reciprocals
+    rays[2000:4000, 4] = 0.0
+    rays[4000:5000, 3] = 1e-35
+    ids, t, nrm = emu.trace_rays(emu.Scene(desc), rays, accel=rt.ACCEL_BVH)
+    rid, rt_, rn = orc.OracleScene(desc).trace_rays(rays)
+    assert np.array_equal(ids, rid) and np.array_equal(t, rt_) and np.array_equal(nrm, rn)
+    r2 = np.where(rng.uniform(size=len(rays)) < 0.3, -1.0, rng.uniform(0.0, 60.0, len(rays)) ** 2)
+    occ = emu.shadow_rays(emu.Scene(desc), rays, r2, accel=rt.ACCEL_BVH)
+    with np.errstate(invalid="ignore"):
+        assert np.array_equal(occ, (rid >= 0) & ((r2 < 0) | (rt_ * rt_ < r2)))
+
+
+def test_node_format_follows_the_grid_resolution(rt, scenes, monkeypatch):
+    monkeypatch.delenv("RAYTRACE_B200_BVH_NODES", raising=False)
+    assert emu.bvh_node_bytes(emu.Scene(scenes.random_spheres(500, 3, 60.0, 8, 8))) == 32       # cell 0.002 vs radius 0.5
+    assert emu.bvh_node_bytes(emu.Scene(scenes.random_spheres(500, 3, 30000.0, 8, 8))) == 64    # cell 0.9: too coarse
+
+
+def test_coarse_grid_is_still_conservative(rt, orc, scenes, monkeypatch):
+    """forcing the grid on a scene it is far too coarse for (cells larger than the spheres) may only cost time"""
+    monkeypatch.setenv("RAYTRACE_B200_BVH_NODES", "q16")
+    desc = scenes.random_spheres(800, 9, 30000.0, 8, 8)
+    assert emu.bvh_node_bytes(emu.Scene(desc)) == 32
+    data = desc["objects"][1]["data"]
+    rng = np.random.default_rng(2)
+    k = rng.integers(0, len(data), 6000)
+    o = np.stack([rng.uniform(-30000, 30000, 6000), rng.uniform(1, 50, 6000), rng.uniform(-30000, 30000, 6000)], 1)
+    tgt = data[k, :3] + rng.normal(size=(6000, 3)) * data[k, 3:4] * 0.7
+    rays = np.concatenate([o, tgt - o], 1)
+    ids, t, nrm = emu.trace_rays(emu.Scene(desc), rays, accel=rt.ACCEL_BVH)
+    rid, rt_, rn = orc.OracleScene(desc).trace_rays(rays)
+    assert np.array_equal(ids, rid) and np.array_equal(t, rt_) and np.array_equal(nrm, rn)
+    assert (rid > 0).mean() > 0.3

@@ -11,7 +11,7 @@ ctx.set_profiling(True)
 ctx.render()
 st = ctx.render()
 rc, rs = st["rays_primary"] + st["rays_secondary"], st["rays_shadow"]
-print(which, "render %.2f ms" % st["render_ms"], {k: round(v, 2) for k, v in st["class_ms"].items()}, "launches", st["class_launches"])
+print(which, "node bytes", st["bvh_node_bytes"], "render %.2f ms" % st["render_ms"], {k: round(v, 2) for k, v in st["class_ms"].items()}, "launches", st["class_launches"])
 print("closest: %d rays, %.1f nodes/ray, %.2f prims/ray, %.0f Mrays/s" % (rc, st["bvh_nodes_visited"]["closest"] / rc, st["bvh_prims_tested"]["closest"] / rc, rc / st["class_ms"]["closest"] / 1e3))
 print("shadow : %d rays, %.1f nodes/ray, %.2f prims/ray, %.0f Mrays/s" % (rs, st["bvh_nodes_visited"]["shadow"] / rs, st["bvh_prims_tested"]["shadow"] / rs, rs / st["class_ms"]["shadow"] / 1e3))
 print("heavy rays:", st["heavy_rays"])
