@@ -255,17 +255,38 @@ constexpr int FETCH_MIN_IDLE = RT_FETCH_MIN_IDLE;  // refill when at least this 
 //   phase 2  every lane with a pending leaf runs the exact f64 sphere test,
 // and lanes whose ray has finished are refilled from the global cursor instead of idling until the slowest lane of
 // a fixed 32-ray batch is done.
+//
+// Registers: the walk needs (cur, sp, bound, the twelve plane constants); the f64 ray, the running best hit / shadow
+// range and t0 are only needed at a leaf or at the end, so they are parked in shared memory (one column per thread, SoA:
+// conflict-free) -- 64 registers per thread, 8 CTAs of 128 threads per SM.
+struct TravSmem {
+    double ray[6][BVH_THREADS];  // origin, direction
+    double aux[BVH_THREADS];     // closest: t of the best hit so far; shadow: squared range
+    double t0[BVH_THREADS];      // parameter of the advanced origin
+};
+__device__ __forceinline__ void park_ray(TravSmem& sm, V3 o, V3 d, double aux, double t0) {
+    const int t = threadIdx.x;
+    sm.ray[0][t] = o.x; sm.ray[1][t] = o.y; sm.ray[2][t] = o.z;
+    sm.ray[3][t] = d.x; sm.ray[4][t] = d.y; sm.ray[5][t] = d.z;
+    sm.aux[t] = aux; sm.t0[t] = t0;
+}
+__device__ __forceinline__ RayQ parked_ray(const TravSmem& sm) {
+    const int t = threadIdx.x;
+    return make_rayq(v3(sm.ray[0][t], sm.ray[1][t], sm.ray[2][t]), v3(sm.ray[3][t], sm.ray[4][t], sm.ray[5][t]));
+}
+
 template <bool QNODES>
-__global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_constant__ DeviceScene sc, RayQueue q, uint32_t first, uint32_t n, Counters* counters,
-                                                             uint32_t* heavy, uint32_t heavy_walks) {
+__global__ void __launch_bounds__(BVH_THREADS, 8) k_closest_bvh(const __grid_constant__ DeviceScene sc, RayQueue q, uint32_t first, uint32_t n, Counters* counters,
+                                                                uint32_t* heavy, uint32_t heavy_walks) {
+    __shared__ TravSmem sm;
     uint32_t* cursor = &counters->cursor;
     uint32_t walks = 0;  // bounded walks spent on the current ray
     TraverseCount tc; tc.nodes = 0; tc.prims = 0;
     TravStack st; int sp = 0;
-    RayQ r; BoxRay32 br; Closest best;
-    r = make_rayq(v3(0, 0, 0), v3(0, 0, 0)); best = closest_none();
-    br.ix = br.iy = br.iz = br.px = br.py = br.pz = br.mx = br.my = br.mz = 0.0f; br.t0 = 0.0; br.enter = false;
+    BoxRay32 br = boxray32_none();
     int32_t cur = TRAV_EMPTY;
+    int32_t best_obj = 0x7FFFFFFF;  // the best hit's t is parked in sm.aux
+    bool best_nan = false;
     float bound = 0.0f;
     uint32_t ray = 0;
     bool active = false, exhausted = false;
@@ -276,16 +297,20 @@ __global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_consta
             if (!active) {
                 if (li < n) {
                     ray = first + li;
-                    r = make_rayq(v3(q.ox[ray], q.oy[ray], q.oz[ray]), v3(q.dx[ray], q.dy[ray], q.dz[ray]));
-                    best = closest_none();
+                    const RayQ r = make_rayq(v3(q.ox[ray], q.oy[ray], q.oz[ray]), v3(q.dx[ray], q.dy[ray], q.dz[ray]));
+                    Closest best = closest_none();
                     planes_closest(sc, r, best);
                     walks = 0;
                     sp = 0;
                     cur = TRAV_EMPTY;
+                    double t0 = 0.0;
                     if (!best.nan && sc.n_spheres > 0) {
                         br = make_boxray32_t<QNODES>(sc, r.o, r.d);
-                        if (br.enter) { cur = 0; bound = closest_bound32(best.t, br.t0); }
+                        t0 = br.t0;
+                        if (br.enter) { cur = 0; bound = closest_bound32(best.t, t0); }
                     }
+                    best_obj = best.obj; best_nan = best.nan;
+                    park_ray(sm, r.o, r.d, best.t, t0);
                     active = true;
                 }
             }
@@ -300,12 +325,15 @@ __global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_consta
         __syncwarp();
         if (active) {
             if (cur == TRAV_EMPTY) {
-                q.hit_id[ray] = closest_id(best);
-                q.hit_t[ray] = best.t;
+                q.hit_id[ray] = best_obj == 0x7FFFFFFF ? -1 : best_obj;
+                q.hit_t[ray] = sm.aux[threadIdx.x];
                 active = false;
             } else if (cur < 0) {
+                const RayQ r = parked_ray(sm);
+                Closest best; best.t = sm.aux[threadIdx.x]; best.obj = best_obj; best.nan = best_nan;
                 leaf_closest(sc, r, ~cur, best, tc);
-                bound = closest_bound32(best.t, br.t0);
+                sm.aux[threadIdx.x] = best.t; best_obj = best.obj; best_nan = best.nan;
+                bound = closest_bound32(best.t, sm.t0[threadIdx.x]);
                 cur = trav_pop(st, sp, bound);
             }
             if (active && ++walks > heavy_walks) {
@@ -320,18 +348,16 @@ __global__ void __launch_bounds__(BVH_THREADS) k_closest_bvh(const __grid_consta
 }
 
 template <bool QNODES>
-__global__ void __launch_bounds__(BVH_THREADS) k_shadow_bvh(const __grid_constant__ DeviceScene sc, ShadowQueue sq, uint32_t n, double* accum, Counters* counters,
-                                                            uint32_t* heavy, uint32_t heavy_walks) {
+__global__ void __launch_bounds__(BVH_THREADS, 8) k_shadow_bvh(const __grid_constant__ DeviceScene sc, ShadowQueue sq, uint32_t n, double* accum, Counters* counters,
+                                                               uint32_t* heavy, uint32_t heavy_walks) {
+    __shared__ TravSmem sm;
     uint32_t* cursor = &counters->cursor;
     uint32_t walks = 0;
     TraverseCount tc; tc.nodes = 0; tc.prims = 0;
     TravStack st; int sp = 0;
-    RayQ r; BoxRay32 br;
-    r = make_rayq(v3(0, 0, 0), v3(0, 0, 0));
-    br.ix = br.iy = br.iz = br.px = br.py = br.pz = br.mx = br.my = br.mz = 0.0f; br.t0 = 0.0; br.enter = false;
+    BoxRay32 br = boxray32_none();
     int32_t cur = TRAV_EMPTY;
     float bound = 0.0f;
-    double range2 = -1.0;
     uint32_t ray = 0;
     bool active = false, exhausted = false, occluded = false;
     while (true) {
@@ -341,8 +367,8 @@ __global__ void __launch_bounds__(BVH_THREADS) k_shadow_bvh(const __grid_constan
             if (!active) {
                 if (li < n) {
                     ray = li;
-                    r = make_rayq(v3(sq.ox[ray], sq.oy[ray], sq.oz[ray]), v3(sq.dx[ray], sq.dy[ray], sq.dz[ray]));
-                    range2 = sq.r2[ray];
+                    const RayQ r = make_rayq(v3(sq.ox[ray], sq.oy[ray], sq.oz[ray]), v3(sq.dx[ray], sq.dy[ray], sq.dz[ray]));
+                    const double range2 = sq.r2[ray];
                     Shadow s; s.nan = false; s.any = false;
                     planes_shadow(sc, r, range2, s);
                     walks = 0;
@@ -353,6 +379,7 @@ __global__ void __launch_bounds__(BVH_THREADS) k_shadow_bvh(const __grid_constan
                         br = make_boxray32_t<QNODES>(sc, r.o, r.d);
                         if (br.enter) { cur = 0; bound = shadow_bound32(range2, br.t0); }
                     }
+                    park_ray(sm, r.o, r.d, range2, 0.0);
                     active = true;
                 }
             }
@@ -366,7 +393,7 @@ __global__ void __launch_bounds__(BVH_THREADS) k_shadow_bvh(const __grid_constan
         __syncwarp();
         if (active) {
             if (cur != TRAV_EMPTY && cur < 0) {
-                if (leaf_shadow(sc, r, ~cur, range2, tc)) { occluded = true; cur = TRAV_EMPTY; }
+                if (leaf_shadow(sc, parked_ray(sm), ~cur, sm.aux[threadIdx.x], tc)) { occluded = true; cur = TRAV_EMPTY; }
                 else cur = trav_pop(st, sp, bound);
             }
             if (cur == TRAV_EMPTY) {

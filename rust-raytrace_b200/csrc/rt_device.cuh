@@ -225,8 +225,9 @@ RT_HD bool shadow_result(const Shadow& s, double range2) { return s.nan ? (range
 //                       itself, and the rounding error of the exact test's discriminant (which makes the scan "hit"
 //                       spheres inflated by up to min(E/2r_min, sqrt(E)), E = 64 eps S^2, S the magnitude of the
 //                       ORIGINAL origin) -- are covered by widening every box by `pad`;
-//   relative errors  -- inv = fl32(1/d) and the FFMA rounding scale each slab distance by (1 +- 2^-23) -- are covered
-//                       by shrinking the entry distance and growing the exit distance by 2^-21.
+//   relative errors  -- inv = fl32(1/d), the f32 rounding of the per-ray slope and the FFMA rounding scale each slab
+//                       distance by (1 +- 2^-22) -- are covered by shrinking entry distances and growing exit distances
+//                       by 2^-21; the factor is folded into the per-ray plane constants (BoxRay32), not applied per box.
 // ---------------------------------------------------------------------------------------------------------
 #define RT_BVH_TSLACK 1.000000000001   // relative slack when a t of the exact test bounds the filter
 
@@ -238,12 +239,19 @@ struct TraverseCount {
 };
 
 struct BoxRay32 {
-    float ix, iy, iz;  // clamped reciprocal direction
-    float px, py, pz;  // (o' + pad) * inv
-    float mx, my, mz;  // (o' - pad) * inv
+    // slab distance of a lower plane v: v * sl - ol; of an upper plane: v * sh - oh.  On each axis the plane the ray
+    // enters through carries the factor (1 - 2^-21), the one it leaves through (1 + 2^-21) (relative slack, below).
+    float slx, sly, slz, olx, oly, olz;
+    float shx, shy, shz, ohx, ohy, ohz;
     double t0;         // ray parameter of the advanced origin o' = o + d * t0 (0 when o is inside the sphere bounds)
     bool enter;        // false: no sphere can be hit (non-finite ray, or the ray misses the bounds) -> skip the tree
 };
+RT_HD BoxRay32 boxray32_none() {
+    BoxRay32 b;
+    b.slx = b.sly = b.slz = b.olx = b.oly = b.olz = b.shx = b.shy = b.shz = b.ohx = b.ohy = b.ohz = 0.0f;
+    b.t0 = 0.0; b.enter = false;
+    return b;
+}
 
 RT_HD float safe_inv32(double d) {
     if (fabs(d) < 1e-30) return (float)copysign(1e30, d);
@@ -303,44 +311,43 @@ RT_HD BoxRay32 make_boxray32_t(const DeviceScene& sc, V3 o, V3 d) {
     const double s2 = fmax(fmax(fabs(oo.x), fabs(oo.y)), fabs(oo.z));
     const double S = s2 + sc.bvh_cmax;
     const double pad = S * 0x1.0p-20 + infl + (s + dm * b.t0) * 0x1.0p-50;
-    b.ix = safe_inv32(d.x); b.iy = safe_inv32(d.y); b.iz = safe_inv32(d.z);
-    if (!QNODES) {
-        b.px = (float)((oo.x + pad) * (double)b.ix); b.py = (float)((oo.y + pad) * (double)b.iy); b.pz = (float)((oo.z + pad) * (double)b.iz);
-        b.mx = (float)((oo.x - pad) * (double)b.ix); b.my = (float)((oo.y - pad) * (double)b.iy); b.mz = (float)((oo.z - pad) * (double)b.iz);
-    } else {
-        // grid form (see load_qnode).  Rounding a to f32 moves a plane by < 0.51 cells ((2^23 + q) * 2^-24), rounding P
-        // by < 0.51 cells (|P| < 2^24 a, o' being inside the bounds): 1.25 more cells of padding cover both.
-        const double oa[3] = {oo.x, oo.y, oo.z};
-        const float inv[3] = {b.ix, b.iy, b.iz};
-        float a32[3], pl[3], ph[3];
-        for (int a = 0; a < 3; a++) {
+    const double oa[3] = {oo.x, oo.y, oo.z};
+    const float inv[3] = {safe_inv32(d.x), safe_inv32(d.y), safe_inv32(d.z)};
+    float sl[3], ol[3], sh[3], oh[3];
+    for (int a = 0; a < 3; a++) {
+        const double iv = (double)inv[a];
+        const double kl = inv[a] > 0.0f ? 1.0 - 0x1.0p-21 : 1.0 + 0x1.0p-21;  // lower plane: entered when the ray runs upward
+        const double kh = inv[a] > 0.0f ? 1.0 + 0x1.0p-21 : 1.0 - 0x1.0p-21;
+        if (!QNODES) {
+            sl[a] = (float)(iv * kl); ol[a] = (float)((oa[a] + pad) * iv * kl);
+            sh[a] = (float)(iv * kh); oh[a] = (float)((oa[a] - pad) * iv * kh);
+        } else {
+            // grid form (see load_qnode).  Rounding the slope to f32 moves a plane by < 0.51 cells ((2^23 + q) * 2^-24),
+            // rounding the offset by < 0.51 cells (|offset| < 2^24 slope, o' being inside the bounds): 1.25 more cells
+            // of padding cover both.
             const double padq = pad + 1.25 * sc.q_cell[a];
-            a32[a] = (float)(sc.q_cell[a] * (double)inv[a]);
-            const double base = 8388608.0 * (double)a32[a];
-            pl[a] = (float)(base - (sc.q_org[a] - oa[a] - padq) * (double)inv[a]);
-            ph[a] = (float)(base - (sc.q_org[a] - oa[a] + padq) * (double)inv[a]);
+            sl[a] = (float)(sc.q_cell[a] * iv * kl);
+            sh[a] = (float)(sc.q_cell[a] * iv * kh);
+            ol[a] = (float)(8388608.0 * (double)sl[a] - (sc.q_org[a] - oa[a] - padq) * iv * kl);
+            oh[a] = (float)(8388608.0 * (double)sh[a] - (sc.q_org[a] - oa[a] + padq) * iv * kh);
         }
-        b.ix = a32[0]; b.iy = a32[1]; b.iz = a32[2];
-        b.px = pl[0]; b.py = pl[1]; b.pz = pl[2];
-        b.mx = ph[0]; b.my = ph[1]; b.mz = ph[2];
     }
+    b.slx = sl[0]; b.sly = sl[1]; b.slz = sl[2]; b.olx = ol[0]; b.oly = ol[1]; b.olz = ol[2];
+    b.shx = sh[0]; b.shy = sh[1]; b.shz = sh[2]; b.ohx = oh[0]; b.ohy = oh[1]; b.ohz = oh[2];
     return b;
 }
 RT_HD BoxRay32 make_boxray32(const DeviceScene& sc, V3 o, V3 d) {
     return sc.bvh_qnodes ? make_boxray32_t<true>(sc, o, d) : make_boxray32_t<false>(sc, o, d);
 }
 
-// conservative entry distance (>= 0, measured from the advanced origin) of the padded box if it can be hit within
-// [0, bound], else -1
-RT_HD float box_entry32(const BoxRay32& b, const float* lo, const float* hi, float bound) {
-    float ax = fmaf(lo[0], b.ix, -b.px), bx = fmaf(hi[0], b.ix, -b.mx);
-    float ay = fmaf(lo[1], b.iy, -b.py), by = fmaf(hi[1], b.iy, -b.my);
-    float az = fmaf(lo[2], b.iz, -b.pz), bz = fmaf(hi[2], b.iz, -b.mz);
-    float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
-    float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
-    tn *= (1.0f - 0x1.0p-21f);
-    tf *= (1.0f + 0x1.0p-21f);
-    return (tn <= tf && tn <= bound) ? tn : -1.0f;
+// can the padded box be hit within [0, bound]?  tn = conservative entry distance (>= 0, from the advanced origin)
+RT_HD bool box_hit32(const BoxRay32& b, const float* lo, const float* hi, float bound, float& tn) {
+    const float ax = fmaf(lo[0], b.slx, -b.olx), bx = fmaf(hi[0], b.shx, -b.ohx);
+    const float ay = fmaf(lo[1], b.sly, -b.oly), by = fmaf(hi[1], b.shy, -b.ohy);
+    const float az = fmaf(lo[2], b.slz, -b.olz), bz = fmaf(hi[2], b.shz, -b.ohz);
+    tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
+    const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
+    return tn <= tf && tn <= bound;
 }
 
 // ---- 32-byte nodes: box planes on the scene's 16-bit grid -------------------------------------------------
@@ -378,7 +385,7 @@ RT_HD BvhQNode quantise_node(const BvhNode& n, const double* org, const double* 
 //   ((org + q*cell) - (o' +- pad)) * inv  =  (2^23 + q) * (cell*inv)  +  ((org - (o' +- pad)) * inv - 2^23 * cell*inv),
 // so with the per-ray constants a = cell*inv and P = the last bracket it is one FFMA on the float 2^23 + q, whose
 // bit pattern is 0x4B000000 | q -- one byte permute per plane.  BoxRay32 holds (a, -P_lo, -P_hi) in place of
-// (inv, (o'+pad)*inv, (o'-pad)*inv) and box_entry32 is shared by both node formats.
+// (inv, (o'+pad)*inv, (o'-pad)*inv) and box_hit32 is shared by both node formats.
 #if defined(__CUDA_ARCH__)
 RT_HD BvhNode load_qnode(const BvhQNode* p) {
     uint32_t w0, w1, w2, w3, w4, w5, w6, w7;
@@ -461,20 +468,17 @@ RT_HD int32_t trav_descend(const DeviceScene& sc, const BoxRay32& br, int32_t cu
     while (cur >= 0 && max_steps-- > 0) {
         const BvhNode n = QNODES ? load_qnode(sc.bvh_qnodes + cur) : load_node(sc.bvh_nodes + cur);
         tc.nodes++;
-        const float t0 = box_entry32(br, n.lo0, n.hi0, bound);
-        const float t1 = box_entry32(br, n.lo1, n.hi1, bound);
-        if (t0 >= 0.0f && t1 >= 0.0f) {
-            const bool swap = t1 < t0;
-            const int32_t farc = swap ? n.c0 : n.c1;
-            if (sp < BVH_STACK) st.e[sp++] = trav_pack(farc, swap ? t0 : t1);
-            cur = swap ? n.c1 : n.c0;
-        } else if (t0 >= 0.0f) {
-            cur = n.c0;
-        } else if (t1 >= 0.0f) {
-            cur = n.c1;
-        } else {
-            cur = trav_pop(st, sp, bound);
-        }
+        float t0, t1;
+        const bool h0 = box_hit32(br, n.lo0, n.hi0, bound, t0);
+        const bool h1 = box_hit32(br, n.lo1, n.hi1, bound, t1);
+        // nearer hit child next, the other one postponed; selects instead of branches: the lanes of a warp take all
+        // four cases at once
+        const bool both = h0 && h1;
+        const bool second = h1 && (!h0 || t1 < t0);
+        const int32_t nearc = second ? n.c1 : n.c0;
+        if (both && sp < BVH_STACK) st.e[sp++] = trav_pack(second ? n.c0 : n.c1, second ? t0 : t1);
+        if (h0 || h1) cur = nearc;
+        else cur = trav_pop(st, sp, bound);
     }
     return cur;
 }
