@@ -198,10 +198,7 @@ cudaError_t bvh_build(cudaStream_t st, const SphereRec* sph, const int32_t* sph_
     BVH_CHECK(cudaMalloc(&out->obj, sizeof(int32_t) * n));
     out->n_nodes = n_nodes;
     double inv[3];
-    for (int a = 0; a < 3; a++) {
-        const double ext = chi[a] - clo[a];
-        inv[a] = ext > 0.0 ? 1.0 / ext : 0.0;
-    }
+    morton_scale(clo, chi, inv);
     const uint32_t T = 256;
     k_morton<<<(n_pow2 + T - 1) / T, T, 0, st>>>(sph, n, n_pow2, clo[0], clo[1], clo[2], inv[0], inv[1], inv[2], keys, idx);
     out->launches++;

@@ -11,6 +11,7 @@
 #pragma once
 #include <math.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "rt_types.h"
@@ -882,6 +883,22 @@ RT_HD uint64_t spread21(uint64_t v) {
     v = (v | (v << 4)) & 0x10C30C30C30C30C3ULL;
     v = (v | (v << 2)) & 0x1249249249249249ULL;
     return v;
+}
+// Scale of the Morton grid: the SAME step on all three axes (1 / longest centroid extent), so that the tree splits the
+// long axes of a flat scene first and its boxes stay near-cubical; per-axis scaling (RAYTRACE_B200_MORTON=axis, kept for
+// A/B runs) splits a 120 x 7 x 120 field as often in y as in x and z and yields pancake boxes.
+inline void morton_scale(const double* lo, const double* hi, double* inv_ext) {
+    double longest = 0.0;
+    for (int a = 0; a < 3; a++) {
+        const double ext = hi[a] - lo[a];
+        inv_ext[a] = ext > 0.0 ? 1.0 / ext : 0.0;
+        if (ext > longest) longest = ext;   // NaN / inf extents never win; their axis keeps inv = 0 or 1/inf = 0
+    }
+    const char* e = getenv("RAYTRACE_B200_MORTON");
+    if (e && !strcmp(e, "axis")) return;
+    if (longest > 0.0 && longest < (double)INFINITY)
+        for (int a = 0; a < 3; a++)
+            if (inv_ext[a] > 0.0) inv_ext[a] = 1.0 / longest;
 }
 RT_HD uint64_t morton63(double cx, double cy, double cz, const double* lo, const double* inv_ext) {
     double fx = (cx - lo[0]) * inv_ext[0], fy = (cy - lo[1]) * inv_ext[1], fz = (cz - lo[2]) * inv_ext[2];

@@ -50,10 +50,7 @@ void build_bvh(EmuScene& e) {
     const uint32_t n = (uint32_t)e.flat.sph.size();
     if (n == 0) return;
     double inv[3];
-    for (int a = 0; a < 3; a++) {
-        const double ext = e.flat.centroid_hi[a] - e.flat.centroid_lo[a];
-        inv[a] = ext > 0.0 ? 1.0 / ext : 0.0;
-    }
+    morton_scale(e.flat.centroid_lo, e.flat.centroid_hi, inv);
     std::vector<std::pair<uint64_t, uint32_t>> keyed(n);
     for (uint32_t i = 0; i < n; i++) keyed[i] = {morton63(e.flat.sph[i].cx, e.flat.sph[i].cy, e.flat.sph[i].cz, e.flat.centroid_lo, inv), i};
     std::sort(keyed.begin(), keyed.end());
