@@ -215,10 +215,10 @@ def roofline_for(stats_sum, steps, peak_gbs, peak_src, accel):
     rays_c = stats_sum["rays_primary"] + stats_sum["rays_secondary"]
     if cls == "closest":
         queue = rays_c * (R_CLOSEST + H_CLOSEST)
-        tree = stats_sum["bvh_nodes"]["closest"] * 64 + stats_sum["bvh_prims"]["closest"] * 32
+        tree = stats_sum["bvh_nodes"]["closest"] * stats_sum.get("node_bytes", 64) + stats_sum["bvh_prims"]["closest"] * 32
     elif cls == "shadow":
         queue = stats_sum["rays_shadow"] * R_SHADOW
-        tree = stats_sum["bvh_nodes"]["shadow"] * 64 + stats_sum["bvh_prims"]["shadow"] * 32
+        tree = stats_sum["bvh_nodes"]["shadow"] * stats_sum.get("node_bytes", 64) + stats_sum["bvh_prims"]["shadow"] * 32
     elif cls == "shade":
         queue = rays_c * R_SHADE_IN + stats_sum["rays_secondary"] * R_CHILD + stats_sum["rays_shadow"] * R_SHADOW_OUT
         tree = 0
@@ -232,7 +232,7 @@ def roofline_for(stats_sum, steps, peak_gbs, peak_src, accel):
             "peak_source": peak_src, "algorithmic_bytes_per_launch": queue / launches, "avg_launch_ms": ms / launches,
             "share_of_step": ms / max(1e-9, sum(stats_sum["class_ms"].values())),
             "class_ms_per_step": {k: v / steps for k, v in stats_sum["class_ms"].items()},
-            "tree_bytes_per_launch_L2": tree / launches,
+            "tree_bytes_per_launch_L2": tree / launches, "bvh_node_bytes": stats_sum.get("node_bytes", 0),
             "tree_gbs_L2": tree / (ms * 1e-3) / 1e9 if ms > 0 else 0.0,
             "note": "achieved = compulsory queue-record bytes of the dominant kernel / its device time; BVH node+leaf fetches "
                     "(tree_*) are served by L1/L2 and reported beside it"}
@@ -316,6 +316,7 @@ def run_ours(args):
         for k, v in st["class_ms"].items():
             acc["class_ms"][k] = acc["class_ms"].get(k, 0.0) + v
             acc["class_launches"][k] = acc["class_launches"].get(k, 0) + st["class_launches"][k]
+        acc["node_bytes"] = st["bvh_node_bytes"]
         for k in ("closest", "shadow"):
             acc["bvh_nodes"][k] += st["bvh_nodes_visited"][k]
             acc["bvh_prims"][k] += st["bvh_prims_tested"][k]

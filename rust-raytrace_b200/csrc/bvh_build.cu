@@ -178,11 +178,11 @@ __global__ void k_untile(const uint32_t* gathered, uint32_t* out, uint32_t heigh
 #define BVH_CHECK(x)                         \
     do {                                     \
         cudaError_t e_ = (x);                \
-        if (e_ != cudaSuccess) { bvh_free(out); cudaFree(keys); cudaFree(idx); cudaFree(child0); cudaFree(child1); cudaFree(pint); cudaFree(pleaf); cudaFree(flags); cudaFree(boxes); return e_; } \
+        if (e_ != cudaSuccess) { bvh_free(out, A); A.release(keys); A.release(idx); A.release(child0); A.release(child1); A.release(pint); A.release(pleaf); A.release(flags); A.release(boxes); return e_; } \
     } while (0)
 
 cudaError_t bvh_build(cudaStream_t st, const SphereRec* sph, const int32_t* sph_obj, uint32_t n, const double* clo, const double* chi,
-                      const double* q_org, const double* q_cell, BvhBuildResult* out) {
+                      const double* q_org, const double* q_cell, const DeviceAllocator& A, BvhBuildResult* out) {
     out->nodes = nullptr; out->qnodes = nullptr; out->sph = nullptr; out->obj = nullptr; out->n_nodes = 0; out->launches = 0;
     uint64_t* keys = nullptr; uint32_t* idx = nullptr;
     int32_t *child0 = nullptr, *child1 = nullptr, *pint = nullptr, *pleaf = nullptr;
@@ -191,11 +191,11 @@ cudaError_t bvh_build(cudaStream_t st, const SphereRec* sph, const int32_t* sph_
     uint32_t n_pow2 = BITONIC_ELEMS;
     while (n_pow2 < n) n_pow2 <<= 1;
     const uint32_t n_nodes = n > 1 ? n - 1 : 1;
-    BVH_CHECK(cudaMalloc(&keys, sizeof(uint64_t) * n_pow2));
-    BVH_CHECK(cudaMalloc(&idx, sizeof(uint32_t) * n_pow2));
-    BVH_CHECK(cudaMalloc(&out->nodes, sizeof(BvhNode) * n_nodes));
-    BVH_CHECK(cudaMalloc(&out->sph, sizeof(SphereRec) * n));
-    BVH_CHECK(cudaMalloc(&out->obj, sizeof(int32_t) * n));
+    BVH_CHECK(A.alloc((void**)&keys, sizeof(uint64_t) * n_pow2));
+    BVH_CHECK(A.alloc((void**)&idx, sizeof(uint32_t) * n_pow2));
+    BVH_CHECK(A.alloc((void**)&out->nodes, sizeof(BvhNode) * n_nodes));
+    BVH_CHECK(A.alloc((void**)&out->sph, sizeof(SphereRec) * n));
+    BVH_CHECK(A.alloc((void**)&out->obj, sizeof(int32_t) * n));
     out->n_nodes = n_nodes;
     double inv[3];
     morton_scale(clo, chi, inv);
@@ -220,21 +220,21 @@ cudaError_t bvh_build(cudaStream_t st, const SphereRec* sph, const int32_t* sph_
         k_single_leaf<<<1, 1, 0, st>>>(out->sph, out->nodes);
         out->launches++;
     } else {
-        BVH_CHECK(cudaMalloc(&child0, sizeof(int32_t) * n_nodes));
-        BVH_CHECK(cudaMalloc(&child1, sizeof(int32_t) * n_nodes));
-        BVH_CHECK(cudaMalloc(&pint, sizeof(int32_t) * n_nodes));
-        BVH_CHECK(cudaMalloc(&pleaf, sizeof(int32_t) * n));
-        BVH_CHECK(cudaMalloc(&flags, sizeof(uint32_t) * n_nodes));
-        BVH_CHECK(cudaMalloc(&boxes, sizeof(Box) * n_nodes));
+        BVH_CHECK(A.alloc((void**)&child0, sizeof(int32_t) * n_nodes));
+        BVH_CHECK(A.alloc((void**)&child1, sizeof(int32_t) * n_nodes));
+        BVH_CHECK(A.alloc((void**)&pint, sizeof(int32_t) * n_nodes));
+        BVH_CHECK(A.alloc((void**)&pleaf, sizeof(int32_t) * n));
+        BVH_CHECK(A.alloc((void**)&flags, sizeof(uint32_t) * n_nodes));
+        BVH_CHECK(A.alloc((void**)&boxes, sizeof(Box) * n_nodes));
         BVH_CHECK(cudaMemsetAsync(flags, 0, sizeof(uint32_t) * n_nodes, st));
         k_hierarchy<<<(n_nodes + T - 1) / T, T, 0, st>>>(keys, n, child0, child1, pint, pleaf);
         k_refit_pack<<<(n + T - 1) / T, T, 0, st>>>(out->sph, n, child0, child1, pint, pleaf, flags, boxes, out->nodes);
         out->launches += 2;
     }
     if (q_org && q_cell) {
-        if (!flags) BVH_CHECK(cudaMalloc(&flags, sizeof(uint32_t)));
+        if (!flags) BVH_CHECK(A.alloc((void**)&flags, sizeof(uint32_t)));
         uint32_t* off_grid = flags;  // the refit is done with its arrival flags (stream order): word 0 becomes the counter
-        BVH_CHECK(cudaMalloc(&out->qnodes, sizeof(BvhQNode) * n_nodes));
+        BVH_CHECK(A.alloc((void**)&out->qnodes, sizeof(BvhQNode) * n_nodes));
         BVH_CHECK(cudaMemsetAsync(off_grid, 0, sizeof(uint32_t), st));
         QuantGrid g;
         for (int a = 0; a < 3; a++) { g.org[a] = q_org[a]; g.cell[a] = q_cell[a]; }
@@ -243,18 +243,18 @@ cudaError_t bvh_build(cudaStream_t st, const SphereRec* sph, const int32_t* sph_
         uint32_t bad = 0;
         BVH_CHECK(cudaMemcpyAsync(&bad, off_grid, sizeof bad, cudaMemcpyDeviceToHost, st));
         BVH_CHECK(cudaStreamSynchronize(st));
-        if (bad) { cudaFree(out->qnodes); out->qnodes = nullptr; }   // a box off the grid: keep the 64-byte nodes
-        else { cudaFree(out->nodes); out->nodes = nullptr; }
+        if (bad) { A.release(out->qnodes); out->qnodes = nullptr; }   // a box off the grid: keep the 64-byte nodes
+        else { A.release(out->nodes); out->nodes = nullptr; }
     }
     BVH_CHECK(cudaStreamSynchronize(st));
     BVH_CHECK(cudaGetLastError());
-    cudaFree(keys); cudaFree(idx); cudaFree(child0); cudaFree(child1); cudaFree(pint); cudaFree(pleaf); cudaFree(flags); cudaFree(boxes);
+    A.release(keys); A.release(idx); A.release(child0); A.release(child1); A.release(pint); A.release(pleaf); A.release(flags); A.release(boxes);
     return cudaSuccess;
 }
 
-void bvh_free(BvhBuildResult* r) {
+void bvh_free(BvhBuildResult* r, const DeviceAllocator& A) {
     if (!r) return;
-    cudaFree(r->nodes); cudaFree(r->qnodes); cudaFree(r->sph); cudaFree(r->obj);
+    A.release(r->nodes); A.release(r->qnodes); A.release(r->sph); A.release(r->obj);
     r->nodes = nullptr; r->qnodes = nullptr; r->sph = nullptr; r->obj = nullptr; r->n_nodes = 0;
 }
 

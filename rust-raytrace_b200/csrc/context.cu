@@ -99,6 +99,33 @@ private:
 };
 DeviceCache g_cache;
 
+// pinned read-back blocks (one Counters record per context), recycled for the same reason
+class PinnedPool {
+public:
+    cudaError_t get(Counters** p) {
+        {
+            std::lock_guard<std::mutex> g(m_);
+            if (!free_.empty()) { *p = free_.back(); free_.pop_back(); return cudaSuccess; }
+        }
+        return cudaMallocHost((void**)p, sizeof(Counters));
+    }
+    void put(Counters* p) {
+        if (!p) return;
+        std::lock_guard<std::mutex> g(m_);
+        free_.push_back(p);
+    }
+    void trim() {
+        std::lock_guard<std::mutex> g(m_);
+        for (Counters* p : free_) cudaFreeHost(p);
+        free_.clear();
+    }
+private:
+    std::mutex m_;
+    std::vector<Counters*> free_;
+};
+PinnedPool g_pinned;
+const DeviceAllocator g_cache_allocator = {[](void** p, size_t bytes) { return g_cache.alloc(p, bytes); }, [](void* p) { g_cache.release(p); }};
+
 template <typename T>
 int dev_alloc(T** p, size_t count) {
     *p = nullptr;
@@ -127,7 +154,7 @@ struct DeviceSceneHolder {
     void release() {
         for (void* p : allocs) g_cache.release(p);
         allocs.clear();
-        bvh_free(&bvh);
+        bvh_free(&bvh, g_cache_allocator);
     }
     template <typename T>
     int up(const std::vector<T>& v, const T** out) {
@@ -170,7 +197,7 @@ struct DeviceSceneHolder {
             CUDA_TRY(cudaEventCreate(&e0));
             CUDA_TRY(cudaEventCreate(&e1));
             CUDA_TRY(cudaEventRecord(e0, st));
-            cudaError_t e = bvh_build(st, ds.sph, ds.sph_obj, ds.n_spheres, clo, chi, f.quant ? f.q_org : nullptr, f.quant ? f.q_cell : nullptr, &bvh);
+            cudaError_t e = bvh_build(st, ds.sph, ds.sph_obj, ds.n_spheres, clo, chi, f.quant ? f.q_org : nullptr, f.quant ? f.q_cell : nullptr, g_cache_allocator, &bvh);
             if (e != cudaSuccess) { set_error(std::string("bvh_build: ") + cudaGetErrorString(e)); return RT_ERR_CUDA; }
             CUDA_TRY(cudaEventRecord(e1, st));
             CUDA_TRY(cudaEventSynchronize(e1));
@@ -274,7 +301,7 @@ struct rt_context {
         cudaSetDevice(device);
         if (stream) cudaStreamSynchronize(stream);  // blocks go back to the cache: nothing may still be using them
         for (void* p : allocs) g_cache.release(p);
-        if (counters_host) cudaFreeHost(counters_host);
+        g_pinned.put(counters_host);
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
         for (cudaEvent_t e : prof_events) cudaEventDestroy(e);
@@ -333,7 +360,7 @@ int process_level(rt_context* c, uint32_t d, uint32_t n) {
 
 extern "C" {
 
-void rt_release_cached_memory(void) { g_cache.trim(); }
+void rt_release_cached_memory(void) { g_cache.trim(); g_pinned.trim(); }
 
 int rt_device_count(void) {
     int n = 0;
@@ -389,7 +416,7 @@ int rt_context_create(const rt_scene* s, const rt_render_opts* o, rt_context** o
     c->allocs.push_back(c->framebuffer);
     if ((rc = dev_alloc(&c->counters, 1)) != RT_OK) return fail(rc);
     c->allocs.push_back(c->counters);
-    if (cudaMallocHost((void**)&c->counters_host, sizeof(Counters)) != cudaSuccess) { set_error("cudaMallocHost failed"); return fail(RT_ERR_CUDA); }
+    if (g_pinned.get(&c->counters_host) != cudaSuccess) { set_error("cudaMallocHost failed"); return fail(RT_ERR_CUDA); }
     if (cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess) { set_error("cudaEventCreate failed"); return fail(RT_ERR_CUDA); }
     std::memset(&c->stats, 0, sizeof c->stats);
     c->stats.bvh_build_ms = c->scene.bvh_ms;

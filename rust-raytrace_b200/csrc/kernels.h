@@ -47,6 +47,11 @@ const KernelTable* kernels_strict();
 const KernelTable* kernels_fast();
 
 // mode-independent kernels (bvh_build.cu)
+// where the build takes its device memory from (context.cu passes its allocation cache; release(nullptr) is a no-op)
+struct DeviceAllocator {
+    cudaError_t (*alloc)(void** p, size_t bytes);
+    void (*release)(void* p);
+};
 struct BvhBuildResult {
     BvhNode* nodes;       // [n_nodes]; null when qnodes is set
     BvhQNode* qnodes;     // [n_nodes] 32-byte grid form, when asked for and every box fits the grid
@@ -59,8 +64,8 @@ struct BvhBuildResult {
 // Morton codes -> bitonic sort -> Karras hierarchy -> bottom-up refit -> packed f32 child boxes.
 // q_org/q_cell non-null: also pack the nodes on that grid (rt_types.h BvhQNode) and drop the 64-byte form.
 cudaError_t bvh_build(cudaStream_t, const SphereRec* sph, const int32_t* sph_obj, uint32_t n, const double* centroid_lo, const double* centroid_hi,
-                      const double* q_org, const double* q_cell, BvhBuildResult* out);
-void bvh_free(BvhBuildResult* r);
+                      const double* q_org, const double* q_cell, const DeviceAllocator& A, BvhBuildResult* out);
+void bvh_free(BvhBuildResult* r, const DeviceAllocator& A);
 
 // de-interleave row bands after the framebuffer all-gather (rank-major input)
 void launch_untile(cudaStream_t, const uint32_t* gathered, uint32_t* out, uint32_t height, uint32_t words_per_row, uint32_t band_rows, uint32_t world,
