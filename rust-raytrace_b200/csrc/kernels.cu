@@ -490,7 +490,10 @@ __global__ void __launch_bounds__(HEAVY_THREADS) k_heavy_scan(const __grid_const
 // ---------------------------------------------------------------------------------------------------------
 // k_shade
 // ---------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(SHADE_THREADS) k_shade(const __grid_constant__ DeviceScene sc, const __grid_constant__ FrameParams fp, RayQueue in,
+#ifndef RT_SHADE_MIN_BLOCKS
+#define RT_SHADE_MIN_BLOCKS 3
+#endif
+__global__ void __launch_bounds__(SHADE_THREADS, RT_SHADE_MIN_BLOCKS) k_shade(const __grid_constant__ DeviceScene sc, const __grid_constant__ FrameParams fp, RayQueue in,
                                                          uint32_t first, uint32_t n, RayQueue out, uint32_t* out_count, ShadowQueue sq,
                                                          uint32_t* sq_count, uint32_t* overflow, double* accum, int32_t* ids) {
     const uint32_t li = blockIdx.x * SHADE_THREADS + threadIdx.x;
@@ -511,12 +514,31 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(const __grid_constant__
         const C3 add = shade_begin(sc, fp, o, d, T, in.sig[i], in.key[i], depth, hid, in.hit_t[i], s);
         accum_add(accum, pixel, add);
     }
-    // light loop: uniform trip count, per-lane predicate
+    // Queue slots for everything this warp will emit are reserved up front, one atomic per queue (both in flight
+    // together, their ~1 us round trip overlapped with the light arithmetic) instead of one per light and child slot.
+    // Every lit hit casts a shadow ray at every light (src/scene.rs:117-155 tests occlusion only), so the count is known.
+    const unsigned FULL = 0xFFFFFFFFu;
+    const int lane = threadIdx.x & 31;
+    const unsigned below = (1u << lane) - 1u;
+    const bool lit = s.alive && s.lit;
+    const unsigned lit_m = __ballot_sync(FULL, lit);
+    const uint32_t n_lit = (uint32_t)__popc(lit_m);
+    uint32_t n_child = 0;
+    for (uint32_t k = 0; k < (uint32_t)sc.max_children; k++) n_child += (uint32_t)__popc(__ballot_sync(FULL, shade_child_wanted(s, k)));
+    uint32_t sbase = 0, cbase = 0;
+    if (lane == 0) {
+        if (n_lit * sc.n_lights) sbase = atomicAdd(sq_count, n_lit * sc.n_lights);
+        if (n_child) cbase = atomicAdd(out_count, n_child);
+    }
+    sbase = __shfl_sync(FULL, sbase, 0);
+    cbase = __shfl_sync(FULL, cbase, 0);
+    // light loop: light-major slots, so the lanes of a warp store side by side and rays to one light stay together
+    const uint32_t lit_rank = (uint32_t)__popc(lit_m & below);
     for (uint32_t li2 = 0; li2 < sc.n_lights; li2++) {
         ShadowRay sr;
-        const bool want = shade_light(sc, s, li2, sr);
-        const uint32_t slot = warp_append(want, sq_count, sq.cap, overflow);
-        if (slot != 0xFFFFFFFFu) {
+        if (shade_light(sc, s, li2, sr)) {
+            const uint32_t slot = sbase + li2 * n_lit + lit_rank;
+            if (slot >= sq.cap) { *overflow = 1u; continue; }
             sq.ox[slot] = sr.o.x; sq.oy[slot] = sr.o.y; sq.oz[slot] = sr.o.z;
             sq.dx[slot] = sr.d.x; sq.dy[slot] = sr.d.y; sq.dz[slot] = sr.d.z;
             sq.r2[slot] = sr.range2;
@@ -528,16 +550,18 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(const __grid_constant__
     for (uint32_t k = 0; k < (uint32_t)sc.max_children; k++) {
         ChildRay cr;
         const bool want = shade_child(sc, s, k, cr);
-        const uint32_t slot = warp_append(want, out_count, out.cap, overflow);
-        if (slot != 0xFFFFFFFFu) {
-            out.ox[slot] = cr.o.x; out.oy[slot] = cr.o.y; out.oz[slot] = cr.o.z;
-            out.dx[slot] = cr.d.x; out.dy[slot] = cr.d.y; out.dz[slot] = cr.d.z;
-            out.tr[slot] = cr.T.r; out.tg[slot] = cr.T.g; out.tb[slot] = cr.T.b;
-            out.sig[slot] = cr.sig;
-            out.key[slot] = cr.key;
-            out.pixel[slot] = pixel;
-            out.meta[slot] = depth + 1u;
-        }
+        const unsigned m = __ballot_sync(FULL, want);
+        const uint32_t slot = cbase + (uint32_t)__popc(m & below);
+        cbase += (uint32_t)__popc(m);
+        if (!want) continue;
+        if (slot >= out.cap) { *overflow = 1u; continue; }
+        out.ox[slot] = cr.o.x; out.oy[slot] = cr.o.y; out.oz[slot] = cr.o.z;
+        out.dx[slot] = cr.d.x; out.dy[slot] = cr.d.y; out.dz[slot] = cr.d.z;
+        out.tr[slot] = cr.T.r; out.tg[slot] = cr.T.g; out.tb[slot] = cr.T.b;
+        out.sig[slot] = cr.sig;
+        out.key[slot] = cr.key;
+        out.pixel[slot] = pixel;
+        out.meta[slot] = depth + 1u;
     }
 }
 

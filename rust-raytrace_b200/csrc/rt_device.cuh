@@ -789,6 +789,15 @@ RT_HD bool shade_light(const DeviceScene& sc, const ShadeCtx& s, uint32_t li, Sh
     return true;
 }
 
+// does child slot k of this hit spawn a ray?  (the cheap part of shade_child: lets the kernel reserve queue slots for
+// all children of a warp with one atomic before doing the arithmetic)
+RT_HD bool shade_child_wanted(const ShadeCtx& s, uint32_t k) {
+    if (!s.alive) return false;
+    if (s.kind == MAT_INDIRECT) return s.lit && k < s.samples;
+    if (k == 0) return s.specular;
+    return k == 1 && s.kind == MAT_TRANSPARENT && s.has_refr;
+}
+
 // child slot k of this hit: 0 = reflection (Phong/Fresnel/Transparent), 1 = refraction (Transparent),
 // k < samples = hemisphere sample k (IndirectPhong).  Returns false when the slot spawns nothing.
 RT_HD bool shade_child(const DeviceScene& sc, const ShadeCtx& s, uint32_t k, ChildRay& out) {
