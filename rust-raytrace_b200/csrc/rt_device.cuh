@@ -226,9 +226,10 @@ RT_HD bool shadow_result(const Shadow& s, double range2) { return s.nan ? (range
 //                       itself, and the rounding error of the exact test's discriminant (which makes the scan "hit"
 //                       spheres inflated by up to min(E/2r_min, sqrt(E)), E = 64 eps S^2, S the magnitude of the
 //                       ORIGINAL origin) -- are covered by widening every box by `pad`;
-//   relative errors  -- inv = fl32(1/d), the f32 rounding of the per-ray slope and the FFMA rounding scale each slab
-//                       distance by (1 +- 2^-22) -- are covered by shrinking entry distances and growing exit distances
-//                       by 2^-21; the factor is folded into the per-ray plane constants (BoxRay32), not applied per box.
+//   relative errors  -- inv = fl32(1/d), the f32 rounding of the per-ray slope and the FFMA rounding scale a slab distance
+//                       by (1 +- 3*2^-24).  A slab distance times |d| is the displacement from o' to the plane along that
+//                       axis, at most 2S because o' lies inside the bounds: the error is at most 6*2^-24 S in space, and
+//                       is covered by the same pad (S * 2^-20) -- no per-box slack multiplications.
 // ---------------------------------------------------------------------------------------------------------
 #define RT_BVH_TSLACK 1.000000000001   // relative slack when a t of the exact test bounds the filter
 
@@ -240,23 +241,21 @@ struct TraverseCount {
 };
 
 struct BoxRay32 {
-    // slab distance of a lower plane v: v * sl - ol; of an upper plane: v * sh - oh.  On each axis the plane the ray
-    // enters through carries the factor (1 - 2^-21), the one it leaves through (1 + 2^-21) (relative slack, below).
-    float slx, sly, slz, olx, oly, olz;
-    float shx, shy, shz, ohx, ohy, ohz;
+    // slab distance of a box plane at coordinate v: v * s - off, with one slope per axis and two offsets:
+    //   f32 nodes : a = offset of lower planes ((o' + pad) * inv), b = offset of upper planes ((o' - pad) * inv);
+    //   grid nodes: a = offset of the plane the ray ENTERS through, b = of the plane it LEAVES through, and sn* / sf*
+    //               are the byte-permute selectors that pick that plane's 16-bit coordinate out of the node word.
+    float sx, sy, sz, ax, ay, az, bx, by, bz;
+    uint32_t snx, sny, snz, sfx, sfy, sfz;
     double t0;         // ray parameter of the advanced origin o' = o + d * t0 (0 when o is inside the sphere bounds)
     bool enter;        // false: no sphere can be hit (non-finite ray, or the ray misses the bounds) -> skip the tree
 };
 RT_HD BoxRay32 boxray32_none() {
     BoxRay32 b;
-    b.slx = b.sly = b.slz = b.olx = b.oly = b.olz = b.shx = b.shy = b.shz = b.ohx = b.ohy = b.ohz = 0.0f;
+    b.sx = b.sy = b.sz = b.ax = b.ay = b.az = b.bx = b.by = b.bz = 0.0f;
+    b.snx = b.sny = b.snz = b.sfx = b.sfy = b.sfz = 0u;
     b.t0 = 0.0; b.enter = false;
     return b;
-}
-
-RT_HD float safe_inv32(double d) {
-    if (fabs(d) < 1e-30) return (float)copysign(1e30, d);
-    return (float)(1.0 / d);
 }
 
 #if defined(__CUDA_ARCH__)
@@ -283,12 +282,22 @@ RT_HD BoxRay32 make_boxray32_t(const DeviceScene& sc, V3 o, V3 d) {
     b.t0 = 0.0;
     const double St = s + sc.bvh_cmax;
     const double E = 64.0 * 2.220446049250313e-16 * St * St;  // bound on the rounding error of the discriminant, in r^2 units
-    const double infl = fmin(E / (2.0 * sc.bvh_rmin), sqrt(E));
+    // min(E / 2 r_min, sqrt(E)) without a division or a square root: sqrt(64 * 2^-52 * St^2) = 2^-23 * St, and
+    // bvh_inv2rmin = 0.5 / r_min rounded up on the host
+    const double infl = fmin(E * sc.bvh_inv2rmin, St * (0x1.0p-23 * (1.0 + 0x1.0p-50)));
+    // one reciprocal per axis serves the advance and (rounded to f32) the filter
+    const double da[3] = {d.x, d.y, d.z};
+    double rcp[3];
+    float inv[3];
+    for (int a = 0; a < 3; a++) {
+        rcp[a] = fabs(da[a]) < 1e-300 ? 0.0 : 1.0 / da[a];
+        inv[a] = fabs(da[a]) < 1e-30 ? (float)copysign(1e30, da[a]) : (float)rcp[a];
+    }
     V3 oo = o;
     if (b.enter) {
         // f64 slab test against the sphere bounds grown by the inflation: where does the ray enter them?
         const double m = infl + St * 0x1.0p-40;
-        const double oa[3] = {o.x, o.y, o.z}, da[3] = {d.x, d.y, d.z};
+        const double oa[3] = {o.x, o.y, o.z};
         double te = 0.0, tx = (double)INFINITY;
         bool miss = false;
         for (int a = 0; a < 3; a++) {
@@ -296,7 +305,7 @@ RT_HD BoxRay32 make_boxray32_t(const DeviceScene& sc, V3 o, V3 d) {
             if (fabs(da[a]) < 1e-300) {
                 if (oa[a] < lo || oa[a] > hi) miss = true;
             } else {
-                double t1 = (lo - oa[a]) / da[a], t2 = (hi - oa[a]) / da[a];
+                double t1 = (lo - oa[a]) * rcp[a], t2 = (hi - oa[a]) * rcp[a];  // within 2 ulp of the quotients; slack below is 2^-40
                 if (t1 > t2) { const double w = t1; t1 = t2; t2 = w; }
                 if (t1 > te) te = t1;
                 if (t2 < tx) tx = t2;
@@ -313,28 +322,31 @@ RT_HD BoxRay32 make_boxray32_t(const DeviceScene& sc, V3 o, V3 d) {
     const double S = s2 + sc.bvh_cmax;
     const double pad = S * 0x1.0p-20 + infl + (s + dm * b.t0) * 0x1.0p-50;
     const double oa[3] = {oo.x, oo.y, oo.z};
-    const float inv[3] = {safe_inv32(d.x), safe_inv32(d.y), safe_inv32(d.z)};
-    float sl[3], ol[3], sh[3], oh[3];
+    float sl[3], fa[3], fb[3];
+    uint32_t sn[3] = {0u, 0u, 0u}, sf[3] = {0u, 0u, 0u};
     for (int a = 0; a < 3; a++) {
         const double iv = (double)inv[a];
-        const double kl = inv[a] > 0.0f ? 1.0 - 0x1.0p-21 : 1.0 + 0x1.0p-21;  // lower plane: entered when the ray runs upward
-        const double kh = inv[a] > 0.0f ? 1.0 + 0x1.0p-21 : 1.0 - 0x1.0p-21;
         if (!QNODES) {
-            sl[a] = (float)(iv * kl); ol[a] = (float)((oa[a] + pad) * iv * kl);
-            sh[a] = (float)(iv * kh); oh[a] = (float)((oa[a] - pad) * iv * kh);
+            sl[a] = inv[a];
+            fa[a] = (float)((oa[a] + pad) * iv);
+            fb[a] = (float)((oa[a] - pad) * iv);
         } else {
-            // grid form (see load_qnode).  Rounding the slope to f32 moves a plane by < 0.51 cells ((2^23 + q) * 2^-24),
-            // rounding the offset by < 0.51 cells (|offset| < 2^24 slope, o' being inside the bounds): 1.25 more cells
-            // of padding cover both.
-            const double padq = pad + 1.25 * sc.q_cell[a];
-            sl[a] = (float)(sc.q_cell[a] * iv * kl);
-            sh[a] = (float)(sc.q_cell[a] * iv * kh);
-            ol[a] = (float)(8388608.0 * (double)sl[a] - (sc.q_org[a] - oa[a] - padq) * iv * kl);
-            oh[a] = (float)(8388608.0 * (double)sh[a] - (sc.q_org[a] - oa[a] + padq) * iv * kh);
+            // grid form (see qplane).  The 2^23 * slope term of the offset is built from the ROUNDED slope, so it cancels
+            // exactly in the FFMA; what is left is the rounding of the offset itself, < 0.51 cells (|offset| <
+            // (2^23 + 2^16) slope, o' being inside the bounds): 0.75 more cells of padding.
+            const double padq = pad + 0.75 * sc.q_cell[a];
+            const bool up = inv[a] > 0.0f;  // the ray runs upward on this axis: it enters boxes through their lower plane
+            sl[a] = (float)(sc.q_cell[a] * iv);
+            const double base = 8388608.0 * (double)sl[a];
+            const double lo_off = base - (sc.q_org[a] - oa[a] - padq) * iv, hi_off = base - (sc.q_org[a] - oa[a] + padq) * iv;
+            fa[a] = (float)(up ? lo_off : hi_off);
+            fb[a] = (float)(up ? hi_off : lo_off);
+            sn[a] = up ? 0x7610u : 0x7632u;  // node word = lower | upper << 16 (BvhQNode)
+            sf[a] = up ? 0x7632u : 0x7610u;
         }
     }
-    b.slx = sl[0]; b.sly = sl[1]; b.slz = sl[2]; b.olx = ol[0]; b.oly = ol[1]; b.olz = ol[2];
-    b.shx = sh[0]; b.shy = sh[1]; b.shz = sh[2]; b.ohx = oh[0]; b.ohy = oh[1]; b.ohz = oh[2];
+    b.sx = sl[0]; b.sy = sl[1]; b.sz = sl[2]; b.ax = fa[0]; b.ay = fa[1]; b.az = fa[2]; b.bx = fb[0]; b.by = fb[1]; b.bz = fb[2];
+    b.snx = sn[0]; b.sny = sn[1]; b.snz = sn[2]; b.sfx = sf[0]; b.sfy = sf[1]; b.sfz = sf[2];
     return b;
 }
 RT_HD BoxRay32 make_boxray32(const DeviceScene& sc, V3 o, V3 d) {
@@ -343,11 +355,11 @@ RT_HD BoxRay32 make_boxray32(const DeviceScene& sc, V3 o, V3 d) {
 
 // can the padded box be hit within [0, bound]?  tn = conservative entry distance (>= 0, from the advanced origin)
 RT_HD bool box_hit32(const BoxRay32& b, const float* lo, const float* hi, float bound, float& tn) {
-    const float ax = fmaf(lo[0], b.slx, -b.olx), bx = fmaf(hi[0], b.shx, -b.ohx);
-    const float ay = fmaf(lo[1], b.sly, -b.oly), by = fmaf(hi[1], b.shy, -b.ohy);
-    const float az = fmaf(lo[2], b.slz, -b.olz), bz = fmaf(hi[2], b.shz, -b.ohz);
-    tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
-    const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
+    const float lx = fmaf(lo[0], b.sx, -b.ax), hx = fmaf(hi[0], b.sx, -b.bx);
+    const float ly = fmaf(lo[1], b.sy, -b.ay), hy = fmaf(hi[1], b.sy, -b.by);
+    const float lz = fmaf(lo[2], b.sz, -b.az), hz = fmaf(hi[2], b.sz, -b.bz);
+    tn = fmaxf(fmaxf(fminf(lx, hx), fminf(ly, hy)), fmaxf(fminf(lz, hz), 0.0f));
+    const float tf = fminf(fminf(fmaxf(lx, hx), fmaxf(ly, hy)), fmaxf(lz, hz));
     return tn <= tf && tn <= bound;
 }
 
@@ -372,48 +384,53 @@ RT_HD uint16_t quant_hi(float v, double org, double cell, bool& ok) {
 }
 RT_HD BvhQNode quantise_node(const BvhNode& n, const double* org, const double* cell, bool& ok) {
     BvhQNode o;
-    for (int a = 0; a < 3; a++) {
-        o.q[a] = quant_lo(n.lo0[a], org[a], cell[a], ok);
-        o.q[3 + a] = quant_hi(n.hi0[a], org[a], cell[a], ok);
-        o.q[6 + a] = quant_lo(n.lo1[a], org[a], cell[a], ok);
-        o.q[9 + a] = quant_hi(n.hi1[a], org[a], cell[a], ok);
+    for (int a = 0; a < 3; a++) {  // per child and axis: lower plane in the low half-word, upper plane in the high one
+        o.q[2 * a] = quant_lo(n.lo0[a], org[a], cell[a], ok);
+        o.q[2 * a + 1] = quant_hi(n.hi0[a], org[a], cell[a], ok);
+        o.q[6 + 2 * a] = quant_lo(n.lo1[a], org[a], cell[a], ok);
+        o.q[6 + 2 * a + 1] = quant_hi(n.hi1[a], org[a], cell[a], ok);
     }
     o.c0 = n.c0; o.c1 = n.c1;
     return o;
 }
 
 // The filter never decodes a grid coordinate: a plane at org + q*cell has slab distance
-//   ((org + q*cell) - (o' +- pad)) * inv  =  (2^23 + q) * (cell*inv)  +  ((org - (o' +- pad)) * inv - 2^23 * cell*inv),
-// so with the per-ray constants a = cell*inv and P = the last bracket it is one FFMA on the float 2^23 + q, whose
-// bit pattern is 0x4B000000 | q -- one byte permute per plane.  BoxRay32 holds (a, -P_lo, -P_hi) in place of
-// (inv, (o'+pad)*inv, (o'-pad)*inv) and box_hit32 is shared by both node formats.
+//   ((org + q*cell) - (o' +- pad)) * inv  =  (2^23 + q) * (cell*inv)  -  (2^23 * cell*inv - (org - (o' +- pad)) * inv),
+// so with the per-ray slope cell*inv and the bracket as offset it is one FFMA on the float 2^23 + q, whose bit pattern
+// is 0x4B000000 | q -- one byte permute of the node word.  The permute's selector also picks WHICH plane (lower or upper
+// half-word), so the ray's direction signs are spent there and the slab test needs no min/max per axis:
+// entry = max of the three entry planes, exit = min of the three exit planes.
+struct QNodeWords { uint32_t w[8]; };  // child 0: x y z | child 1: x y z | c0 c1
 #if defined(__CUDA_ARCH__)
-RT_HD BvhNode load_qnode(const BvhQNode* p) {
-    uint32_t w0, w1, w2, w3, w4, w5, w6, w7;
+RT_HD QNodeWords load_qnode(const BvhQNode* p) {
+    QNodeWords n;
     asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                 : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3), "=r"(w4), "=r"(w5), "=r"(w6), "=r"(w7) : "l"(p));
-    const uint32_t K = 0x4B000000u;
-    BvhNode n;
-    n.lo0[0] = __uint_as_float(__byte_perm(w0, K, 0x7610)); n.lo0[1] = __uint_as_float(__byte_perm(w0, K, 0x7632));
-    n.lo0[2] = __uint_as_float(__byte_perm(w1, K, 0x7610)); n.hi0[0] = __uint_as_float(__byte_perm(w1, K, 0x7632));
-    n.hi0[1] = __uint_as_float(__byte_perm(w2, K, 0x7610)); n.hi0[2] = __uint_as_float(__byte_perm(w2, K, 0x7632));
-    n.lo1[0] = __uint_as_float(__byte_perm(w3, K, 0x7610)); n.lo1[1] = __uint_as_float(__byte_perm(w3, K, 0x7632));
-    n.lo1[2] = __uint_as_float(__byte_perm(w4, K, 0x7610)); n.hi1[0] = __uint_as_float(__byte_perm(w4, K, 0x7632));
-    n.hi1[1] = __uint_as_float(__byte_perm(w5, K, 0x7610)); n.hi1[2] = __uint_as_float(__byte_perm(w5, K, 0x7632));
-    n.c0 = (int32_t)w6; n.c1 = (int32_t)w7;
+                 : "=r"(n.w[0]), "=r"(n.w[1]), "=r"(n.w[2]), "=r"(n.w[3]), "=r"(n.w[4]), "=r"(n.w[5]), "=r"(n.w[6]), "=r"(n.w[7]) : "l"(p));
     return n;
+}
+RT_HD float qplane(uint32_t word, uint32_t sel) {  // prmt directly: __byte_perm would mask the selector on every call
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(word), "r"(0x4B000000u), "r"(sel));
+    return __uint_as_float(r);
 }
 #else
-RT_HD BvhNode load_qnode(const BvhQNode* p) {
-    BvhNode n;
-    for (int a = 0; a < 3; a++) {
-        n.lo0[a] = (float)(8388608u + p->q[a]); n.hi0[a] = (float)(8388608u + p->q[3 + a]);
-        n.lo1[a] = (float)(8388608u + p->q[6 + a]); n.hi1[a] = (float)(8388608u + p->q[9 + a]);
-    }
-    n.c0 = p->c0; n.c1 = p->c1;
+RT_HD QNodeWords load_qnode(const BvhQNode* p) {
+    QNodeWords n;
+    memcpy(n.w, p, 32);
     return n;
 }
+RT_HD float qplane(uint32_t word, uint32_t sel) {  // the two selectors in use: 0x7610 lower, 0x7632 upper half-word
+    return (float)(8388608u + (sel == 0x7610u ? (word & 0xFFFFu) : (word >> 16)));
+}
 #endif
+RT_HD bool box_hit_q(const BoxRay32& b, uint32_t wx, uint32_t wy, uint32_t wz, float bound, float& tn) {
+    const float nx = fmaf(qplane(wx, b.snx), b.sx, -b.ax), fx = fmaf(qplane(wx, b.sfx), b.sx, -b.bx);
+    const float ny = fmaf(qplane(wy, b.sny), b.sy, -b.ay), fy = fmaf(qplane(wy, b.sfy), b.sy, -b.by);
+    const float nz = fmaf(qplane(wz, b.snz), b.sz, -b.az), fz = fmaf(qplane(wz, b.sfz), b.sz, -b.bz);
+    tn = fmaxf(fmaxf(nx, ny), fmaxf(nz, 0.0f));
+    const float tf = fminf(fminf(fx, fy), fz);
+    return tn <= tf && tn <= bound;
+}
 
 #if defined(__CUDA_ARCH__)
 // the 64-byte node in two 256-bit loads (sm_100 LDG.E.ENL2.256): a divergent node fetch costs the L1 data pipe one
@@ -467,17 +484,27 @@ template <bool QNODES>
 RT_HD int32_t trav_descend(const DeviceScene& sc, const BoxRay32& br, int32_t cur, float bound, TravStack& st, int& sp, TraverseCount& tc,
                            int max_steps = 0x7FFFFFFF) {
     while (cur >= 0 && max_steps-- > 0) {
-        const BvhNode n = QNODES ? load_qnode(sc.bvh_qnodes + cur) : load_node(sc.bvh_nodes + cur);
-        tc.nodes++;
         float t0, t1;
-        const bool h0 = box_hit32(br, n.lo0, n.hi0, bound, t0);
-        const bool h1 = box_hit32(br, n.lo1, n.hi1, bound, t1);
+        bool h0, h1;
+        int32_t c0, c1;
+        if (QNODES) {
+            const QNodeWords n = load_qnode(sc.bvh_qnodes + cur);
+            h0 = box_hit_q(br, n.w[0], n.w[1], n.w[2], bound, t0);
+            h1 = box_hit_q(br, n.w[3], n.w[4], n.w[5], bound, t1);
+            c0 = (int32_t)n.w[6]; c1 = (int32_t)n.w[7];
+        } else {
+            const BvhNode n = load_node(sc.bvh_nodes + cur);
+            h0 = box_hit32(br, n.lo0, n.hi0, bound, t0);
+            h1 = box_hit32(br, n.lo1, n.hi1, bound, t1);
+            c0 = n.c0; c1 = n.c1;
+        }
+        tc.nodes++;
         // nearer hit child next, the other one postponed; selects instead of branches: the lanes of a warp take all
         // four cases at once
         const bool both = h0 && h1;
         const bool second = h1 && (!h0 || t1 < t0);
-        const int32_t nearc = second ? n.c1 : n.c0;
-        if (both && sp < BVH_STACK) st.e[sp++] = trav_pack(second ? n.c0 : n.c1, second ? t0 : t1);
+        const int32_t nearc = second ? c1 : c0;
+        if (both && sp < BVH_STACK) st.e[sp++] = trav_pack(second ? c0 : c1, second ? t0 : t1);
         if (h0 || h1) cur = nearc;
         else cur = trav_pop(st, sp, bound);
     }

@@ -103,6 +103,7 @@ struct DeviceScene {
     uint32_t _pad0;
     double bvh_cmax;  // max over spheres of (|c|_inf + r): scale term of the per-ray box padding
     double bvh_rmin;  // min radius
+    double bvh_inv2rmin;  // 0.5 / bvh_rmin, rounded up
     double bvh_lo[3], bvh_hi[3];  // bounds of all sphere boxes (f64): rays are advanced to this box before the f32 filter
     const BvhQNode* bvh_qnodes;   // non-null: traverse these instead of bvh_nodes
     double q_org[3], q_cell[3];   // the grid of bvh_qnodes
