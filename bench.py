@@ -238,6 +238,22 @@ def roofline_for(stats_sum, steps, peak_gbs, peak_src, accel):
                     "(tree_*) are served by L1/L2 and reported beside it"}
 
 
+def add_ncu_traffic(roof, workload, world):
+    """roofline.traffic = DRAM bytes (read + write) of ONE launch of the dominant kernel from the committed ncu --set full
+    capture of this workload (profiles/ncu_traffic.json, written from profiles/*_ncu_<kernel>.txt); null when there is no
+    capture for this workload / kernel / world size.  bench.py never runs under a profiler itself."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            t = json.load(f)
+        k = t["kernels"].get(roof["kernel"])
+        if world == 1 and t.get("workload") == workload and k:
+            roof["traffic"] = k["dram_bytes_read"] + k["dram_bytes_write"]
+            roof["traffic_source"] = k["source"]
+    except (OSError, ValueError, KeyError):
+        pass
+    return roof
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -412,7 +428,7 @@ def main():
                 "wall_ms_per_step": wall_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "f64", "fp_mode": args.fp, "data": "synthetic", "config": workload_config(name, R["w"], R["h"], R["aa"], R["desc"]),
                 "rays_per_step": rays_all / args.steps, "gpu_launches": launches_all, "clocks": R["clocks"],
-                "roofline": roofline_for(acc, args.steps, peak, peak_src, WORKLOADS[name]["accel"]),
+                "roofline": add_ncu_traffic(roofline_for(acc, args.steps, peak, peak_src, WORKLOADS[name]["accel"]), name, world),
                 "bvh_build_ms": R["ctx"].create_stats["bvh_build_ms"]}
         if e2e_val is not None:
             line["e2e"] = {"value": e2e_val, "unit": "Mrays/s", "ms_per_step": e2e_ms, "h2d_bytes_per_step": scene_h2d_bytes(R["desc"]),

@@ -243,7 +243,7 @@ __device__ __forceinline__ uint32_t warp_fetch(unsigned idle_mask, uint32_t* cur
 }
 
 #ifndef RT_FETCH_MIN_IDLE
-#define RT_FETCH_MIN_IDLE 8
+#define RT_FETCH_MIN_IDLE 16
 #endif
 #ifndef RT_DESCEND_STEPS
 #define RT_DESCEND_STEPS 16  // walk at most this many nodes before looking at the warp again (sweep: profiles/r01_v5_sweep.md)
