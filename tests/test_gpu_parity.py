@@ -112,6 +112,31 @@ def test_intersect_far_origins(gpu, orc, scenes, accel):
     assert (rid[:n] > 0).mean() > 0.2
 
 
+@pytest.mark.parametrize("nodes,morton", [("q16", "cubic"), ("f32", "cubic"), ("q16", "axis")])
+def test_bvh_node_formats_and_morton_grids(gpu, orc, scenes, nodes, morton, monkeypatch):
+    """the 32-byte grid nodes, the 64-byte f32 nodes and either Morton scaling are only different conservative filters /
+    different trees in front of the same exact test: ids, t, normals bit-identical, a whole frame byte-identical in ids"""
+    monkeypatch.setenv("RAYTRACE_B200_BVH_NODES", nodes)
+    monkeypatch.setenv("RAYTRACE_B200_MORTON", morton)
+    desc = scenes.random_spheres(8000, 13, 50.0, 320, 200)
+    sc = gpu.Scene(desc)
+    rng = np.random.default_rng(9)
+    rays = _random_rays(rng, 100_000, 55.0, 9.0)
+    rays[:3000, 3:] = np.array([0.0, 0.0, 1.0]) * rng.choice([-1.0, 1.0], 3000)[:, None]   # axis-parallel: clamped reciprocals
+    rays[3000:6000, 4] = 0.0
+    rays[6000:7000, 3] = 1e-35
+    ids, t, nrm = gpu.raytrace.intersect(sc, rays, accel=gpu.ACCEL_BVH)
+    rid, rt_, rn = orc.OracleScene(desc).trace_rays(rays)
+    assert np.array_equal(ids, rid) and np.array_equal(t, rt_) and np.array_equal(nrm, rn)
+    bvh = gpu.raytrace.render(sc, max_depth=4, seed=2, accel=gpu.ACCEL_BVH)
+    assert bvh.stats["bvh_node_bytes"] == (32 if nodes == "q16" else 64)
+    lin = gpu.raytrace.render(sc, max_depth=4, seed=2, accel=gpu.ACCEL_LINEAR)
+    assert np.array_equal(bvh.ids, lin.ids)
+    assert bvh.stats["rays_total"] == lin.stats["rays_total"] and bvh.stats["rays_shadow"] == lin.stats["rays_shadow"]
+    diff = np.abs(bvh.bgr.astype(np.int16) - lin.bgr.astype(np.int16))
+    assert diff.max() <= 1 and (diff == 0).mean() >= 0.999
+
+
 def test_intersect_edge_cases(gpu, orc):
     S = gpu.scene
     b = S.SceneBuilder()
