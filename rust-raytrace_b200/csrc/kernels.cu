@@ -262,13 +262,12 @@ constexpr int FETCH_MIN_IDLE = RT_FETCH_MIN_IDLE;  // refill when at least this 
 struct TravSmem {
     double ray[6][BVH_THREADS];  // origin, direction
     double aux[BVH_THREADS];     // closest: t of the best hit so far; shadow: squared range
-    double t0[BVH_THREADS];      // parameter of the advanced origin
-};
-__device__ __forceinline__ void park_ray(TravSmem& sm, V3 o, V3 d, double aux, double t0) {
+};                               // 7 KB + 1 KB the runtime reserves per CTA: 8 CTAs fit the 64 KB carve-out, 192 KB stay L1
+__device__ __forceinline__ void park_ray(TravSmem& sm, V3 o, V3 d, double aux) {
     const int t = threadIdx.x;
     sm.ray[0][t] = o.x; sm.ray[1][t] = o.y; sm.ray[2][t] = o.z;
     sm.ray[3][t] = d.x; sm.ray[4][t] = d.y; sm.ray[5][t] = d.z;
-    sm.aux[t] = aux; sm.t0[t] = t0;
+    sm.aux[t] = aux;
 }
 __device__ __forceinline__ RayQ parked_ray(const TravSmem& sm) {
     const int t = threadIdx.x;
@@ -288,6 +287,7 @@ __global__ void __launch_bounds__(BVH_THREADS, 8) k_closest_bvh(const __grid_con
     int32_t best_obj = 0x7FFFFFFF;  // the best hit's t is parked in sm.aux
     bool best_nan = false;
     float bound = 0.0f;
+    float t0f = 0.0f;  // t0 of the advanced origin rounded down: a later bound (t - t0f) can only be looser than (t - t0)
     uint32_t ray = 0;
     bool active = false, exhausted = false;
     while (true) {
@@ -303,14 +303,14 @@ __global__ void __launch_bounds__(BVH_THREADS, 8) k_closest_bvh(const __grid_con
                     walks = 0;
                     sp = 0;
                     cur = TRAV_EMPTY;
-                    double t0 = 0.0;
+                    t0f = 0.0f;
                     if (!best.nan && sc.n_spheres > 0) {
                         br = make_boxray32_t<QNODES>(sc, r.o, r.d);
-                        t0 = br.t0;
-                        if (br.enter) { cur = 0; bound = closest_bound32(best.t, t0); }
+                        t0f = f64_to_f32_down(br.t0);
+                        if (br.enter) { cur = 0; bound = closest_bound32(best.t, br.t0); }
                     }
                     best_obj = best.obj; best_nan = best.nan;
-                    park_ray(sm, r.o, r.d, best.t, t0);
+                    park_ray(sm, r.o, r.d, best.t);
                     active = true;
                 }
             }
@@ -333,7 +333,7 @@ __global__ void __launch_bounds__(BVH_THREADS, 8) k_closest_bvh(const __grid_con
                 Closest best; best.t = sm.aux[threadIdx.x]; best.obj = best_obj; best.nan = best_nan;
                 leaf_closest(sc, r, ~cur, best, tc);
                 sm.aux[threadIdx.x] = best.t; best_obj = best.obj; best_nan = best.nan;
-                bound = closest_bound32(best.t, sm.t0[threadIdx.x]);
+                bound = closest_bound32(best.t, (double)t0f);
                 cur = trav_pop(st, sp, bound);
             }
             if (active && ++walks > heavy_walks) {
@@ -379,7 +379,7 @@ __global__ void __launch_bounds__(BVH_THREADS, 8) k_shadow_bvh(const __grid_cons
                         br = make_boxray32_t<QNODES>(sc, r.o, r.d);
                         if (br.enter) { cur = 0; bound = shadow_bound32(range2, br.t0); }
                     }
-                    park_ray(sm, r.o, r.d, range2, 0.0);
+                    park_ray(sm, r.o, r.d, range2);
                     active = true;
                 }
             }
