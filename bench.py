@@ -34,6 +34,8 @@ import numpy as np  # noqa: E402
 WORKLOADS = {
     # BASELINE.json configs[2]: the metric's 4K single-GPU throughput configuration (default)
     "spheres-10k-4k-d8": dict(gen="spheres_10k", gen_kw=dict(width=3840, height=2160), opts=dict(max_depth=8, seed=3), accel="bvh"),
+    # configs[0]: the reference's own CPU-runnable case, test_scene.txt at its own options (800x800, 1024 spp, depth 4)
+    "test-scene-800-1024spp": dict(gen="cornell", gen_kw={}, opts=dict(max_depth=4, seed=1), accel="linear"),
     # configs[1]: pixel-match configuration
     "cornell-4k-1spp": dict(gen="cornell", gen_kw={}, opts=dict(width=3840, height=2160, antialias=1, max_depth=4, seed=1), accel="linear"),
     # configs[3] and its 4K variant (north_star target statement)
@@ -61,7 +63,7 @@ def frame_size(name, desc):
     o = WORKLOADS[name]["opts"]
     if desc is not None:
         return o.get("width") or desc["options"]["width"], o.get("height") or desc["options"]["height"], o.get("antialias", desc["options"]["antialias"])
-    return o["width"], o["height"], o["antialias"]
+    return o.get("width", 800), o.get("height", 800), o.get("antialias", 1024)   # test_scene.txt's own options block
 
 
 class ClockSampler:

@@ -18,6 +18,7 @@ CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libraytrace_b200.so")
+CLI = os.path.join(LIBDIR, "raytrace_b200")  # the reference's binary (src/main.rs) over the C ABI: csrc/cli.cpp
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
@@ -78,6 +79,10 @@ def build(force=False, verbose=False):
             rebuilt = True
     if rebuilt or not os.path.exists(LIB):
         _run([nvcc, "-shared", "-o", LIB] + objs + ARCH + ["-cudart", "static", "-Xlinker", "--no-undefined", "-lpthread", "-ldl", "-lrt"], verbose, log)
+    cli_src = os.path.join(CSRC, "cli.cpp")
+    if rebuilt or _newer(CLI, [cli_src, os.path.join(INCLUDE, "raytrace_b200.h")]):
+        _run(["g++"] + [f for f in HOST_FLAGS if f != "-fPIC"] + ["-I", INCLUDE, cli_src, "-o", CLI, "-L", LIBDIR, "-lraytrace_b200",
+                                                                  "-Wl,-rpath,$ORIGIN"], verbose, log)
     with open(os.path.join(OBJ, "build.log"), "a" if not rebuilt else "w") as f:
         f.write("\n".join(log))
     return LIB

@@ -4,6 +4,8 @@ Bars (BASELINE.json north_star): primary hit ids bit-exact; every byte of the qu
 >= 99.9 % identical; ray counts (Scene::intersect calls) equal.  In RT_FP_STRICT mode geometry is the same
 unfused f64 arithmetic as the oracle, so hit distances are required to be bit-identical too.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -352,3 +354,44 @@ def test_config5_skybox100k_4k(gpu, orc, scenes):
     fr = gpu.raytrace.render(gpu.Scene(desc), max_depth=4, seed=5)
     same = _sparse_check(fr, orc.OracleScene(desc), 2048, "config5", antialias=4, max_depth=4, seed=5)
     print("config5@4spp: %d rays, %.1f ms, sparse identical %.5f" % (fr.stats["rays_total"], fr.stats["render_ms"], same))
+
+
+def test_cli_renders_test_scene_to_out_bmp(gpu, tmp_path):
+    """the reference binary's behaviour (src/main.rs:16,34): ./test_scene.txt -> ./out.bmp; same bytes as the library call"""
+    import subprocess
+    cli = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "rust-raytrace_b200", "lib", "raytrace_b200")
+    (tmp_path / "test_scene.txt").write_text(REF_TEXT_SCENE)
+    r = subprocess.run([cli, "--width", "200", "--height", "160", "--antialias", "2", "--seed", "5", "--stats"], capture_output=True, text=True, cwd=tmp_path)
+    assert r.returncode == 0, r.stderr
+    assert "Mrays/s" in r.stderr
+    raw = (tmp_path / "out.bmp").read_bytes()
+    fr = gpu.raytrace.render(gpu.serialize.deserialize(REF_TEXT_SCENE), width=200, height=160, antialias=2, seed=5)
+    assert len(raw) == 122 + fr.rows.size
+    assert raw[:2] == b"BM"
+    got = np.frombuffer(raw[122:], dtype=np.uint8).reshape(fr.rows.shape)
+    diff = np.abs(got.astype(np.int16) - fr.rows.astype(np.int16))   # f64 atomics: the sum order differs between two runs
+    assert diff.max() <= 1 and (diff == 0).mean() >= 0.999
+
+
+def test_config1_test_scene_at_its_own_options_matches_out_bmp(gpu, orc):
+    """BASELINE config 1: test_scene.txt unmodified (800x800, 1024 spp, depth 4; 6.6e8 paths) on the GPU, against the
+    8x8-block linear means of upstream's own out.bmp (tests/golden/outbmp_block_means.npz) -- a statistical golden, the
+    only rendered artefact upstream ships"""
+    golden = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "outbmp_block_means.npz"))
+    sc = gpu.serialize.deserialize(REF_TEXT_SCENE)
+    assert sc.options() == (800, 800, 1024)
+    fr = gpu.raytrace.render(sc, seed=11, want_ids=False)
+    assert fr.stats["paths"] == 800 * 800 * 1024
+    v, _ = orc.srgb_tables()
+    lin = v[fr.bgr]                                                     # decoded 8-bit codes, as a BMP reader sees them
+    mine = lin.reshape(100, 8, 100, 8, 3).mean(axis=(1, 3))
+    g = golden["linear_bgr"].astype(np.float64)
+    ok = (golden["saturated"].max(axis=2) < 0.02)[:, :, None] & (g > 2e-3)
+    ratio = mine[ok] / g[ok]
+    assert ok.sum() > 3000
+    assert abs(np.median(ratio) - 1.0) < 0.01, np.median(ratio)
+    # per-block noise of two independent 1024-spp renders (64 pixels per block): a few per cent
+    assert np.abs(ratio - 1.0).mean() < 0.05, np.abs(ratio - 1.0).mean()
+    assert np.quantile(np.abs(ratio - 1.0), 0.99) < 0.15, np.quantile(np.abs(ratio - 1.0), 0.99)
+    for flipped in (mine[::-1], mine[:, ::-1]):                         # controls: orientation matters
+        assert np.abs(flipped[ok] / g[ok] - 1.0).mean() > 3.0 * np.abs(ratio - 1.0).mean()

@@ -220,3 +220,28 @@ def test_bmp_header_and_file(rt, orc, tmp_path):
         rt.bmp.write(str(p), 5, 7, rows[:, :15])
     with pytest.raises(rt.RtError):
         rt.bmp.write(str(tmp_path / "no_such_dir" / "o.bmp"), 5, 7, rows)
+
+
+CLI = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "rust-raytrace_b200", "lib", "raytrace_b200")
+
+
+def test_cli_reports_like_the_reference_binary(rt, tmp_path):
+    """csrc/cli.cpp = src/main.rs over the C ABI: default file names, "Error parsing scene:" + row:col: message, exit code 1;
+    without a GPU the render step fails loudly (no CPU path)"""
+    assert os.path.exists(CLI), "rust-raytrace_b200/build.py builds the CLI next to the library"
+    r = subprocess.run([CLI, "--help"], capture_output=True, text=True)
+    assert r.returncode == 0 and "test_scene.txt -> out.bmp" in r.stderr
+    bad = tmp_path / "bad.txt"
+    bad.write_text("camera { bogus }")
+    r = subprocess.run([CLI, str(bad)], capture_output=True, text=True, cwd=tmp_path)
+    assert r.returncode == 1
+    assert r.stdout.splitlines()[0] == "Error parsing scene:"
+    assert re.match(r"^1:\d+: ", r.stdout.splitlines()[1])
+    r = subprocess.run([CLI], capture_output=True, text=True, cwd=tmp_path)   # no test_scene.txt in the working directory
+    assert r.returncode == 1 and "test_scene.txt" in r.stdout
+    if rt.device_count() == 0:
+        good = tmp_path / "test_scene.txt"
+        good.write_text(REF_TEXT_SCENE)
+        r = subprocess.run([CLI, "--width", "16", "--height", "16", "--antialias", "1"], capture_output=True, text=True, cwd=tmp_path)
+        assert r.returncode == 1 and "render failed" in r.stderr
+        assert not (tmp_path / "out.bmp").exists()
