@@ -660,11 +660,17 @@ static void scan_attr_once() {
     }
 }
 
-// a traversal that has looked at the warp this many times (16 nodes or one leaf each) is handed to k_heavy_scan:
-// about the point where a CTA-wide scan of the whole sphere buffer is the cheaper way to finish the ray
+// A traversal that has looked at the warp this many times (16 nodes or one leaf each) is handed to k_heavy_scan.
+// A runaway ray walks ALONE at the tail of the launch, one dependent node fetch after the other (~300 cycles each), while
+// the scan costs one CTA n/256 exact tests per thread (~100 cycles each) next to the other CTAs: break-even near n/12000
+// looks.  Measured on the 1M-sphere frame: with the old n/256 = 3906 looks one ray held its GPU for 8 ms (and, sharded over
+// 8 GPUs, the seven others in the gather); n/8192 hands over after ~2000 nodes, 80 x what an average ray needs.
+#ifndef RT_HEAVY_DIV
+#define RT_HEAVY_DIV 8192u
+#endif
 static uint32_t heavy_walks(const DeviceScene& sc) {
-    const uint32_t w = sc.n_spheres / 256u;
-    return w < 256u ? 256u : (w > 8192u ? 8192u : w);
+    const uint32_t w = sc.n_spheres / RT_HEAVY_DIV;
+    return w < 32u ? 32u : (w > 4096u ? 4096u : w);
 }
 
 static void l_closest(cudaStream_t st, const DeviceScene& sc, bool bvh, RayQueue q, uint32_t first, uint32_t n, Counters* counters, int sm_count,
