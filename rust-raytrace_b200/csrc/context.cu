@@ -206,8 +206,9 @@ struct DeviceSceneHolder {
             bvh_ms = ms;
             cudaEventDestroy(e0); cudaEventDestroy(e1);
             ds.bvh_nodes = bvh.nodes; ds.bvh_qnodes = bvh.qnodes; ds.bvh_sph = bvh.sph; ds.bvh_obj = bvh.obj; ds.n_bvh_nodes = bvh.n_nodes;
-            if ((rc = dev_alloc(&heavy, HEAVY_CAP)) != RT_OK) return rc;
+            if ((rc = dev_alloc(&heavy, HEAVY_WORDS)) != RT_OK) return rc;
             allocs.push_back(heavy);
+            CUDA_TRY(cudaMemsetAsync(heavy + HEAVY_CAP, 0, sizeof(HeavyScratch), st));
             build_launches = bvh.launches;
         }
         return RT_OK;

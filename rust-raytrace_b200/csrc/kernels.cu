@@ -424,65 +424,108 @@ __device__ __forceinline__ bool closest_before(const Closest& a, const Closest& 
     return a.t < b.t || (a.t == b.t && a.obj < b.obj);
 }
 
+// exact tests of spheres [k0, k1) by the 256 threads of the CTA; SHADOW: returns "an occluder was found" (CTA-wide),
+// else the CTA's best hit in `best` of thread 0
 template <bool SHADOW>
-__global__ void __launch_bounds__(HEAVY_THREADS) k_heavy_scan(const __grid_constant__ DeviceScene sc, RayQueue q, ShadowQueue sq, uint32_t first,
-                                                              double* accum, Counters* counters, const uint32_t* heavy) {
+__device__ __forceinline__ bool heavy_scan_range(const DeviceScene& sc, const RayQ& r, double range2, uint32_t k0, uint32_t k1, Closest& best) {
     __shared__ double s_t[HEAVY_THREADS / 32];
     __shared__ int32_t s_obj[HEAVY_THREADS / 32];
     __shared__ int s_nan[HEAVY_THREADS / 32];
+    if (SHADOW) {
+        bool any = false;
+        for (uint32_t k = k0 + threadIdx.x; k < k1 && !any; k += HEAVY_THREADS) {
+            const double2 c01 = *reinterpret_cast<const double2*>(&sc.sph[k].cx), c23 = *reinterpret_cast<const double2*>(&sc.sph[k].cz);
+            double th;
+            if (sphere_hit(r, c01.x, c01.y, c23.x, c23.y, th) && shadow_hit_counts(th, range2)) any = true;
+        }
+        return __syncthreads_or(any ? 1 : 0) != 0;
+    }
+    for (uint32_t k = k0 + threadIdx.x; k < k1; k += HEAVY_THREADS) {
+        const double2 c01 = *reinterpret_cast<const double2*>(&sc.sph[k].cx), c23 = *reinterpret_cast<const double2*>(&sc.sph[k].cz);
+        double th;
+        if (sphere_hit(r, c01.x, c01.y, c23.x, c23.y, th)) closest_update(best, th, __ldg(sc.sph_obj + k));
+    }
+#pragma unroll
+    for (int x = 16; x > 0; x >>= 1) {
+        Closest other;
+        other.t = __shfl_xor_sync(0xFFFFFFFFu, best.t, x);
+        other.obj = __shfl_xor_sync(0xFFFFFFFFu, best.obj, x);
+        other.nan = __shfl_xor_sync(0xFFFFFFFFu, best.nan ? 1 : 0, x) != 0;
+        if (closest_before(other, best)) best = other;
+    }
+    if ((threadIdx.x & 31) == 0) { s_t[threadIdx.x >> 5] = best.t; s_obj[threadIdx.x >> 5] = best.obj; s_nan[threadIdx.x >> 5] = best.nan ? 1 : 0; }
+    __syncthreads();
+    if (threadIdx.x == 0)
+        for (int w = 1; w < HEAVY_THREADS / 32; w++) {
+            Closest other; other.t = s_t[w]; other.obj = s_obj[w]; other.nan = s_nan[w] != 0;
+            if (closest_before(other, best)) best = other;
+        }
+    __syncthreads();
+    return false;
+}
+
+// Two shapes.  Many heavy rays: one CTA per ray, CTAs loop over the list.  A few (<= HEAVY_SPLIT_RAYS, the usual case: a
+// handful of horizon rays per frame): the sphere buffer of each ray is cut into G = grid / count slices, one CTA per
+// slice, and the last CTA to finish a ray (arrival counter behind a __threadfence) merges the slices -- a 1M-sphere scan is
+// then microseconds instead of 0.5 ms on one SM.  The merge is a minimum under closest_update's total order (or an OR), so
+// it does not depend on which CTA comes last.
+template <bool SHADOW>
+__global__ void __launch_bounds__(HEAVY_THREADS) k_heavy_scan(const __grid_constant__ DeviceScene sc, RayQueue q, ShadowQueue sq, uint32_t first,
+                                                              double* accum, Counters* counters, uint32_t* heavy) {
     const uint32_t count = counters->heavy_count < HEAVY_CAP ? counters->heavy_count : HEAVY_CAP;
-    for (uint32_t e = blockIdx.x; e < count; e += gridDim.x) {
-        const uint32_t ray = heavy[e];
-        const uint32_t i = ray;  // closest: already the absolute queue index (first + local)
+    if (count == 0) return;
+    HeavyScratch* hs = reinterpret_cast<HeavyScratch*>(heavy + HEAVY_CAP);
+    uint32_t G = 1;
+    if (count <= HEAVY_SPLIT_RAYS && gridDim.x <= HEAVY_SPLIT_ITEMS) G = gridDim.x / count;
+    if (G < 1) G = 1;
+    const uint32_t items = count * G;
+    for (uint32_t item = blockIdx.x; item < items; item += gridDim.x) {  // G > 1: items <= gridDim.x, one pass
+        const uint32_t e = item / G, j = item - e * G;
+        const uint32_t chunk = (sc.n_spheres + G - 1) / G;
+        const uint32_t k0 = j * chunk < sc.n_spheres ? j * chunk : sc.n_spheres;
+        const uint32_t k1 = k0 + chunk < sc.n_spheres ? k0 + chunk : sc.n_spheres;
+        const uint32_t i = heavy[e];  // closest: already the absolute queue index (first + local)
         const V3 o = SHADOW ? v3(sq.ox[i], sq.oy[i], sq.oz[i]) : v3(q.ox[i], q.oy[i], q.oz[i]);
         const V3 d = SHADOW ? v3(sq.dx[i], sq.dy[i], sq.dz[i]) : v3(q.dx[i], q.dy[i], q.dz[i]);
         const RayQ r = make_rayq(o, d);
-        if (SHADOW) {
-            const double range2 = sq.r2[i];
-            Shadow s; s.nan = false; s.any = false;
-            planes_shadow(sc, r, range2, s);
-            bool any = false;
-            if (!s.nan && !s.any)
-                for (uint32_t k = threadIdx.x; k < sc.n_spheres && !any; k += HEAVY_THREADS) {
-                    const double2 c01 = *reinterpret_cast<const double2*>(&sc.sph[k].cx), c23 = *reinterpret_cast<const double2*>(&sc.sph[k].cz);
-                    double th;
-                    if (sphere_hit(r, c01.x, c01.y, c23.x, c23.y, th) && shadow_hit_counts(th, range2)) any = true;
-                }
-            const int occluded_by_sphere = __syncthreads_or(any ? 1 : 0);
-            if (threadIdx.x == 0) {
-                s.any = s.any || occluded_by_sphere != 0;
-                if (!shadow_result(s, range2)) accum_add(accum, sq.pixel[i], c3(sq.cr[i], sq.cg[i], sq.cb[i]));
-                atomicAdd(&counters->heavy_rays[1], 1ull);
+        const double range2 = SHADOW ? sq.r2[i] : -1.0;
+        Closest best = closest_none();
+        bool any = heavy_scan_range<SHADOW>(sc, r, range2, k0, k1, best);
+        if (threadIdx.x != 0) continue;
+        if (G > 1) {
+            if (SHADOW) {
+                if (any) atomicOr(&hs->flag[e], 1u);
+            } else {
+                hs->t[item] = best.t; hs->obj[item] = best.obj; hs->nan[item] = best.nan ? 1 : 0;
             }
-        } else {
-            Closest best = closest_none();
-            if (threadIdx.x == 0) planes_closest(sc, r, best);
-            // a NaN plane hit wins whatever the spheres say (src/scene.rs:227-233); spheres never produce NaN
-            for (uint32_t k = threadIdx.x; k < sc.n_spheres; k += HEAVY_THREADS) {
-                const double2 c01 = *reinterpret_cast<const double2*>(&sc.sph[k].cx), c23 = *reinterpret_cast<const double2*>(&sc.sph[k].cz);
-                double th;
-                if (sphere_hit(r, c01.x, c01.y, c23.x, c23.y, th)) closest_update(best, th, __ldg(sc.sph_obj + k));
-            }
-#pragma unroll
-            for (int x = 16; x > 0; x >>= 1) {
-                Closest other;
-                other.t = __shfl_xor_sync(0xFFFFFFFFu, best.t, x);
-                other.obj = __shfl_xor_sync(0xFFFFFFFFu, best.obj, x);
-                other.nan = __shfl_xor_sync(0xFFFFFFFFu, best.nan ? 1 : 0, x) != 0;
-                if (closest_before(other, best)) best = other;
-            }
-            if ((threadIdx.x & 31) == 0) { s_t[threadIdx.x >> 5] = best.t; s_obj[threadIdx.x >> 5] = best.obj; s_nan[threadIdx.x >> 5] = best.nan ? 1 : 0; }
-            __syncthreads();
-            if (threadIdx.x == 0) {
-                for (int w = 1; w < HEAVY_THREADS / 32; w++) {
-                    Closest other; other.t = s_t[w]; other.obj = s_obj[w]; other.nan = s_nan[w] != 0;
+            __threadfence();
+            if (atomicAdd(&hs->done[e], 1u) != G - 1) continue;  // not the last slice of this ray
+            __threadfence();
+            if (SHADOW) {
+                any = atomicExch(&hs->flag[e], 0u) != 0u;
+            } else {
+                for (uint32_t w = e * G; w < e * G + G; w++) {
+                    Closest other;
+                    other.t = __ldcg(&hs->t[w]); other.obj = __ldcg(&hs->obj[w]); other.nan = __ldcg(&hs->nan[w]) != 0;
                     if (closest_before(other, best)) best = other;
                 }
-                q.hit_id[i] = closest_id(best);
-                q.hit_t[i] = best.t;
-                atomicAdd(&counters->heavy_rays[0], 1ull);
             }
-            __syncthreads();
+            hs->done[e] = 0u;
+        }
+        if (SHADOW) {
+            Shadow s; s.nan = false; s.any = false;
+            planes_shadow(sc, r, range2, s);   // the traversal kernel handed the ray over only if no plane decided it; same result
+            s.any = s.any || any;
+            if (!shadow_result(s, range2)) accum_add(accum, sq.pixel[i], c3(sq.cr[i], sq.cg[i], sq.cb[i]));
+            atomicAdd(&counters->heavy_rays[1], 1ull);
+        } else {
+            // a NaN plane hit wins whatever the spheres say (src/scene.rs:227-233); spheres never produce NaN
+            Closest pl = closest_none();
+            planes_closest(sc, r, pl);
+            if (closest_before(pl, best)) best = pl;
+            q.hit_id[i] = closest_id(best);
+            q.hit_t[i] = best.t;
+            atomicAdd(&counters->heavy_rays[0], 1ull);
         }
     }
 }

@@ -19,6 +19,18 @@ struct Counters {
     unsigned long long heavy_rays[2];  // rays finished by the block-wide scan (whole render): [0] closest, [1] shadow
 };
 constexpr uint32_t HEAVY_CAP = 1u << 16;  // entries of the heavy-ray list (rays beyond it simply keep traversing)
+// Behind the list: scratch for splitting a few heavy rays over many CTAs (k_heavy_scan).  Zeroed once when allocated;
+// the last CTA of a ray leaves its words zero again.
+constexpr uint32_t HEAVY_SPLIT_RAYS = 64;     // split mode when at most this many rays are on the list
+constexpr uint32_t HEAVY_SPLIT_ITEMS = 2048;  // >= grid size of k_heavy_scan
+struct HeavyScratch {
+    uint32_t done[HEAVY_SPLIT_RAYS];          // CTAs that have finished their slice of ray e
+    uint32_t flag[HEAVY_SPLIT_RAYS];          // shadow: some slice found an occluder
+    double t[HEAVY_SPLIT_ITEMS];              // closest: best hit of each slice
+    int32_t obj[HEAVY_SPLIT_ITEMS];
+    int32_t nan[HEAVY_SPLIT_ITEMS];
+};
+constexpr size_t HEAVY_WORDS = HEAVY_CAP + (sizeof(HeavyScratch) + 3) / 4;  // uint32 words to allocate for `heavy`
 
 struct KernelTable {
     // camera.rs primary-ray generation: paths [path_base, path_base + n_paths) -> level-0 queue
