@@ -229,3 +229,19 @@ def test_coarse_grid_is_still_conservative(rt, orc, scenes, monkeypatch):
     rid, rt_, rn = orc.OracleScene(desc).trace_rays(rays)
     assert np.array_equal(ids, rid) and np.array_equal(t, rt_) and np.array_equal(nrm, rn)
     assert (rid > 0).mean() > 0.3
+
+
+@pytest.mark.parametrize("n", [1, 2, 3])
+def test_tiny_trees(rt, orc, scenes, n):
+    """one, two, three spheres forced through the BVH (single-leaf root, one internal node, ...) in both node formats"""
+    desc = scenes.random_spheres(n, 40 + n, 3.0, 8, 8)
+    rng = np.random.default_rng(n)
+    rays = _rays(rng, 4000, 5.0, 6.0)
+    data = desc["objects"][1]["data"]
+    aim = data[rng.integers(0, n, 2000), :3] + rng.normal(size=(2000, 3)) * 0.3
+    rays[:2000, 3:] = aim - rays[:2000, :3]
+    rid, rt_, rn = orc.OracleScene(desc).trace_rays(rays)
+    assert (rid > 0).mean() > 0.05
+    ids, t, nrm = emu.trace_rays(emu.Scene(desc), rays, accel=rt.ACCEL_BVH)
+    assert np.array_equal(ids, rid) and np.array_equal(t, rt_) and np.array_equal(nrm, rn)
+    assert emu.bvh_node_bytes(emu.Scene(desc)) == 32

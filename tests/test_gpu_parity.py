@@ -404,3 +404,21 @@ def test_config1_test_scene_at_its_own_options_matches_out_bmp(gpu, orc):
     assert np.quantile(np.abs(ratio - 1.0), 0.99) < 0.15, np.quantile(np.abs(ratio - 1.0), 0.99)
     for flipped in (mine[::-1], mine[:, ::-1]):                         # controls: orientation matters
         assert np.abs(flipped[ok] / g[ok] - 1.0).mean() > 3.0 * np.abs(ratio - 1.0).mean()
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 65])
+def test_tiny_trees(gpu, orc, scenes, n):
+    """one, two, three spheres forced through the device BVH (single-leaf root, one internal node, ...), and the smallest
+    scene ACCEL_AUTO sends there"""
+    desc = scenes.random_spheres(n, 40 + n, 3.0, 64, 48)
+    rng = np.random.default_rng(n)
+    rays = _random_rays(rng, 4000, 5.0, 6.0)
+    data = desc["objects"][1]["data"]
+    aim = data[rng.integers(0, n, 2000), :3] + rng.normal(size=(2000, 3)) * 0.3
+    rays[:2000, 3:] = aim - rays[:2000, :3]
+    rid, rt_, rn = orc.OracleScene(desc).trace_rays(rays)
+    ids, t, nrm = gpu.raytrace.intersect(gpu.Scene(desc), rays, accel=gpu.ACCEL_BVH)
+    assert np.array_equal(ids, rid) and np.array_equal(t, rt_) and np.array_equal(nrm, rn)
+    fr = gpu.raytrace.render(gpu.Scene(desc), max_depth=4, seed=n, accel=gpu.ACCEL_BVH)
+    assert_parity(fr, orc.OracleScene(desc).render(max_depth=4, seed=n), "tiny tree n=%d" % n)
+    assert fr.stats["accel_used"] == gpu.ACCEL_BVH and fr.stats["n_bvh_nodes"] == max(1, n - 1)
