@@ -21,7 +21,10 @@ namespace RT_NS {
 constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_TILE = 1024;  // spheres per shared-memory tile (32 KB), double buffered
 constexpr int BVH_THREADS = 128;
-constexpr int SHADE_THREADS = 128;
+#ifndef RT_SHADE_THREADS
+#define RT_SHADE_THREADS 128
+#endif
+constexpr int SHADE_THREADS = RT_SHADE_THREADS;
 
 // ---------------------------------------------------------------------------------------------------------
 // small PTX wrappers: mbarrier + 1-D TMA bulk copy (global -> shared)
