@@ -4,8 +4,9 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 rt = importlib.import_module("rust-raytrace_b200")
 scenes = importlib.import_module("rust-raytrace_b200.scenes")
-scene = rt.Scene(scenes.spheres_10k())
-kw = dict(max_depth=8, seed=3, accel=rt.ACCEL_BVH)
+which = sys.argv[1] if len(sys.argv) > 1 else "10k"
+scene = rt.Scene(scenes.spheres_10k() if which == "10k" else scenes.spheres_1m(3840, 2160))
+kw = dict(max_depth=8, seed=3 if which == "10k" else 4, accel=rt.ACCEL_BVH)
 keep = rt.Context(scene, **kw)   # bench.py keeps its device-resident context alive while the e2e leg runs
 keep.render()
 host = torch.empty(keep.framebuffer_ptr()[1], dtype=torch.uint8).pin_memory()
