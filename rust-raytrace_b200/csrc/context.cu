@@ -277,6 +277,7 @@ struct rt_context {
     uint8_t* framebuffer = nullptr;
     size_t fb_bytes = 0;
     uint32_t slice = 0;
+    uint32_t shadow_queued = 0;  // shadow rays appended since the last trace of the shadow queue
     uint64_t total_paths = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     rt_stats stats{};
@@ -320,18 +321,35 @@ int ctx_fetch_counters(rt_context* c) {
     return RT_OK;
 }
 
+// traces what the shadow queue holds and empties it
+int flush_shadow(rt_context* c) {
+    if (c->shadow_queued) {
+        c->prof_begin(3);
+        c->k->shadow(c->stream, c->scene.ds, c->scene.use_bvh, c->shadowq, c->shadow_queued, c->accum, c->counters, c->sm_count, c->scene.heavy);
+        c->prof_end();
+        c->stats.kernel_launches += c->scene.use_bvh ? 2 : 1;  // shadow (+ heavy scan)
+        c->shadow_queued = 0;
+    }
+    CUDA_TRY(cudaMemsetAsync(&c->counters->shadow_count, 0, sizeof(uint32_t), c->stream));
+    return RT_OK;
+}
+
 int process_level(rt_context* c, uint32_t d, uint32_t n) {
     const bool last = d + 1 >= c->levels.size();
     RayQueue& in = c->levels[d];
     RayQueue& out = last ? c->null_queue : c->levels[d + 1];
     uint32_t* next_count = &c->counters->level_count[last ? 63 : d + 1];
+    const uint64_t lights = std::max(1u, c->scene.ds.n_lights);
     for (uint32_t first = 0; first < n; first += c->slice) {
         const uint32_t cnt = std::min(c->slice, n - first);
         c->prof_begin(1);
         c->k->closest(c->stream, c->scene.ds, c->scene.use_bvh, in, first, cnt, c->counters, c->sm_count, c->scene.heavy);
         c->prof_end();
         CUDA_TRY(cudaMemsetAsync(next_count, 0, sizeof(uint32_t), c->stream));
-        CUDA_TRY(cudaMemsetAsync(&c->counters->shadow_count, 0, sizeof(uint32_t), c->stream));
+        if ((uint64_t)c->shadow_queued + (uint64_t)cnt * lights > c->shadowq.cap) {  // this slice might not fit behind what is queued
+            int rc = flush_shadow(c);
+            if (rc != RT_OK) return rc;
+        }
         c->prof_begin(2);
         c->k->shade(c->stream, c->scene.ds, c->fp, in, first, cnt, out, next_count, c->shadowq, &c->counters->shadow_count, &c->counters->overflow,
                     c->accum, c->ids);
@@ -339,16 +357,11 @@ int process_level(rt_context* c, uint32_t d, uint32_t n) {
         c->stats.kernel_launches += c->scene.use_bvh ? 3 : 2;  // closest (+ heavy scan), shade
         int rc = ctx_fetch_counters(c);
         if (rc != RT_OK) return rc;
-        const uint32_t n_shadow = c->counters_host->shadow_count;
+        const uint32_t n_total = c->counters_host->shadow_count;  // appended behind the rays of earlier slices / levels
         const uint32_t n_next = last ? 0 : c->counters_host->level_count[d + 1];
         if (d == 0) c->stats.rays_primary += cnt; else c->stats.rays_secondary += cnt;
-        c->stats.rays_shadow += n_shadow;
-        if (n_shadow) {
-            c->prof_begin(3);
-            c->k->shadow(c->stream, c->scene.ds, c->scene.use_bvh, c->shadowq, n_shadow, c->accum, c->counters, c->sm_count, c->scene.heavy);
-            c->prof_end();
-            c->stats.kernel_launches += c->scene.use_bvh ? 2 : 1;  // shadow (+ heavy scan)
-        }
+        c->stats.rays_shadow += n_total - c->shadow_queued;
+        c->shadow_queued = n_total;
         if (n_next) {
             rc = process_level(c, d + 1, n_next);
             if (rc != RT_OK) return rc;
@@ -398,7 +411,10 @@ int rt_context_create(const rt_scene* s, const rt_render_opts* o, rt_context** o
     cap = std::min(cap, want);
     cap = std::max<uint64_t>(cap, (uint64_t)branch * 32);
     cap = (cap + 1023) & ~1023ull;
-    const uint64_t shadow_cap = std::min<uint64_t>(cap * 2, (std::max<uint64_t>(c->total_paths * lights, 1024) + 1023) & ~1023ull);
+    // Shadow queries only feed the accumulator, so they are not traced level by level: the queue keeps filling across
+    // levels and is traced when it could not take the next slice's worst case, or at the end of the frame -- one or two
+    // large launches instead of one small one per level (a 4K frame's deep levels hold a few thousand rays each).
+    const uint64_t shadow_cap = std::min<uint64_t>(cap * 8, (std::max<uint64_t>(c->total_paths * lights * 3, 1024) + 1023) & ~1023ull);
     c->slice = (uint32_t)std::max<uint64_t>(32, std::min<uint64_t>(cap / branch, shadow_cap / lights));
     const uint32_t n_levels = fp.max_depth + 2;
     c->levels.resize(n_levels);
@@ -446,6 +462,7 @@ int rt_context_render(rt_context* c, rt_stats* stats) {
     CUDA_TRY(cudaMemsetAsync(c->accum, 0, npix * 3 * sizeof(double), c->stream));
     CUDA_TRY(cudaMemsetAsync(c->ids, 0xFF, npix * sizeof(int32_t), c->stream));
     CUDA_TRY(cudaMemsetAsync(c->counters, 0, sizeof(Counters), c->stream));
+    c->shadow_queued = 0;
     const uint64_t batch = c->levels[0].cap;
     for (uint64_t base = 0; base < c->total_paths; base += batch) {
         const uint32_t n = (uint32_t)std::min<uint64_t>(batch, c->total_paths - base);
@@ -462,6 +479,10 @@ int rt_context_render(rt_context* c, rt_stats* stats) {
             rc = process_level(c, 0, n0);
             if (rc != RT_OK) return rc;
         }
+    }
+    {
+        int rc = flush_shadow(c);
+        if (rc != RT_OK) return rc;
     }
     c->prof_begin(4);
     c->k->resolve(c->stream, c->scene.ds, fp, c->accum, c->framebuffer, c->bytewidth);
