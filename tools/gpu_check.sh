@@ -13,6 +13,7 @@ cat $O/${TAG}_bench.json
 if [ "$2" != "noncu" ]; then
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${TAG}_launches.csv python bench.py --steps 1 --warmup 3 --no-e2e --no-cpu-baseline > $O/${TAG}_ncu_list.log 2>&1; echo "ncu list rc=$?"
 for K in k_shadow_bvh k_closest_bvh k_shade; do
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:$K -s 12 -c 1 -o $O/${TAG}_full_$K -f python bench.py --steps 1 --warmup 3 --no-e2e --no-cpu-baseline > $O/${TAG}_ncu_full_$K.log 2>&1; echo "ncu full $K rc=$?"
+  SKIP=12; [ $K = k_shadow_bvh ] && SKIP=2   # one shadow launch per frame, ten of the others
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:$K -s $SKIP -c 1 -o $O/${TAG}_full_$K -f python bench.py --steps 1 --warmup 3 --no-e2e --no-cpu-baseline > $O/${TAG}_ncu_full_$K.log 2>&1; echo "ncu full $K rc=$?"
 done
 fi
