@@ -251,6 +251,8 @@ def add_ncu_traffic(roof, workload, world):
         if world == 1 and t.get("workload") == workload and k:
             roof["traffic"] = k["dram_bytes_read"] + k["dram_bytes_write"]
             roof["traffic_source"] = k["source"]
+            # what the same capture says binds the kernel when it is not the HBM roofline
+            roof["ncu"] = {m: k[m] for m in ("issue_slots_pct", "lanes_per_instruction", "l1_lsu_wavefronts_pct", "warps_active_pct") if m in k}
     except (OSError, ValueError, KeyError):
         pass
     return roof
