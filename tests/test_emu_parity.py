@@ -245,3 +245,38 @@ def test_tiny_trees(rt, orc, scenes, n):
     ids, t, nrm = emu.trace_rays(emu.Scene(desc), rays, accel=rt.ACCEL_BVH)
     assert np.array_equal(ids, rid) and np.array_equal(t, rt_) and np.array_equal(nrm, rn)
     assert emu.bvh_node_bytes(emu.Scene(desc)) == 32
+
+
+@pytest.mark.parametrize("case", range(8))
+def test_filter_is_conservative_on_odd_scenes(rt, orc, case):
+    """CPU twin of tests/test_gpu_parity.py::test_bvh_filter_is_conservative_on_odd_scenes (same scene recipes, fewer rays):
+    the header's BVH path against the oracle's scan"""
+    from test_gpu_parity import _stress_scene
+    rng = np.random.default_rng(100 + case)
+    centre, extent, rlo, rhi = [
+        ((0.0, 0.0, 0.0), (50.0, 50.0, 50.0), 0.05, 5.0),
+        ((4000.0, -2500.0, 9000.0), (40.0, 5.0, 40.0), 0.1, 1.0),
+        ((0.0, 0.0, 0.0), (2000.0, 0.5, 2000.0), 0.2, 0.8),
+        ((0.0, 0.0, 0.0), (0.2, 300.0, 0.2), 0.01, 0.3),
+        ((10.0, 10.0, 10.0), (30.0, 30.0, 30.0), 1e-3, 30.0),
+        ((-1e5, 2e5, 5e4), (500.0, 500.0, 500.0), 0.5, 5.0),
+        ((0.0, 0.0, 0.0), (1e-3, 1e-3, 1e-3), 1e-5, 1e-4),
+        ((0.0, 0.0, 0.0), (3e4, 10.0, 3e4), 0.3, 0.6),
+    ][case]
+    centre, extent = np.array(centre), np.array(extent)
+    desc, c, r = _stress_scene(rt.scene, rng, 1500, centre, extent, rlo, rhi)
+    n = 8000
+    k = rng.integers(0, len(c), n)
+    target = c[k] + rng.normal(size=(n, 3)) * r[k][:, None] * rng.choice([0.3, 1.0, 1.5], n)[:, None]
+    dist = np.exp(rng.uniform(np.log(np.linalg.norm(extent) * 1e-3), np.log(np.linalg.norm(extent) * 1e3), n))
+    dirs = rng.normal(size=(n, 3)); dirs /= np.linalg.norm(dirs, axis=1, keepdims=True)
+    o = target - dirs * dist[:, None]
+    d = dirs * np.exp(rng.uniform(-3, 3, n))[:, None]
+    d[:300, 0] = 0.0; d[300:600, 1] = 0.0; d[600:800, [0, 2]] = 0.0
+    o[800:1000] = c[k[800:1000]]
+    rays = np.concatenate([o, d], axis=1)
+    ids, t, nrm = emu.trace_rays(emu.Scene(desc), rays, accel=rt.ACCEL_BVH)
+    rid, rt_, rn = orc.OracleScene(desc).trace_rays(rays)
+    assert np.array_equal(ids, rid), "%d ids differ" % int((ids != rid).sum())
+    assert np.array_equal(t, rt_, equal_nan=True) and np.array_equal(nrm, rn, equal_nan=True)
+    assert emu.bvh_node_bytes(emu.Scene(desc)) == (64 if case in (2, 7) else 32)   # 4000- and 60000-wide fields: grid too coarse

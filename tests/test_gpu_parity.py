@@ -422,3 +422,53 @@ def test_tiny_trees(gpu, orc, scenes, n):
     fr = gpu.raytrace.render(gpu.Scene(desc), max_depth=4, seed=n, accel=gpu.ACCEL_BVH)
     assert_parity(fr, orc.OracleScene(desc).render(max_depth=4, seed=n), "tiny tree n=%d" % n)
     assert fr.stats["accel_used"] == gpu.ACCEL_BVH and fr.stats["n_bvh_nodes"] == max(1, n - 1)
+
+
+def _stress_scene(S, rng, n, centre, extent, rlo, rhi):
+    b = S.SceneBuilder()
+    m = b.add_material(S.PhongMaterial((0.5, 0.5, 0.5), (0.1, 0.1, 0.1), 10.0, (0.01, 0.01, 0.01)))
+    b.add_object(S.Plane((centre[0], centre[1] - extent[1] - 1.0, centre[2]), (0.0, 1.0, 0.0)), m)
+    c = centre + rng.uniform(-1.0, 1.0, size=(n, 3)) * extent
+    r = np.exp(rng.uniform(np.log(rlo), np.log(rhi), n))
+    b.add_spheres(np.concatenate([c, r[:, None]], axis=1), np.zeros(n, dtype=np.uint32))
+    b.add_light(S.PointLight((centre[0], centre[1] + 3 * extent[1] + 10, centre[2]), (1.0, 1.0, 1.0)))
+    b.camera = S.SimplePerspectiveCamera.new((centre[0], centre[1], centre[2] + 2 * extent[2] + 5), (0.0, 0.0, -1.0), (0.0, 1.0, 0.0), 2.0)
+    b.background = S.SolidColorBackground((0.1, 0.1, 0.1))
+    b.options = S.Options(8, 8, 1)
+    return b.build(), c, r
+
+
+@pytest.mark.parametrize("case", range(8))
+def test_bvh_filter_is_conservative_on_odd_scenes(gpu, case):
+    """the f32 / 16-bit-grid filter in front of the exact test must never lose a hit: BVH == GPU linear scan, bit for bit,
+    on scenes far from the origin, flat, needle-like, with radii over five decades, and with rays that start inside,
+    far outside, on axis planes and along box faces"""
+    rng = np.random.default_rng(100 + case)
+    centre, extent, rlo, rhi = [
+        ((0.0, 0.0, 0.0), (50.0, 50.0, 50.0), 0.05, 5.0),
+        ((4000.0, -2500.0, 9000.0), (40.0, 5.0, 40.0), 0.1, 1.0),        # far from the origin: large |c|, small extent
+        ((0.0, 0.0, 0.0), (2000.0, 0.5, 2000.0), 0.2, 0.8),              # very flat
+        ((0.0, 0.0, 0.0), (0.2, 300.0, 0.2), 0.01, 0.3),                 # a needle
+        ((10.0, 10.0, 10.0), (30.0, 30.0, 30.0), 1e-3, 30.0),            # radii over 4.5 decades, heavy overlap
+        ((-1e5, 2e5, 5e4), (500.0, 500.0, 500.0), 0.5, 5.0),             # 1e5 from the origin
+        ((0.0, 0.0, 0.0), (1e-3, 1e-3, 1e-3), 1e-5, 1e-4),               # a tiny scene
+        ((0.0, 0.0, 0.0), (3e4, 10.0, 3e4), 0.3, 0.6),                   # grid too coarse: f32 nodes are chosen
+    ][case]
+    centre, extent = np.array(centre), np.array(extent)
+    desc, c, r = _stress_scene(gpu.scene, rng, 6000, centre, extent, rlo, rhi)
+    sc = gpu.Scene(desc)
+    n = 60000
+    k = rng.integers(0, len(c), n)
+    target = c[k] + rng.normal(size=(n, 3)) * r[k][:, None] * rng.choice([0.3, 1.0, 1.5], n)[:, None]
+    dist = np.exp(rng.uniform(np.log(np.linalg.norm(extent) * 1e-3), np.log(np.linalg.norm(extent) * 1e3), n))
+    dirs = rng.normal(size=(n, 3)); dirs /= np.linalg.norm(dirs, axis=1, keepdims=True)
+    o = target - dirs * dist[:, None]
+    d = dirs * np.exp(rng.uniform(-3, 3, n))[:, None]                      # un-normalised directions
+    d[:2000, 0] = 0.0; d[2000:4000, 1] = 0.0; d[4000:5000, [0, 2]] = 0.0  # axis-plane and axis-parallel rays
+    o[5000:6000] = c[k[5000:6000]]                                         # from sphere centres
+    rays = np.concatenate([o, d], axis=1)
+    a = gpu.raytrace.intersect(sc, rays, accel=gpu.ACCEL_LINEAR)
+    b = gpu.raytrace.intersect(sc, rays, accel=gpu.ACCEL_BVH)
+    assert np.array_equal(a[0], b[0]), "%d ids differ" % int((a[0] != b[0]).sum())
+    assert np.array_equal(a[1], b[1], equal_nan=True) and np.array_equal(a[2], b[2], equal_nan=True)
+    assert (a[0] > 0).mean() > 0.15
