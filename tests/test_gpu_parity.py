@@ -472,3 +472,10 @@ def test_bvh_filter_is_conservative_on_odd_scenes(gpu, case):
     assert np.array_equal(a[0], b[0]), "%d ids differ" % int((a[0] != b[0]).sum())
     assert np.array_equal(a[1], b[1], equal_nan=True) and np.array_equal(a[2], b[2], equal_nan=True)
     assert (a[0] > 0).mean() > 0.15
+    # the same through whole frames (shadow queries and reflections included)
+    fb = gpu.raytrace.render(sc, width=96, height=64, antialias=2, max_depth=3, seed=case, accel=gpu.ACCEL_BVH)
+    fl = gpu.raytrace.render(sc, width=96, height=64, antialias=2, max_depth=3, seed=case, accel=gpu.ACCEL_LINEAR)
+    assert np.array_equal(fb.ids, fl.ids)
+    assert fb.stats["rays_total"] == fl.stats["rays_total"] and fb.stats["rays_shadow"] == fl.stats["rays_shadow"]
+    diff = np.abs(fb.rows.astype(np.int16) - fl.rows.astype(np.int16))
+    assert diff.max() <= 1 and (diff == 0).mean() >= 0.999
