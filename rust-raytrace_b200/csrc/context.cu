@@ -133,12 +133,40 @@ int dev_alloc(T** p, size_t count) {
     CUDA_TRY(g_cache.alloc((void**)p, count * sizeof(T)));
     return RT_OK;
 }
-template <typename T>
-int dev_upload(T** p, const std::vector<T>& v) {
-    int rc = dev_alloc(p, v.size());
-    if (rc != RT_OK) return rc;
-    if (!v.empty()) CUDA_TRY(cudaMemcpy(*p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
-    return RT_OK;
+// Page-locks the big vectors of a cache entry, once (portable: every device of the process copies from them).  Small
+// scenes stay pageable: the registration would cost more than it saves.
+struct HostPins {
+    std::vector<void*> regions;
+    ~HostPins() {
+        for (void* p : regions) cudaHostUnregister(p);
+        cudaGetLastError();
+    }
+};
+void pin_flat_cache(const rt_scene* s, FlatCache* fc) {
+    std::lock_guard<std::mutex> g(s->flat_cache.m);
+    if (fc->pin) return;
+    const FlatScene& f = fc->flat;
+    size_t total = f.sph.size() * sizeof(SphereRec) + (f.sph_obj.size() + f.obj_shape.size() + f.obj_material.size()) * 4 +
+                   s->materials.size() * sizeof(MaterialRec);
+    if (s->bg_kind == BG_SKYBOX)
+        for (int k = 0; k < 6; k++) total += s->faces[k].data.size();
+    std::shared_ptr<HostPins> pins = std::make_shared<HostPins>();
+    if (total >= (4u << 20)) {
+        auto reg = [&](const void* p, size_t bytes) {
+            if (!bytes) return;
+            if (cudaHostRegister(const_cast<void*>(p), bytes, cudaHostRegisterPortable) == cudaSuccess) pins->regions.push_back(const_cast<void*>(p));
+            else cudaGetLastError();  // not fatal: that buffer is copied from pageable memory
+        };
+        reg(f.sph.data(), f.sph.size() * sizeof(SphereRec));
+        reg(f.sph_obj.data(), f.sph_obj.size() * sizeof(int32_t));
+        reg(f.obj_shape.data(), f.obj_shape.size() * sizeof(uint32_t));
+        reg(f.obj_material.data(), f.obj_material.size() * sizeof(uint32_t));
+        // the scene's own vectors: rt::scene_touch drops this entry before anything reallocates them
+        reg(s->materials.data(), s->materials.size() * sizeof(MaterialRec));
+        if (s->bg_kind == BG_SKYBOX)
+            for (int k = 0; k < 6; k++) reg(s->faces[k].data.data(), s->faces[k].data.size());
+    }
+    fc->pin = pins;
 }
 
 // device copy of a scene: flattened buffers + optional BVH
@@ -156,41 +184,48 @@ struct DeviceSceneHolder {
         allocs.clear();
         bvh_free(&bvh, g_cache_allocator);
     }
+    uint32_t* heavy = nullptr;  // list of rays handed from the BVH traversal to the block-wide scan (kernels.h HEAVY_CAP)
+
+    // the flat buffers come from the scene's cache (host_scene.h FlatCache) and, for big scenes, from page-locked memory:
+    // copies on the context's stream, the BVH build queued right behind them
     template <typename T>
-    int up(const std::vector<T>& v, const T** out) {
+    int up_flat(const std::vector<T>& v, const T** out, cudaStream_t st) {
         T* p = nullptr;
-        int rc = dev_upload(&p, v);
+        int rc = dev_alloc(&p, v.size());
         if (rc != RT_OK) return rc;
-        if (p) allocs.push_back(p);
+        if (p) {
+            allocs.push_back(p);
+            CUDA_TRY(cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, st));
+        }
         *out = p;
         return RT_OK;
     }
 
-    uint32_t* heavy = nullptr;  // list of rays handed from the BVH traversal to the block-wide scan (kernels.h HEAVY_CAP)
-
     int init(const rt_scene* s, int accel, cudaStream_t st) {
-        FlatScene f;
-        int rc = flatten_scene(s, &f);
+        std::shared_ptr<FlatCache> fc;
+        int rc = flatten_scene_cached(s, &fc);
         if (rc != RT_OK) return rc;
+        pin_flat_cache(s, fc.get());
+        const FlatScene& f = fc->flat;
         fill_scene_header(s, f, &ds);
         const double* clo = f.centroid_lo;
         const double* chi = f.centroid_hi;
-        if ((rc = up(f.sph, &ds.sph)) != RT_OK) return rc;
-        if ((rc = up(f.sph_obj, &ds.sph_obj)) != RT_OK) return rc;
-        if ((rc = up(f.planes, &ds.planes)) != RT_OK) return rc;
-        if ((rc = up(f.obj_shape, &ds.obj_shape)) != RT_OK) return rc;
-        if ((rc = up(f.obj_material, &ds.obj_material)) != RT_OK) return rc;
-        if ((rc = up(s->materials, &ds.materials)) != RT_OK) return rc;
-        if ((rc = up(s->lights, &ds.lights)) != RT_OK) return rc;
+        if ((rc = up_flat(f.sph, &ds.sph, st)) != RT_OK) return rc;
+        if ((rc = up_flat(f.sph_obj, &ds.sph_obj, st)) != RT_OK) return rc;
+        if ((rc = up_flat(f.planes, &ds.planes, st)) != RT_OK) return rc;
+        if ((rc = up_flat(f.obj_shape, &ds.obj_shape, st)) != RT_OK) return rc;
+        if ((rc = up_flat(f.obj_material, &ds.obj_material, st)) != RT_OK) return rc;
+        if ((rc = up_flat(s->materials, &ds.materials, st)) != RT_OK) return rc;
+        if ((rc = up_flat(s->lights, &ds.lights, st)) != RT_OK) return rc;
         if (s->bg_kind == BG_SKYBOX)
             for (int k = 0; k < 6; k++) {
                 const uint8_t* p = nullptr;
-                if ((rc = up(s->faces[k].data, &p)) != RT_OK) return rc;
+                if ((rc = up_flat(s->faces[k].data, &p, st)) != RT_OK) return rc;
                 ds.faces[k].data = p;
             }
         std::vector<double> vals(SRGB_VALUES, SRGB_VALUES + 256), avg(SRGB_AVERAGE, SRGB_AVERAGE + 255);
-        if ((rc = up(vals, &ds.srgb_values)) != RT_OK) return rc;
-        if ((rc = up(avg, &ds.srgb_average)) != RT_OK) return rc;
+        if ((rc = up_flat(vals, &ds.srgb_values, st)) != RT_OK) return rc;
+        if ((rc = up_flat(avg, &ds.srgb_average, st)) != RT_OK) return rc;
         use_bvh = accel_uses_bvh(accel, ds.n_spheres);
         if (use_bvh) {
             cudaEvent_t e0, e1;
@@ -211,6 +246,7 @@ struct DeviceSceneHolder {
             CUDA_TRY(cudaMemsetAsync(heavy + HEAVY_CAP, 0, sizeof(HeavyScratch), st));
             build_launches = bvh.launches;
         }
+        CUDA_TRY(cudaStreamSynchronize(st));  // the cache entry may go away (scene changed or freed) once this returns
         return RT_OK;
     }
 };

@@ -192,6 +192,37 @@ int flatten_scene(const rt_scene* s, FlatScene* f) {
     return RT_OK;
 }
 
+void scene_touch(rt_scene* s) {
+    std::lock_guard<std::mutex> g(s->flat_cache.m);
+    s->flat_cache.p.reset();
+    s->revision++;
+}
+
+int flatten_scene_cached(const rt_scene* s, std::shared_ptr<FlatCache>* out) {
+    const char* e = std::getenv("RAYTRACE_B200_BVH_NODES");
+    const std::string quant_override = e ? e : "";
+    std::lock_guard<std::mutex> g(s->flat_cache.m);
+    std::shared_ptr<FlatCache>& c = s->flat_cache.p;
+    if (c && c->revision == s->revision && c->quant_override == quant_override && c->flat.obj_shape.size() == s->objects.size()) {
+        // what flatten_scene checks without looking at the objects
+        if (!s->camera_set) { set_error("scene has no camera"); return RT_ERR_INVALID; }
+        if (!s->background_set) { set_error("scene has no background"); return RT_ERR_INVALID; }
+        if (s->bg_kind == BG_SKYBOX)
+            for (int k = 0; k < 6; k++)
+                if (s->faces[k].data.empty()) { set_error("skybox face missing"); return RT_ERR_INVALID; }
+        *out = c;
+        return RT_OK;
+    }
+    std::shared_ptr<FlatCache> fresh = std::make_shared<FlatCache>();
+    int rc = flatten_scene(s, &fresh->flat);
+    if (rc != RT_OK) return rc;
+    fresh->revision = s->revision;
+    fresh->quant_override = quant_override;
+    c = fresh;
+    *out = c;
+    return RT_OK;
+}
+
 // The 32-byte nodes store box planes on a 65535-step grid over the sphere bounds.  A box grows by up to one cell from
 // the rounding and the filter pads it by another 1.25 cells (rt_device.cuh make_boxray32), so the grid is used only
 // when 2.25 cells stay under a quarter of the mean radius on every axis and the bounds are small enough for the f32
@@ -302,6 +333,7 @@ static int add_material(rt_scene* s, int32_t kind, const double* diffuse, const 
     }
     m.exponent = exponent;
     m.ior = ior;
+    scene_touch(s);
     s->materials.push_back(m);
     return (int)s->materials.size() - 1;
 }
@@ -323,6 +355,7 @@ int rt_scene_add_spheres(rt_scene* s, uint64_t n, const double* cr, const uint32
     for (uint64_t i = 0; i < n; i++)
         if (material[i] >= s->materials.size()) { set_error("rt_scene_add_spheres: material index out of range"); return RT_ERR_INVALID; }
     if (s->objects.size() + n > 0x7FFFFFF0ull) { set_error("too many objects"); return RT_ERR_INVALID; }
+    scene_touch(s);
     s->objects.reserve(s->objects.size() + n);
     for (uint64_t i = 0; i < n; i++) {
         HostObject o{};
@@ -342,6 +375,7 @@ int rt_scene_add_plane(rt_scene* s, const double* point, const double* normal, u
     o.is_plane = true;
     for (int i = 0; i < 3; i++) { o.p[i] = point[i]; o.n[i] = normal[i]; }
     o.material = material;
+    scene_touch(s);
     s->objects.push_back(o);
     s->n_planes++;
     return RT_OK;
@@ -398,6 +432,7 @@ int rt_scene_set_background_solid(rt_scene* s, const double* color) {
 int rt_scene_set_skybox_face(rt_scene* s, int face, uint32_t w, uint32_t h, const uint8_t* rgb) {
     if (!s || !rgb || face < 0 || face > 5 || w == 0 || h == 0) { set_error("set_skybox_face: bad argument"); return RT_ERR_INVALID; }
     s->bg_kind = BG_SKYBOX;
+    scene_touch(s);
     s->faces[face].width = w; s->faces[face].height = h;
     s->faces[face].data.assign(rgb, rgb + (size_t)3 * w * h);
     s->background_set = true;
@@ -409,6 +444,7 @@ int rt_scene_load_skybox_face(rt_scene* s, int face, const char* path) {
     HostTexture t;
     if (!load_texture_file(path, &t, &err)) { set_error(std::string("error loading \"") + path + "\": " + err); return RT_ERR_IO; }
     s->bg_kind = BG_SKYBOX;
+    scene_touch(s);
     s->faces[face] = std::move(t);
     s->background_set = true;
     return RT_OK;

@@ -4,6 +4,8 @@
 // The host only *describes* the scene; all tracing happens on the device.
 #pragma once
 #include <cstdint>
+#include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -26,6 +28,38 @@ struct HostObject {
     uint32_t material;
 };
 
+// Flattened scene: the reference's Vec<Object> of boxed trait objects (src/scene.rs:93-98) as tagged SoA buffers.
+struct FlatScene {
+    std::vector<SphereRec> sph;         // scan order = object order among spheres
+    std::vector<int32_t> sph_obj;
+    std::vector<PlaneRec> planes;
+    std::vector<uint32_t> obj_shape, obj_material;
+    double centroid_lo[3], centroid_hi[3];
+    double box_lo[3], box_hi[3];  // bounds of the sphere boxes (c -+ |r|); -+inf when unusable
+    double cmax, rmin;
+    int32_t max_children;
+    // 16-bit grid for the 32-byte BVH nodes (rt_types.h BvhQNode); quant == false: grid too coarse / unusable bounds
+    bool quant;
+    double q_org[3], q_cell[3];
+};
+// What rt_context_create needs from the host scene, kept with the scene between contexts: a caller that builds a context
+// per frame (the reference's main does the equivalent) flattens a 1M-object scene once, not per frame, and uploads it
+// from page-locked memory (`pin`, set by context.cu, undoes the registration when the cache entry goes away).
+struct FlatCache {
+    FlatScene flat;
+    uint64_t revision = 0;
+    std::string quant_override;  // RAYTRACE_B200_BVH_NODES at the time of flattening
+    std::shared_ptr<void> pin;
+};
+// the scene's slot for it; copying a scene does not copy the cache
+struct FlatCacheSlot {
+    std::mutex m;
+    std::shared_ptr<FlatCache> p;
+    FlatCacheSlot() = default;
+    FlatCacheSlot(const FlatCacheSlot&) {}
+    FlatCacheSlot& operator=(const FlatCacheSlot&) { p.reset(); return *this; }
+};
+
 }  // namespace rt
 
 // the C handle
@@ -43,6 +77,8 @@ struct rt_scene {
     bool options_set = false;
     std::string warnings;
     uint64_t n_spheres = 0, n_planes = 0;
+    uint64_t revision = 0;  // bumped by rt::scene_touch
+    mutable rt::FlatCacheSlot flat_cache;
 };
 
 namespace rt {
@@ -61,22 +97,13 @@ bool load_texture_file(const std::string& path, HostTexture* out, std::string* e
 // serialize::deserialize; returns RT_OK or RT_ERR_SYNTAX with `err` = "row:col: message"
 int parse_scene_text(const char* text, size_t len, rt_scene* scene, std::string* err);
 
-// Flattened scene: the reference's Vec<Object> of boxed trait objects (src/scene.rs:93-98) as tagged SoA buffers.
-struct FlatScene {
-    std::vector<SphereRec> sph;         // scan order = object order among spheres
-    std::vector<int32_t> sph_obj;
-    std::vector<PlaneRec> planes;
-    std::vector<uint32_t> obj_shape, obj_material;
-    double centroid_lo[3], centroid_hi[3];
-    double box_lo[3], box_hi[3];  // bounds of the sphere boxes (c -+ |r|); -+inf when unusable
-    double cmax, rmin;
-    int32_t max_children;
-    // 16-bit grid for the 32-byte BVH nodes (rt_types.h BvhQNode); quant == false: grid too coarse / unusable bounds
-    bool quant;
-    double q_org[3], q_cell[3];
-};
+// Called BEFORE anything changes the objects, materials or skybox faces of a scene: drops the cache entry (and with it the
+// page-lock on the vectors about to be reallocated) and bumps the revision.
+void scene_touch(rt_scene* s);
 // returns RT_OK or RT_ERR_INVALID (missing camera/background/skybox face)
 int flatten_scene(const rt_scene* s, FlatScene* out);
+// the same through the scene's cache: flattens on the first call after a change, validates every time
+int flatten_scene_cached(const rt_scene* s, std::shared_ptr<FlatCache>* out);
 // fills the fields of DeviceScene that do not point into device memory
 void fill_scene_header(const rt_scene* s, const FlatScene& f, DeviceScene* ds);
 // image-space shard + frame parameters from the scene's Options and the render options

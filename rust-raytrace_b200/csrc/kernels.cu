@@ -357,7 +357,11 @@ __global__ void __launch_bounds__(BVH_THREADS, 8) k_shadow_bvh(const __grid_cons
     uint32_t* cursor = &counters->cursor;
     uint32_t walks = 0;
     TraverseCount tc; tc.nodes = 0; tc.prims = 0;
+#ifdef RT_SHADOW_STACK64
     TravStack st; int sp = 0;
+#else
+    TravStackFixed st; int sp = 0;
+#endif
     BoxRay32 br = boxray32_none();
     int32_t cur = TRAV_EMPTY;
     float bound = 0.0f;

@@ -465,6 +465,7 @@ RT_HD unsigned long long trav_pack(int32_t node, float t) {
     return (unsigned long long)(uint32_t)node | ((unsigned long long)tb << 32);
 }
 
+RT_HD void trav_push(TravStack& st, int& sp, int32_t node, float t) { st.e[sp++] = trav_pack(node, t); }
 RT_HD int32_t trav_pop(const TravStack& st, int& sp, float bound) {
     while (sp > 0) {
         const unsigned long long e = st.e[--sp];
@@ -475,13 +476,20 @@ RT_HD int32_t trav_pop(const TravStack& st, int& sp, float bound) {
     }
     return TRAV_EMPTY;
 }
+// Shadow queries: the bound (the light's distance) never shrinks during the walk, so a child that passed the box test when
+// it was postponed still passes when it is popped -- 4-byte entries, no entry distance, no test on pop.
+struct TravStackFixed {
+    int32_t e[BVH_STACK];
+};
+RT_HD void trav_push(TravStackFixed& st, int& sp, int32_t node, float) { st.e[sp++] = node; }
+RT_HD int32_t trav_pop(const TravStackFixed& st, int& sp, float) { return sp > 0 ? st.e[--sp] : TRAV_EMPTY; }
 
 // Walk internal nodes from `cur` (near child first, far child pushed) until the next thing to do is a leaf test
 // (returns ~slot < 0) or nothing is left (TRAV_EMPTY).  Leaves are NOT tested here: postponing them keeps the lanes
 // of a warp in the same code (box tests together, sphere tests together).
 // `max_steps` bounds the walk (the kernels come back to refill finished lanes; an unfinished walk returns cur >= 0).
-template <bool QNODES>
-RT_HD int32_t trav_descend(const DeviceScene& sc, const BoxRay32& br, int32_t cur, float bound, TravStack& st, int& sp, TraverseCount& tc,
+template <bool QNODES, typename STACK>
+RT_HD int32_t trav_descend(const DeviceScene& sc, const BoxRay32& br, int32_t cur, float bound, STACK& st, int& sp, TraverseCount& tc,
                            int max_steps = 0x7FFFFFFF) {
     while (cur >= 0 && max_steps-- > 0) {
         float t0, t1;
@@ -504,7 +512,7 @@ RT_HD int32_t trav_descend(const DeviceScene& sc, const BoxRay32& br, int32_t cu
         const bool both = h0 && h1;
         const bool second = h1 && (!h0 || t1 < t0);
         const int32_t nearc = second ? c1 : c0;
-        if (both && sp < BVH_STACK) st.e[sp++] = trav_pack(second ? c0 : c1, second ? t0 : t1);
+        if (both && sp < BVH_STACK) trav_push(st, sp, second ? c0 : c1, second ? t0 : t1);
         if (h0 || h1) cur = nearc;
         else cur = trav_pop(st, sp, bound);
     }
@@ -563,7 +571,7 @@ RT_HD bool shadow_bvh(const DeviceScene& sc, const RayQ& r, double range2, Trave
     if (!s.nan && !s.any && sc.n_spheres > 0) {
         const BoxRay32 br = make_boxray32(sc, r.o, r.d);
         if (br.enter) {
-            TravStack st;
+            TravStackFixed st;
             int sp = 0;
             int32_t cur = 0;
             const float bound = shadow_bound32(range2, br.t0);

@@ -492,6 +492,7 @@ public:
         ShapeOut sh{};
         MaterialRec m{};
         parse_struct({{"bounds", [&] { sh = shape(); }}, {"material", [&] { m = material(); }}});
+        scene_touch(sc);
         sc->materials.push_back(m);
         HostObject o{};
         o.is_plane = sh.is_plane;
@@ -564,7 +565,7 @@ public:
                         parse_struct({{"px", [&] { load_texture(&f[0]); }}, {"nx", [&] { load_texture(&f[1]); }}, {"py", [&] { load_texture(&f[2]); }},
                                       {"ny", [&] { load_texture(&f[3]); }}, {"pz", [&] { load_texture(&f[4]); }}, {"nz", [&] { load_texture(&f[5]); }}});
                         sc->bg_kind = BG_SKYBOX;
-                        for (int i = 0; i < 6; i++) sc->faces[i] = std::move(f[i]);
+                        scene_touch(sc); for (int i = 0; i < 6; i++) sc->faces[i] = std::move(f[i]);
                     }}});
         sc->background_set = true;
     }
@@ -582,7 +583,7 @@ public:
     void scene() {
         parse_struct({{"objects", [&] {
                            // a repeated `objects:` field replaces the earlier vector upstream
-                           sc->objects.clear(); sc->materials.clear(); sc->n_spheres = sc->n_planes = 0;
+                           scene_touch(sc); sc->objects.clear(); sc->materials.clear(); sc->n_spheres = sc->n_planes = 0;
                            parse_vec([&] { object(); });
                        }},
                       {"lights", [&] { sc->lights.clear(); parse_vec([&] { light(); }); }},

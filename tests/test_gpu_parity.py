@@ -268,6 +268,37 @@ def test_queue_slicing_is_invisible(gpu, scenes):
     assert small.stats["kernel_launches"] > big.stats["kernel_launches"]
 
 
+def test_scene_cache_follows_edits(gpu, scenes):
+    """rt_context_create keeps the flattened, page-locked scene with the rt_scene between contexts (host_scene.h
+    FlatCache); an edit of the scene must drop it.  60k spheres with their own materials = 8 MB: the page-locked path."""
+    import copy
+    import ctypes as C
+    from importlib import import_module
+    B = import_module("rust-raytrace_b200._binding")
+    desc = scenes.random_spheres(60000, 21, 150.0, 160, 96)
+    sc = gpu.Scene(desc)
+    first = gpu.raytrace.render(sc, max_depth=3, seed=5)
+    again = gpu.raytrace.render(sc, max_depth=3, seed=5)  # second context: cached buffers
+    assert np.array_equal(first.rows, again.rows) and np.array_equal(first.ids, again.ids)
+    assert first.stats["rays_total"] == again.stats["rays_total"]
+    # a mirror ball in front of the camera, appended through the builder API to the live scene
+    L = gpu.lib()
+    ball = np.array([[0.0, 12.0, 150.0, 4.0]], dtype=np.float64)
+    mat = np.array([1], dtype=np.uint32)
+    B.check(L, L.rt_scene_add_spheres(sc.handle, 1, B.ptr(ball, C.c_double), B.ptr(mat, C.c_uint32)))
+    edited = gpu.raytrace.render(sc, max_depth=3, seed=5)
+    desc2 = copy.copy(desc)
+    desc2["objects"] = list(desc["objects"]) + [{"shape": "sphere", "center": (0.0, 12.0, 150.0), "radius": 4.0, "material": 1}]
+    fresh = gpu.raytrace.render(gpu.Scene(desc2), max_depth=3, seed=5)
+    assert np.array_equal(edited.rows, fresh.rows) and np.array_equal(edited.ids, fresh.ids)
+    assert (edited.ids == 60001).any() and not (first.ids == 60001).any()
+    # a new material reallocates the page-locked material vector
+    rgb = (C.c_double * 3)(0.5, 0.5, 0.5)
+    assert L.rt_scene_add_material_phong(sc.handle, rgb, rgb, 10.0, rgb) == len(desc["materials"])
+    after = gpu.raytrace.render(sc, max_depth=3, seed=5)
+    assert np.array_equal(after.rows, fresh.rows)
+
+
 def test_antialias_zero_is_nan_white(gpu, scenes):
     fr = gpu.raytrace.render(gpu.Scene(scenes.materials_showcase(16, 12, 1)), antialias=0)
     assert (fr.bgr == 255).all()  # 0/0 -> NaN -> code 255 (src/main.rs:56, src/color.rs:593-600)
