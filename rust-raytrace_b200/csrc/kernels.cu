@@ -546,7 +546,40 @@ __global__ void __launch_bounds__(HEAVY_THREADS) k_heavy_scan(const __grid_const
 __global__ void __launch_bounds__(SHADE_THREADS, RT_SHADE_MIN_BLOCKS) k_shade(const __grid_constant__ DeviceScene sc, const __grid_constant__ FrameParams fp, RayQueue in,
                                                          uint32_t first, uint32_t n, RayQueue out, uint32_t* out_count, ShadowQueue sq,
                                                          uint32_t* sq_count, uint32_t* overflow, double* accum, int32_t* ids) {
+#ifdef RT_SHADE_COMPACT
+    // Hits first: the threads of the CTA are dealt its rays so that the hits fill whole warps and the misses (background
+    // only) the rest.  Deeper levels mix hits and misses at random; a warp costs its full light loop however few of its
+    // lanes hit.  The rays stay inside the CTA's own 128-slot window of the queue, so the loads coalesce as before.
+    __shared__ uint8_t perm[SHADE_THREADS];
+    __shared__ uint32_t warp_hits[SHADE_THREADS / 32];
+    uint32_t li;
+    {
+        const uint32_t base = blockIdx.x * SHADE_THREADS;
+        const uint32_t own = base + threadIdx.x;
+        const uint32_t n_valid = min((uint32_t)SHADE_THREADS, n - base);
+        const bool hit = own < n && in.hit_id[first + own] >= 0;
+        const unsigned hm = __ballot_sync(0xFFFFFFFFu, hit);
+        const int w = threadIdx.x >> 5, ln = threadIdx.x & 31;
+        if (ln == 0) warp_hits[w] = (uint32_t)__popc(hm);
+        __syncthreads();
+        uint32_t hits_before = 0, hits_total = 0;
+#pragma unroll
+        for (int k = 0; k < SHADE_THREADS / 32; k++) {
+            const uint32_t c = warp_hits[k];
+            if (k < w) hits_before += c;
+            hits_total += c;
+        }
+        const uint32_t hit_rank = hits_before + (uint32_t)__popc(hm & ((1u << ln) - 1u));
+        // valid lanes before this one that missed = (valid lanes before) - (hits before)
+        const uint32_t rank = hit ? hit_rank : (own < n ? hits_total + (threadIdx.x - hit_rank) : threadIdx.x);
+        perm[rank] = (uint8_t)threadIdx.x;
+        __syncthreads();
+        li = base + perm[threadIdx.x];
+        (void)n_valid;
+    }
+#else
     const uint32_t li = blockIdx.x * SHADE_THREADS + threadIdx.x;
+#endif
     const bool active = li < n;
     ShadeCtx s;
     s.alive = false; s.lit = false;

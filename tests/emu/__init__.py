@@ -52,6 +52,7 @@ def lib():
         L.emu_quantize_bgr.argtypes = [dp, C.c_uint64, u8p]
         L.emu_quantize_bgr.restype = None
         L.emu_bvh_stats.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]
+        L.emu_flat_cache_probe.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
         _lib = L
     return _lib
 

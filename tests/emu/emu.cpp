@@ -305,6 +305,21 @@ RT_API int emu_bvh_stats(const rt_scene* s, uint64_t* n_nodes, uint32_t* max_dep
     return RT_OK;
 }
 
+// the scene's flatten cache (host_scene.h FlatCache), as rt_context_create sees it: out = {entry identity, revision,
+// spheres, planes, objects, max_children}
+RT_API int emu_flat_cache_probe(const rt_scene* s, uint64_t* out) {
+    std::shared_ptr<FlatCache> fc;
+    int rc = flatten_scene_cached(s, &fc);
+    if (rc != RT_OK) return rc;
+    out[0] = (uint64_t)(uintptr_t)fc.get();
+    out[1] = fc->revision;
+    out[2] = fc->flat.sph.size();
+    out[3] = fc->flat.planes.size();
+    out[4] = fc->flat.obj_shape.size();
+    out[5] = (uint64_t)fc->flat.max_children;
+    return RT_OK;
+}
+
 RT_API int emu_bvh_node_bytes(const rt_scene* s, uint32_t* bytes) {
     EmuScene e;
     int rc = make_scene(s, RT_ACCEL_BVH, &e);

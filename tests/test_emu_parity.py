@@ -280,3 +280,38 @@ def test_filter_is_conservative_on_odd_scenes(rt, orc, case):
     assert np.array_equal(ids, rid), "%d ids differ" % int((ids != rid).sum())
     assert np.array_equal(t, rt_, equal_nan=True) and np.array_equal(nrm, rn, equal_nan=True)
     assert emu.bvh_node_bytes(emu.Scene(desc)) == (64 if case in (2, 7) else 32)   # 4000- and 60000-wide fields: grid too coarse
+
+
+def test_flatten_cache_follows_scene_edits(scenes, monkeypatch):
+    """rt_context_create flattens a scene once and keeps the result with the rt_scene (host_scene.h FlatCache); every
+    builder call that changes objects, materials or skybox faces must drop it (it may be page-locked in place)."""
+    import ctypes as C
+    B = emu.B
+    L = emu.lib()
+    sc = emu.Scene(scenes.random_spheres(50, 3, 10.0, 32, 24))
+
+    def probe():
+        out = (C.c_uint64 * 6)()
+        assert L.emu_flat_cache_probe(sc.handle, out) == 0
+        return list(out)
+
+    a, b = probe(), probe()
+    assert a == b and a[2:5] == [50, 1, 51]          # same entry, 50 spheres + the ground plane
+    ball = np.array([[0.0, 1.0, 0.0, 1.0]])
+    mat = np.array([0], dtype=np.uint32)
+    assert L.rt_scene_add_spheres(sc.handle, 1, B.ptr(ball, C.c_double), B.ptr(mat, C.c_uint32)) == 0
+    c = probe()
+    assert c[1] > a[1] and c[2:5] == [51, 1, 52]
+    rgb = (C.c_double * 3)(0.5, 0.5, 0.5)
+    assert L.rt_scene_add_material_indirect(sc.handle, rgb, rgb, 1.0, rgb, 5) == 51  # max_children follows materials
+    d = probe()
+    assert d[1] > c[1] and d[5] == 5 and c[5] == 2
+    assert L.rt_scene_add_plane(sc.handle, (C.c_double * 3)(0, 9, 0), (C.c_double * 3)(0, -1, 0), 0) == 0
+    e = probe()
+    assert e[1] > d[1] and e[2:5] == [51, 2, 53]
+    # the node-format override is part of the key (A/B runs switch it between contexts of one scene)
+    monkeypatch.setenv("RAYTRACE_B200_BVH_NODES", "f32")
+    f = probe()
+    assert f[1] == e[1] and probe() == f
+    monkeypatch.delenv("RAYTRACE_B200_BVH_NODES")
+    assert probe()[1] == e[1]
