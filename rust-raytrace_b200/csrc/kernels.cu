@@ -546,40 +546,7 @@ __global__ void __launch_bounds__(HEAVY_THREADS) k_heavy_scan(const __grid_const
 __global__ void __launch_bounds__(SHADE_THREADS, RT_SHADE_MIN_BLOCKS) k_shade(const __grid_constant__ DeviceScene sc, const __grid_constant__ FrameParams fp, RayQueue in,
                                                          uint32_t first, uint32_t n, RayQueue out, uint32_t* out_count, ShadowQueue sq,
                                                          uint32_t* sq_count, uint32_t* overflow, double* accum, int32_t* ids) {
-#ifdef RT_SHADE_COMPACT
-    // Hits first: the threads of the CTA are dealt its rays so that the hits fill whole warps and the misses (background
-    // only) the rest.  Deeper levels mix hits and misses at random; a warp costs its full light loop however few of its
-    // lanes hit.  The rays stay inside the CTA's own 128-slot window of the queue, so the loads coalesce as before.
-    __shared__ uint8_t perm[SHADE_THREADS];
-    __shared__ uint32_t warp_hits[SHADE_THREADS / 32];
-    uint32_t li;
-    {
-        const uint32_t base = blockIdx.x * SHADE_THREADS;
-        const uint32_t own = base + threadIdx.x;
-        const uint32_t n_valid = min((uint32_t)SHADE_THREADS, n - base);
-        const bool hit = own < n && in.hit_id[first + own] >= 0;
-        const unsigned hm = __ballot_sync(0xFFFFFFFFu, hit);
-        const int w = threadIdx.x >> 5, ln = threadIdx.x & 31;
-        if (ln == 0) warp_hits[w] = (uint32_t)__popc(hm);
-        __syncthreads();
-        uint32_t hits_before = 0, hits_total = 0;
-#pragma unroll
-        for (int k = 0; k < SHADE_THREADS / 32; k++) {
-            const uint32_t c = warp_hits[k];
-            if (k < w) hits_before += c;
-            hits_total += c;
-        }
-        const uint32_t hit_rank = hits_before + (uint32_t)__popc(hm & ((1u << ln) - 1u));
-        // valid lanes before this one that missed = (valid lanes before) - (hits before)
-        const uint32_t rank = hit ? hit_rank : (own < n ? hits_total + (threadIdx.x - hit_rank) : threadIdx.x);
-        perm[rank] = (uint8_t)threadIdx.x;
-        __syncthreads();
-        li = base + perm[threadIdx.x];
-        (void)n_valid;
-    }
-#else
     const uint32_t li = blockIdx.x * SHADE_THREADS + threadIdx.x;
-#endif
     const bool active = li < n;
     ShadeCtx s;
     s.alive = false; s.lit = false;
@@ -597,24 +564,37 @@ __global__ void __launch_bounds__(SHADE_THREADS, RT_SHADE_MIN_BLOCKS) k_shade(co
         const C3 add = shade_begin(sc, fp, o, d, T, in.sig[i], in.key[i], depth, hid, in.hit_t[i], s);
         accum_add(accum, pixel, add);
     }
-    // Queue slots for everything this warp will emit are reserved up front, one atomic per queue (both in flight
-    // together, their ~1 us round trip overlapped with the light arithmetic) instead of one per light and child slot.
+    // Queue slots for everything this CTA will emit are reserved up front with ONE atomic per queue.  (One per warp was a
+    // third of this kernel's stall samples: 2 x 260k returning atomics per 4K level on the same line of Counters queue up
+    // in one L2 slice; ncu source view, profiles/r01_v17_ncu_k_shade_stalls.md.)  The warps leave their counts in
+    // shared memory, thread 0 reserves for all of them, and every warp takes its share in warp order.
     // Every lit hit casts a shadow ray at every light (src/scene.rs:117-155 tests occlusion only), so the count is known.
     const unsigned FULL = 0xFFFFFFFFu;
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned below = (1u << lane) - 1u;
     const bool lit = s.alive && s.lit;
     const unsigned lit_m = __ballot_sync(FULL, lit);
     const uint32_t n_lit = (uint32_t)__popc(lit_m);
     uint32_t n_child = 0;
     for (uint32_t k = 0; k < (uint32_t)sc.max_children; k++) n_child += (uint32_t)__popc(__ballot_sync(FULL, shade_child_wanted(s, k)));
-    uint32_t sbase = 0, cbase = 0;
-    if (lane == 0) {
-        if (n_lit * sc.n_lights) sbase = atomicAdd(sq_count, n_lit * sc.n_lights);
-        if (n_child) cbase = atomicAdd(out_count, n_child);
+    constexpr int SHADE_WARPS = SHADE_THREADS / 32;
+    __shared__ uint32_t w_shadow[SHADE_WARPS], w_child[SHADE_WARPS], cta_base[2];
+    if (lane == 0) { w_shadow[warp] = n_lit * sc.n_lights; w_child[warp] = n_child; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t ts = 0, tc = 0;
+#pragma unroll
+        for (int k = 0; k < SHADE_WARPS; k++) { ts += w_shadow[k]; tc += w_child[k]; }
+        uint32_t bs = 0, bc = 0;
+        if (ts) bs = atomicAdd(sq_count, ts);
+        if (tc) bc = atomicAdd(out_count, tc);
+        cta_base[0] = bs; cta_base[1] = bc;
     }
-    sbase = __shfl_sync(FULL, sbase, 0);
-    cbase = __shfl_sync(FULL, cbase, 0);
+    __syncthreads();
+    uint32_t sbase = cta_base[0], cbase = cta_base[1];
+#pragma unroll
+    for (int k = 0; k < SHADE_WARPS; k++)
+        if (k < warp) { sbase += w_shadow[k]; cbase += w_child[k]; }
     // light loop: light-major slots, so the lanes of a warp store side by side and rays to one light stay together
     const uint32_t lit_rank = (uint32_t)__popc(lit_m & below);
     for (uint32_t li2 = 0; li2 < sc.n_lights; li2++) {
