@@ -61,18 +61,29 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// warp-aggregated queue append: one atomicAdd per warp.  Must be called by all 32 lanes.
-// Returns the slot for lanes with want == true (0xFFFFFFFF when the queue is full -> overflow flag).
+// queue append with one atomicAdd per CTA (returning atomics on one counter queue up in its L2 slice: see k_shade).
+// Returns the slot for threads with want == true (0xFFFFFFFF when the queue is full -> overflow flag).  Must be
+// called by all THREADS threads of the block, once.
 // ---------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t warp_append(bool want, uint32_t* counter, uint32_t cap, uint32_t* overflow) {
+template <int THREADS>
+__device__ __forceinline__ uint32_t block_append(bool want, uint32_t* counter, uint32_t cap, uint32_t* overflow) {
+    __shared__ uint32_t w_count[THREADS / 32];
+    __shared__ uint32_t base_s;
     const unsigned m = __ballot_sync(0xFFFFFFFFu, want);
-    if (m == 0) return 0xFFFFFFFFu;
-    const int lane = threadIdx.x & 31;
-    const int leader = __ffs(m) - 1;
-    uint32_t base = 0;
-    if (lane == leader) base = atomicAdd(counter, (uint32_t)__popc(m));
-    base = __shfl_sync(0xFFFFFFFFu, base, leader);
-    uint32_t slot = base + (uint32_t)__popc(m & ((1u << lane) - 1u));
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) w_count[warp] = (uint32_t)__popc(m);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t total = 0;
+#pragma unroll
+        for (int k = 0; k < THREADS / 32; k++) total += w_count[k];
+        base_s = total ? atomicAdd(counter, total) : 0u;
+    }
+    __syncthreads();
+    uint32_t slot = base_s + (uint32_t)__popc(m & ((1u << lane) - 1u));
+#pragma unroll
+    for (int k = 0; k < THREADS / 32; k++)
+        if (k < warp) slot += w_count[k];
     if (want && slot >= cap) {
         *overflow = 1u;
         return 0xFFFFFFFFu;
@@ -114,7 +125,7 @@ __global__ void __launch_bounds__(256) k_primary(const __grid_constant__ DeviceS
         ck = child_key(sk, CODE_CAMERA0 + cs);
         camera_project(sc.camera, px, py, ck, o, d);
     }
-    const uint32_t s = warp_append(valid, q_count, q.cap, overflow);
+    const uint32_t s = block_append<256>(valid, q_count, q.cap, overflow);
     if (s != 0xFFFFFFFFu) {
         q.ox[s] = o.x; q.oy[s] = o.y; q.oz[s] = o.z;
         q.dx[s] = d.x; q.dy[s] = d.y; q.dz[s] = d.z;
@@ -234,15 +245,42 @@ __device__ __forceinline__ void flush_traverse_count(const TraverseCount& tc, Co
     }
 }
 
-// Warp-aggregated refill: every idle lane takes the next ray index off the cursor (one atomicAdd per warp).
-// Must be called by all 32 lanes.  Returns the ray index for lanes that were idle (may be >= n: nothing left).
-__device__ __forceinline__ uint32_t warp_fetch(unsigned idle_mask, uint32_t* cursor) {
+// Warp-aggregated refill: every idle lane takes the next ray index.  The warp reserves a block of `chunk` consecutive
+// rays with one atomicAdd and hands them to its idle lanes over the next few refills; only the refill that finds the
+// block short waits for the round trip to the cursor (one per ~24 rays was 5.5 % of k_shadow_bvh's stall samples).
+// Blocks are aligned powers of two, so `next` alone describes what is left (up to the next multiple of chunk;
+// FETCH_NONE = nothing).  Big launches take bigger blocks; small ones stay at 32 so that no warp sits on rays the others
+// are waiting to finish.  Must be called by all 32 lanes.  Returns the ray index for lanes that were idle (may be >= n).
+// k_closest_bvh keeps the plain form (one atomicAdd per refill): its launches are short, a warp sitting on a reserved block
+// at the end of one costs more than the waits (measured: 5.1 -> 5.3 ms per frame with blocks), and it has no register to spare.
+__device__ __forceinline__ uint32_t warp_fetch_each(unsigned idle_mask, uint32_t* cursor) {
     const int lane = threadIdx.x & 31;
     const int leader = __ffs(idle_mask) - 1;
     uint32_t base = 0;
     if (lane == leader) base = atomicAdd(cursor, (uint32_t)__popc(idle_mask));
     base = __shfl_sync(0xFFFFFFFFu, base, leader);
     return base + (uint32_t)__popc(idle_mask & ((1u << lane) - 1u));
+}
+constexpr uint32_t FETCH_NONE = 0xFFFFFFFFu;
+__device__ __forceinline__ uint32_t fetch_chunk(uint32_t n) { return n >= (1u << 24) ? 128u : (n >= (1u << 22) ? 64u : 32u); }
+__device__ __forceinline__ uint32_t warp_fetch(unsigned idle_mask, uint32_t* cursor, uint32_t& next, uint32_t chunk) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t need = (uint32_t)__popc(idle_mask);
+    const uint32_t rank = (uint32_t)__popc(idle_mask & ((1u << lane) - 1u));
+    const uint32_t avail = next == FETCH_NONE ? 0u : chunk - (next & (chunk - 1u));
+    uint32_t idx = next + rank;
+    if (avail > need) {
+        next += need;
+    } else if (avail == need) {
+        next = FETCH_NONE;
+    } else {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(cursor, chunk);
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+        if (rank >= avail) idx = base + (rank - avail);
+        next = need - avail == chunk ? FETCH_NONE : base + (need - avail);
+    }
+    return idx;
 }
 
 #ifndef RT_FETCH_MIN_IDLE
@@ -296,7 +334,7 @@ __global__ void __launch_bounds__(BVH_THREADS, 8) k_closest_bvh(const __grid_con
     while (true) {
         const unsigned idle = __ballot_sync(0xFFFFFFFFu, !active);
         if (idle != 0u && !exhausted && (__popc(idle) >= FETCH_MIN_IDLE || idle == 0xFFFFFFFFu)) {
-            const uint32_t li = warp_fetch(idle, cursor);
+            const uint32_t li = warp_fetch_each(idle, cursor);
             if (!active) {
                 if (li < n) {
                     ray = first + li;
@@ -355,6 +393,8 @@ __global__ void __launch_bounds__(BVH_THREADS, 8) k_shadow_bvh(const __grid_cons
                                                                uint32_t* heavy, uint32_t heavy_walks) {
     __shared__ TravSmem sm;
     uint32_t* cursor = &counters->cursor;
+    uint32_t range_next = FETCH_NONE;
+    const uint32_t chunk = fetch_chunk(n);
     uint32_t walks = 0;
     TraverseCount tc; tc.nodes = 0; tc.prims = 0;
 #ifdef RT_SHADOW_STACK64
@@ -370,7 +410,7 @@ __global__ void __launch_bounds__(BVH_THREADS, 8) k_shadow_bvh(const __grid_cons
     while (true) {
         const unsigned idle = __ballot_sync(0xFFFFFFFFu, !active);
         if (idle != 0u && !exhausted && (__popc(idle) >= FETCH_MIN_IDLE || idle == 0xFFFFFFFFu)) {
-            const uint32_t li = warp_fetch(idle, cursor);
+            const uint32_t li = warp_fetch(idle, cursor, range_next, chunk);
             if (!active) {
                 if (li < n) {
                     ray = li;
