@@ -1,4 +1,4 @@
-python tools/gpu_stats.py 10k 2>&1 | grep -v "^heavy"
-python tools/gpu_stats.py 1m 2>&1 | grep -v "^heavy"
-timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -2
-bash tools/gpu_ncu_src.sh s16f k_shade 10
+bash tools/gpu_check.sh s16h
+for W in spheres-1m-4k-d8 spheres-1m-8k-d8 skybox-100k-4k-16spp test-scene-800-1024spp cornell-4k-1spp; do
+  timeout 600 python bench.py --workload $W --no-cpu-baseline > gpurun_out/s16h_bench_$W.json 2> gpurun_out/s16h_bench_$W.err; echo "bench $W rc=$?"; cut -c1-400 gpurun_out/s16h_bench_$W.json
+done
