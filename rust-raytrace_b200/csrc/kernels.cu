@@ -283,6 +283,9 @@ __device__ __forceinline__ uint32_t warp_fetch(unsigned idle_mask, uint32_t* cur
     return idx;
 }
 
+#ifndef RT_BVH_MIN_BLOCKS
+#define RT_BVH_MIN_BLOCKS 8  // 64 registers; 9 and 10 CTAs per SM (56 / 48 registers) spill in the walk: measured slower
+#endif
 #ifndef RT_FETCH_MIN_IDLE
 #define RT_FETCH_MIN_IDLE 16
 #endif
@@ -316,7 +319,7 @@ __device__ __forceinline__ RayQ parked_ray(const TravSmem& sm) {
 }
 
 template <bool QNODES>
-__global__ void __launch_bounds__(BVH_THREADS, 8) k_closest_bvh(const __grid_constant__ DeviceScene sc, RayQueue q, uint32_t first, uint32_t n, Counters* counters,
+__global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_closest_bvh(const __grid_constant__ DeviceScene sc, RayQueue q, uint32_t first, uint32_t n, Counters* counters,
                                                                 uint32_t* heavy, uint32_t heavy_walks) {
     __shared__ TravSmem sm;
     uint32_t* cursor = &counters->cursor;
@@ -389,7 +392,7 @@ __global__ void __launch_bounds__(BVH_THREADS, 8) k_closest_bvh(const __grid_con
 }
 
 template <bool QNODES>
-__global__ void __launch_bounds__(BVH_THREADS, 8) k_shadow_bvh(const __grid_constant__ DeviceScene sc, ShadowQueue sq, uint32_t n, double* accum, Counters* counters,
+__global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_shadow_bvh(const __grid_constant__ DeviceScene sc, ShadowQueue sq, uint32_t n, double* accum, Counters* counters,
                                                                uint32_t* heavy, uint32_t heavy_walks) {
     __shared__ TravSmem sm;
     uint32_t* cursor = &counters->cursor;
@@ -782,7 +785,7 @@ static void l_closest(cudaStream_t st, const DeviceScene& sc, bool bvh, RayQueue
     if (bvh) {
         cudaMemsetAsync(&counters->cursor, 0, 2 * sizeof(uint32_t), st);  // cursor + heavy_count
         uint32_t want = div_up(n, BVH_THREADS);
-        uint32_t grid = (uint32_t)sm_count * 8u;  // 8 resident CTAs of 128 threads per SM
+        uint32_t grid = (uint32_t)sm_count * (uint32_t)RT_BVH_MIN_BLOCKS;  // resident CTAs of 128 threads per SM
         if (sc.bvh_qnodes) k_closest_bvh<true><<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, q, first, n, counters, heavy, heavy_walks(sc));
         else k_closest_bvh<false><<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, q, first, n, counters, heavy, heavy_walks(sc));
         ShadowQueue none{};
@@ -805,7 +808,7 @@ static void l_shadow(cudaStream_t st, const DeviceScene& sc, bool bvh, ShadowQue
     if (bvh) {
         cudaMemsetAsync(&counters->cursor, 0, 2 * sizeof(uint32_t), st);
         uint32_t want = div_up(n, BVH_THREADS);
-        uint32_t grid = (uint32_t)sm_count * 8u;
+        uint32_t grid = (uint32_t)sm_count * (uint32_t)RT_BVH_MIN_BLOCKS;
         if (sc.bvh_qnodes) k_shadow_bvh<true><<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters, heavy, heavy_walks(sc));
         else k_shadow_bvh<false><<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters, heavy, heavy_walks(sc));
         RayQueue none{};
