@@ -166,7 +166,12 @@ typedef struct rt_stats {
  * Requires world == 1 in opts. */
 RT_API int rt_render(const rt_scene*, const rt_render_opts*, uint8_t* bgr_rows, int32_t* primary_ids, double* accum, rt_stats* stats);
 
-/* Device-resident path (bench / multi-GPU): the scene and all buffers stay in HBM between frames. */
+/* Device-resident path (bench / multi-GPU): the scene and all buffers stay in HBM between frames.
+ * rt_context_create (and rt_render, which calls it) uploads the scene and builds the BVH on the device every time; what
+ * it keeps with the rt_scene between calls is host-side only: the flattened (structure-of-arrays) form of the objects,
+ * page-locked in place for scenes above 4 MB so that the upload is one asynchronous DMA per buffer.  Any builder call
+ * that changes objects, materials or skybox faces drops it; contexts may be created from one scene concurrently, but not
+ * while another thread is changing that scene. */
 RT_API int rt_context_create(const rt_scene*, const rt_render_opts*, rt_context** out);
 RT_API void rt_context_destroy(rt_context*);
 /* traces the shard and leaves quantised BGR rows (local_rows x bytewidth) in the context's device framebuffer */
