@@ -320,8 +320,9 @@ __device__ __forceinline__ RayQ parked_ray(const TravSmem& sm) {
 
 template <bool QNODES>
 __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_closest_bvh(const __grid_constant__ DeviceScene sc, RayQueue q, uint32_t first, uint32_t n, Counters* counters,
-                                                                uint32_t* heavy, uint32_t heavy_walks) {
+                                                                uint32_t* heavy, uint32_t heavy_walks, const uint32_t* n_dev) {
     __shared__ TravSmem sm;
+    if (n_dev) n = *n_dev;  // launched ahead of the host's count read-back (context.cu process_level)
     uint32_t* cursor = &counters->cursor;
     uint32_t walks = 0;  // bounded walks spent on the current ray
     TraverseCount tc; tc.nodes = 0; tc.prims = 0;
@@ -780,14 +781,15 @@ static uint32_t heavy_walks(const DeviceScene& sc) {
 }
 
 static void l_closest(cudaStream_t st, const DeviceScene& sc, bool bvh, RayQueue q, uint32_t first, uint32_t n, Counters* counters, int sm_count,
-                      uint32_t* heavy) {
-    if (!n) return;
+                      uint32_t* heavy, const uint32_t* n_dev) {
+    if (!n && !n_dev) return;
     if (bvh) {
         cudaMemsetAsync(&counters->cursor, 0, 2 * sizeof(uint32_t), st);  // cursor + heavy_count
         uint32_t want = div_up(n, BVH_THREADS);
         uint32_t grid = (uint32_t)sm_count * (uint32_t)RT_BVH_MIN_BLOCKS;  // resident CTAs of 128 threads per SM
-        if (sc.bvh_qnodes) k_closest_bvh<true><<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, q, first, n, counters, heavy, heavy_walks(sc));
-        else k_closest_bvh<false><<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, q, first, n, counters, heavy, heavy_walks(sc));
+        if (!n_dev && want < grid) grid = want;
+        if (sc.bvh_qnodes) k_closest_bvh<true><<<grid, BVH_THREADS, 0, st>>>(sc, q, first, n, counters, heavy, heavy_walks(sc), n_dev);
+        else k_closest_bvh<false><<<grid, BVH_THREADS, 0, st>>>(sc, q, first, n, counters, heavy, heavy_walks(sc), n_dev);
         ShadowQueue none{};
         k_heavy_scan<false><<<(uint32_t)sm_count * 4u, HEAVY_THREADS, 0, st>>>(sc, q, none, first, nullptr, counters, heavy);
     } else {

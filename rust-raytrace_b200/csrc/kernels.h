@@ -39,8 +39,10 @@ struct KernelTable {
     // Scene::intersect for rays [first, first+n) of q; fills hit_id / hit_t
     // `heavy`: device scratch of HEAVY_CAP uint32 (BVH only): rays whose traversal runs away (huge filter padding for origins
     // 10^7+ units out) are finished by a block-wide scan instead of holding one lane for milliseconds
+    // n_dev != nullptr (BVH only): the ray count is read on the device from *n_dev (first must be 0, n is ignored) -- the
+    // launch can be queued before the host knows how many rays the level holds
     void (*closest)(cudaStream_t, const DeviceScene&, bool bvh, RayQueue q, uint32_t first, uint32_t n, Counters* counters, int sm_count,
-                    uint32_t* heavy);
+                    uint32_t* heavy, const uint32_t* n_dev);
     // material evaluation: pixel accumulation, shadow-ray and child-ray emission with warp-aggregated appends
     void (*shade)(cudaStream_t, const DeviceScene&, const FrameParams&, RayQueue in, uint32_t first, uint32_t n, RayQueue out, uint32_t* out_count,
                   ShadowQueue sq, uint32_t* sq_count, uint32_t* overflow, double* accum, int32_t* ids);

@@ -1,6 +1,4 @@
-for L in rust-raytrace_b200/lib/libraytrace_b200*.so; do
-  V=$(basename $L .so | sed 's/libraytrace_b200_*//'); V=${V:-default}
-  for W in 10k 1m; do
-    RAYTRACE_B200_LIB=$PWD/$L timeout 300 python tools/gpu_stats.py $W 2>&1 | grep "render" | sed "s/^/[$V] /" | cut -c1-150
-  done
-done
+python tools/gpu_shard_stats.py 10k 8 2>&1 | tail -1
+python tools/gpu_stats.py 10k 2>&1 | grep render | cut -c1-160
+timeout 600 python -m pytest tests -m gpu -x -q > gpurun_out/s16k_pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/s16k_pytest_gpu.log
+timeout 300 python bench.py > gpurun_out/s16k_bench.json 2> gpurun_out/s16k_bench.err; echo "bench rc=$?"; cut -c1-330 gpurun_out/s16k_bench.json
