@@ -1,5 +1,5 @@
 #!/bin/bash
-# One GPU-box visit (session 16): parity of the new build, A/B of the shadow stack, context-creation phases at 1M spheres.
+# One GPU-box visit : parity of the new build, A/B of the shadow stack, context-creation phases at 1M spheres.
 O=gpurun_out; T=s16
 mkdir -p $O
 nvidia-smi --query-gpu=name,clocks.max.sm,memory.total --format=csv > $O/${T}_smi.txt 2>&1; nproc >> $O/${T}_smi.txt
