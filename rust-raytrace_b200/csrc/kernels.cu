@@ -584,8 +584,12 @@ __global__ void __launch_bounds__(HEAVY_THREADS) k_heavy_scan(const __grid_const
 // ---------------------------------------------------------------------------------------------------------
 // k_shade
 // ---------------------------------------------------------------------------------------------------------
+// 4 CTAs per SM = 128 registers (52 bytes spilled; the kernel wants 176): 16 warps instead of 12 to cover the HBM latency of
+// the ray record and the dependent gathers.  Measured once the queue reservations had stopped queueing in L2 (before that
+// more warps only meant more contention: 7.75 ms vs 6.15): 3 / 4 / 5 CTAs = 5.20 / 4.23 / 4.53 ms per 10k frame, 4.00 / 3.28 /
+// 3.52 ms at 1M.
 #ifndef RT_SHADE_MIN_BLOCKS
-#define RT_SHADE_MIN_BLOCKS 3
+#define RT_SHADE_MIN_BLOCKS 4
 #endif
 __global__ void __launch_bounds__(SHADE_THREADS, RT_SHADE_MIN_BLOCKS) k_shade(const __grid_constant__ DeviceScene sc, const __grid_constant__ FrameParams fp, RayQueue in,
                                                          uint32_t first, uint32_t n, RayQueue out, uint32_t* out_count, ShadowQueue sq,
