@@ -6,8 +6,8 @@
 //   k_closest_scan  src/scene.rs:247-249 + src/shapes.rs:50-112          sphere records staged through shared memory
 //                                                                        with 1-D TMA bulk copies (cp.async.bulk + mbarrier)
 //   k_closest_bvh   same, through the device-built LBVH                  persistent warps pulling rays off a cursor
-//   k_shade         src/raytrace.rs:30-256, src/scene.rs:117-155,        material switch on a tag, warp-aggregated queue
-//                   src/texture.rs:39-58, src/color.rs ops               appends (__ballot_sync/__popc/__shfl_sync)
+//   k_shade         src/raytrace.rs:30-256, src/scene.rs:117-155,        material switch on a tag; queue slots reserved once per
+//                   src/texture.rs:39-58, src/color.rs ops               CTA, shared out by __ballot_sync/__popc ranks
 //   k_shadow_*      src/raytrace.rs:43-50 (and siblings)                 any-hit with range, adds the pending contribution
 //   k_resolve       src/main.rs:56 + src/color.rs:593-600,628-632        threshold-table search, BGR pack, 128-bit stores
 #include <cuda_runtime.h>
