@@ -165,6 +165,12 @@ __global__ void k_quantise(const BvhNode* nodes, uint32_t n_nodes, QuantGrid g, 
     if (!ok) atomicAdd(off_grid, 1u);
 }
 
+__global__ void k_widen(const BvhQNode* qnodes, uint32_t n_nodes, BvhWNode* out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_nodes) return;
+    out[i] = widen_node(qnodes, i);
+}
+
 __global__ void k_untile(const uint32_t* gathered, uint32_t* out, uint32_t height, uint32_t words_per_row, uint32_t band_rows, uint32_t world,
                          uint32_t local_rows) {
     const uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -182,8 +188,8 @@ __global__ void k_untile(const uint32_t* gathered, uint32_t* out, uint32_t heigh
     } while (0)
 
 cudaError_t bvh_build(cudaStream_t st, const SphereRec* sph, const int32_t* sph_obj, uint32_t n, const double* clo, const double* chi,
-                      const double* q_org, const double* q_cell, const DeviceAllocator& A, BvhBuildResult* out) {
-    out->nodes = nullptr; out->qnodes = nullptr; out->sph = nullptr; out->obj = nullptr; out->n_nodes = 0; out->launches = 0;
+                      const double* q_org, const double* q_cell, const DeviceAllocator& A, BvhBuildResult* out, bool wide) {
+    out->nodes = nullptr; out->qnodes = nullptr; out->wnodes = nullptr; out->sph = nullptr; out->obj = nullptr; out->n_nodes = 0; out->launches = 0;
     uint64_t* keys = nullptr; uint32_t* idx = nullptr;
     int32_t *child0 = nullptr, *child1 = nullptr, *pint = nullptr, *pleaf = nullptr;
     uint32_t* flags = nullptr; Box* boxes = nullptr;
@@ -245,6 +251,11 @@ cudaError_t bvh_build(cudaStream_t st, const SphereRec* sph, const int32_t* sph_
         BVH_CHECK(cudaStreamSynchronize(st));
         if (bad) { A.release(out->qnodes); out->qnodes = nullptr; }   // a box off the grid: keep the 64-byte nodes
         else { A.release(out->nodes); out->nodes = nullptr; }
+        if (wide && out->qnodes) {
+            BVH_CHECK(A.alloc((void**)&out->wnodes, sizeof(BvhWNode) * n_nodes));
+            k_widen<<<(n_nodes + T - 1) / T, T, 0, st>>>(out->qnodes, n_nodes, out->wnodes);
+            out->launches++;
+        }
     }
     BVH_CHECK(cudaStreamSynchronize(st));
     BVH_CHECK(cudaGetLastError());
@@ -254,8 +265,8 @@ cudaError_t bvh_build(cudaStream_t st, const SphereRec* sph, const int32_t* sph_
 
 void bvh_free(BvhBuildResult* r, const DeviceAllocator& A) {
     if (!r) return;
-    A.release(r->nodes); A.release(r->qnodes); A.release(r->sph); A.release(r->obj);
-    r->nodes = nullptr; r->qnodes = nullptr; r->sph = nullptr; r->obj = nullptr; r->n_nodes = 0;
+    A.release(r->nodes); A.release(r->qnodes); A.release(r->wnodes); A.release(r->sph); A.release(r->obj);
+    r->nodes = nullptr; r->qnodes = nullptr; r->wnodes = nullptr; r->sph = nullptr; r->obj = nullptr; r->n_nodes = 0;
 }
 
 void launch_untile(cudaStream_t st, const uint32_t* gathered, uint32_t* out, uint32_t height, uint32_t words_per_row, uint32_t band_rows,

@@ -12,6 +12,8 @@
 //   k_resolve       src/main.rs:56 + src/color.rs:593-600,628-632        threshold-table search, BGR pack, 128-bit stores
 #include <cuda_runtime.h>
 
+#include <type_traits>
+
 #include "kernels.h"
 #include "rt_device.cuh"
 
@@ -392,7 +394,9 @@ __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_closest_bvh(
     flush_traverse_count(tc, counters, 0);
 }
 
-template <bool QNODES>
+// WIDE (experimental, RAYTRACE_B200_BVH_WIDE=1): the walk goes over sc.bvh_wnodes, four boxes per visit (rt_device.cuh
+// trav_descend_wide); everything else is the same kernel.
+template <bool QNODES, bool WIDE = false>
 __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_shadow_bvh(const __grid_constant__ DeviceScene sc, ShadowQueue sq, uint32_t n, double* accum, Counters* counters,
                                                                uint32_t* heavy, uint32_t heavy_walks) {
     __shared__ TravSmem sm;
@@ -404,7 +408,7 @@ __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_shadow_bvh(c
 #ifdef RT_SHADOW_STACK64
     TravStack st; int sp = 0;
 #else
-    TravStackFixed st; int sp = 0;
+    typename std::conditional<WIDE, TravStackWide, TravStackFixed>::type st; int sp = 0;
 #endif
     BoxRay32 br = boxray32_none();
     int32_t cur = TRAV_EMPTY;
@@ -440,7 +444,10 @@ __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_shadow_bvh(c
             if (exhausted) break;
             continue;
         }
-        if (active) cur = trav_descend<QNODES>(sc, br, cur, bound, st, sp, tc, RT_DESCEND_STEPS);
+        if (active) {
+            if constexpr (WIDE) cur = trav_descend_wide(sc, br, cur, bound, st, sp, tc, RT_DESCEND_STEPS / 2);
+            else cur = trav_descend<QNODES>(sc, br, cur, bound, st, sp, tc, RT_DESCEND_STEPS);
+        }
         __syncwarp();
         if (active) {
             if (cur != TRAV_EMPTY && cur < 0) {
@@ -815,7 +822,8 @@ static void l_shadow(cudaStream_t st, const DeviceScene& sc, bool bvh, ShadowQue
         cudaMemsetAsync(&counters->cursor, 0, 2 * sizeof(uint32_t), st);
         uint32_t want = div_up(n, BVH_THREADS);
         uint32_t grid = (uint32_t)sm_count * (uint32_t)RT_BVH_MIN_BLOCKS;
-        if (sc.bvh_qnodes) k_shadow_bvh<true><<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters, heavy, heavy_walks(sc));
+        if (sc.bvh_qnodes && sc.bvh_wnodes) k_shadow_bvh<true, true><<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters, heavy, heavy_walks(sc));
+        else if (sc.bvh_qnodes) k_shadow_bvh<true><<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters, heavy, heavy_walks(sc));
         else k_shadow_bvh<false><<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters, heavy, heavy_walks(sc));
         RayQueue none{};
         k_heavy_scan<true><<<(uint32_t)sm_count * 4u, HEAVY_THREADS, 0, st>>>(sc, none, sq, 0u, accum, counters, heavy);

@@ -69,6 +69,7 @@ struct DeviceAllocator {
 struct BvhBuildResult {
     BvhNode* nodes;       // [n_nodes]; null when qnodes is set
     BvhQNode* qnodes;     // [n_nodes] 32-byte grid form, when asked for and every box fits the grid
+    BvhWNode* wnodes;     // [n_nodes] wide form of qnodes (rt_types.h BvhWNode), when asked for and qnodes exists
     SphereRec* sph;       // Morton order
     int32_t* obj;
     uint32_t n_nodes;
@@ -77,8 +78,9 @@ struct BvhBuildResult {
 // Builds the LBVH over `n` spheres (scan-order records + object ids, device pointers).  Device-side throughout:
 // Morton codes -> bitonic sort -> Karras hierarchy -> bottom-up refit -> packed f32 child boxes.
 // q_org/q_cell non-null: also pack the nodes on that grid (rt_types.h BvhQNode) and drop the 64-byte form.
+// wide: also derive the wide nodes from the grid form (experimental, shadow queries).
 cudaError_t bvh_build(cudaStream_t, const SphereRec* sph, const int32_t* sph_obj, uint32_t n, const double* centroid_lo, const double* centroid_hi,
-                      const double* q_org, const double* q_cell, const DeviceAllocator& A, BvhBuildResult* out);
+                      const double* q_org, const double* q_cell, const DeviceAllocator& A, BvhBuildResult* out, bool wide = false);
 void bvh_free(BvhBuildResult* r, const DeviceAllocator& A);
 
 // de-interleave row bands after the framebuffer all-gather (rank-major input)

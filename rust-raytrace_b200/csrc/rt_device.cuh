@@ -488,6 +488,64 @@ RT_HD int32_t trav_pop(const TravStackFixed& st, int& sp, float) { return sp > 0
 // (returns ~slot < 0) or nothing is left (TRAV_EMPTY).  Leaves are NOT tested here: postponing them keeps the lanes
 // of a warp in the same code (box tests together, sphere tests together).
 // `max_steps` bounds the walk (the kernels come back to refill finished lanes; an unfinished walk returns cur >= 0).
+// ---- wide nodes (experimental, shadow queries) ----------------------------------------------------------
+// One half of wide node i from binary node `parent`: the child `which` of it is either an internal node (its own two
+// children become the half) or a leaf (the half holds the leaf itself and an empty slot that no ray can hit).
+RT_HD BvhQNode widen_half(const BvhQNode& parent, int which, const BvhQNode* qnodes) {
+    const int32_t c = which ? parent.c1 : parent.c0;
+    if (c >= 0) return qnodes[c];
+    BvhQNode h;
+    for (int a = 0; a < 3; a++) {
+        h.q[2 * a] = parent.q[6 * which + 2 * a];
+        h.q[2 * a + 1] = parent.q[6 * which + 2 * a + 1];
+        h.q[6 + 2 * a] = 0xFFFFu;  // lower plane above the upper one on every axis
+        h.q[6 + 2 * a + 1] = 0u;
+    }
+    h.c0 = c;
+    h.c1 = TRAV_EMPTY;
+    return h;
+}
+RT_HD BvhWNode widen_node(const BvhQNode* qnodes, uint32_t i) {
+    BvhWNode w;
+    const BvhQNode p = qnodes[i];
+    w.h[0] = widen_half(p, 0, qnodes);
+    w.h[1] = widen_half(p, 1, qnodes);
+    return w;
+}
+// up to three children postponed per visit and one visit per two binary levels: 3 * ceil(95 / 2)
+constexpr int BVH_STACK_WIDE = 144;
+struct TravStackWide {
+    int32_t e[BVH_STACK_WIDE];
+};
+RT_HD void trav_push(TravStackWide& st, int& sp, int32_t node, float) {
+    if (sp < BVH_STACK_WIDE) st.e[sp++] = node;
+}
+RT_HD int32_t trav_pop(const TravStackWide& st, int& sp, float) { return sp > 0 ? st.e[--sp] : TRAV_EMPTY; }
+
+// The walk of a shadow query over wide nodes.  No order among the children: the query only asks whether anything is
+// hit within the bound, which never shrinks.  Returns like trav_descend (leaf to test, TRAV_EMPTY, or an unfinished walk).
+RT_HD int32_t trav_descend_wide(const DeviceScene& sc, const BoxRay32& br, int32_t cur, float bound, TravStackWide& st, int& sp, TraverseCount& tc,
+                                int max_steps = 0x7FFFFFFF) {
+    while (cur >= 0 && max_steps-- > 0) {
+        const BvhQNode* p = sc.bvh_wnodes[cur].h;
+        const QNodeWords a = load_qnode(p), b = load_qnode(p + 1);
+        float t;
+        const int32_t c0 = (int32_t)a.w[6], c1 = (int32_t)a.w[7], c2 = (int32_t)b.w[6], c3 = (int32_t)b.w[7];
+        const bool h0 = box_hit_q(br, a.w[0], a.w[1], a.w[2], bound, t) && c0 != TRAV_EMPTY;
+        const bool h1 = box_hit_q(br, a.w[3], a.w[4], a.w[5], bound, t) && c1 != TRAV_EMPTY;
+        const bool h2 = box_hit_q(br, b.w[0], b.w[1], b.w[2], bound, t) && c2 != TRAV_EMPTY;
+        const bool h3 = box_hit_q(br, b.w[3], b.w[4], b.w[5], bound, t) && c3 != TRAV_EMPTY;
+        tc.nodes++;
+        int32_t next = TRAV_EMPTY;
+        if (h3) next = c3;
+        if (h2) { if (next != TRAV_EMPTY) trav_push(st, sp, next, 0.0f); next = c2; }
+        if (h1) { if (next != TRAV_EMPTY) trav_push(st, sp, next, 0.0f); next = c1; }
+        if (h0) { if (next != TRAV_EMPTY) trav_push(st, sp, next, 0.0f); next = c0; }
+        cur = next != TRAV_EMPTY ? next : trav_pop(st, sp, bound);
+    }
+    return cur;
+}
+
 #ifndef RT_DESCEND_MIN_LANES
 #define RT_DESCEND_MIN_LANES 0  // leave the bounded walk when fewer lanes are still in it; 8 / 12 / 16 measured: closest-hit launches
 #endif                          // 4.94 -> 5.02 / 5.12 / 5.28 ms (10k), 5.10 -> 5.75+ ms (1M); only the 1M shadow launch gained (7.73 -> 7.40)
@@ -578,7 +636,18 @@ RT_HD bool shadow_bvh(const DeviceScene& sc, const RayQ& r, double range2, Trave
     planes_shadow(sc, r, range2, s);
     if (!s.nan && !s.any && sc.n_spheres > 0) {
         const BoxRay32 br = make_boxray32(sc, r.o, r.d);
-        if (br.enter) {
+        if (br.enter && sc.bvh_wnodes) {
+            TravStackWide st;
+            int sp = 0;
+            int32_t cur = 0;
+            const float bound = shadow_bound32(range2, br.t0);
+            while (true) {
+                cur = trav_descend_wide(sc, br, cur, bound, st, sp, tc);
+                if (cur == TRAV_EMPTY) break;
+                if (leaf_shadow(sc, r, ~cur, range2, tc)) { s.any = true; break; }
+                cur = trav_pop(st, sp, bound);
+            }
+        } else if (br.enter) {
             TravStackFixed st;
             int sp = 0;
             int32_t cur = 0;

@@ -76,6 +76,14 @@ struct alignas(32) BvhQNode {
     int32_t c0, c1;
 };
 
+// 64-byte wide node (experimental; shadow queries only, RAYTRACE_B200_BVH_WIDE=1): the four grandchildren of binary node i
+// as two BvhQNode halves -- h[0] = the two children of node i's child 0, h[1] = those of its child 1 -- so a visit tests four
+// boxes behind one dependent fetch (two 256-bit loads of one 64-byte line) instead of two.  A child of node i that is a
+// leaf fills slot 0 of its half with its own box and link; slot 1 is then empty: link TRAV_EMPTY, box inside out.
+struct alignas(64) BvhWNode {
+    BvhQNode h[2];
+};
+
 // Everything a kernel needs to know about the scene (passed by value as a __grid_constant__ parameter).
 struct DeviceScene {
     uint32_t n_objects, n_spheres, n_planes, n_lights;
@@ -107,6 +115,7 @@ struct DeviceScene {
     double bvh_lo[3], bvh_hi[3];  // bounds of all sphere boxes (f64): rays are advanced to this box before the f32 filter
     const BvhQNode* bvh_qnodes;   // non-null: traverse these instead of bvh_nodes
     double q_org[3], q_cell[3];   // the grid of bvh_qnodes
+    const BvhWNode* bvh_wnodes;   // non-null (only together with bvh_qnodes): shadow queries walk these
 };
 
 // Ray queue of one wavefront level, structure of arrays (one allocation, capacity `cap`)

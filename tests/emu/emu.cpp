@@ -9,6 +9,7 @@
 // aggregation, atomics, the device BVH build kernels (sort/refit), persistent scheduling.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -27,6 +28,7 @@ struct EmuScene {
     DeviceScene ds{};
     std::vector<BvhNode> nodes;
     std::vector<BvhQNode> qnodes;  // grid form, when the scene's grid is fine enough (host_scene.cpp choose_quantisation)
+    std::vector<BvhWNode> wnodes;  // wide form for shadow queries, when RAYTRACE_B200_BVH_WIDE=1 (as in context.cu)
     std::vector<SphereRec> bvh_sph;
     std::vector<int32_t> bvh_obj;
     bool use_bvh = false;
@@ -124,6 +126,12 @@ int make_scene(const rt_scene* s, int accel, EmuScene* e) {
             e->qnodes.resize(e->nodes.size());
             for (size_t i = 0; i < e->nodes.size(); i++) e->qnodes[i] = quantise_node(e->nodes[i], e->flat.q_org, e->flat.q_cell, ok);
             if (ok) e->ds.bvh_qnodes = e->qnodes.data();
+            const char* wide = std::getenv("RAYTRACE_B200_BVH_WIDE");
+            if (ok && wide && wide[0] == '1') {
+                e->wnodes.resize(e->qnodes.size());
+                for (size_t i = 0; i < e->qnodes.size(); i++) e->wnodes[i] = widen_node(e->qnodes.data(), (uint32_t)i);
+                e->ds.bvh_wnodes = e->wnodes.data();
+            }
         }
     }
     return RT_OK;
@@ -155,6 +163,7 @@ RT_API int emu_render_shard(const rt_scene* s, const rt_render_opts* o, uint8_t*
     std::vector<double> accum(npix * 3, 0.0);
     std::vector<int32_t> idbuf(npix, -1);
     rt_stats st{};
+    TraverseCount tc_closest{0, 0}, tc_shadow{0, 0};
     const uint64_t total_paths = fp.npix_padded * fp.antialias * fp.cam_samples;
     std::vector<QRay> cur, next;
     struct SRay { ShadowRay r; uint32_t pixel; };
@@ -190,7 +199,7 @@ RT_API int emu_render_shard(const rt_scene* s, const rt_render_opts* o, uint8_t*
             for (const QRay& r : cur) {
                 RayQ rq = make_rayq(r.o, r.d);
                 int32_t id; double t;
-                if (e.use_bvh) closest_bvh(e.ds, rq, id, t, g_tc); else closest_linear(e.ds, rq, id, t);
+                if (e.use_bvh) closest_bvh(e.ds, rq, id, t, tc_closest); else closest_linear(e.ds, rq, id, t);
                 if (r.meta & META_RECORD_ID) idbuf[r.pixel] = id;
                 ShadeCtx sc;
                 C3 a = shade_begin(e.ds, fp, r.o, r.d, r.T, r.sig, r.key, r.meta & META_DEPTH_MASK, id, t, sc);
@@ -212,13 +221,15 @@ RT_API int emu_render_shard(const rt_scene* s, const rt_render_opts* o, uint8_t*
             st.rays_shadow += shadows.size();
             for (const SRay& sr : shadows) {
                 RayQ rq = make_rayq(sr.r.o, sr.r.d);
-                const bool occ = e.use_bvh ? shadow_bvh(e.ds, rq, sr.r.range2, g_tc) : shadow_linear(e.ds, rq, sr.r.range2);
+                const bool occ = e.use_bvh ? shadow_bvh(e.ds, rq, sr.r.range2, tc_shadow) : shadow_linear(e.ds, rq, sr.r.range2);
                 if (!occ) add(sr.pixel, sr.r.c);
             }
             cur.swap(next);
         }
     }
     st.rays_total = st.rays_primary + st.rays_secondary + st.rays_shadow;
+    st.bvh_nodes_visited[0] = tc_closest.nodes; st.bvh_nodes_visited[1] = tc_shadow.nodes;
+    st.bvh_prims_tested[0] = tc_closest.prims; st.bvh_prims_tested[1] = tc_shadow.prims;
     st.local_rows = fp.local_rows; st.bytewidth = bytewidth;
     st.accel_used = e.use_bvh ? RT_ACCEL_BVH : RT_ACCEL_LINEAR;
     st.n_bvh_nodes = e.nodes.size();

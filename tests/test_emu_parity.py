@@ -315,3 +315,64 @@ def test_flatten_cache_follows_scene_edits(scenes, monkeypatch):
     assert f[1] == e[1] and probe() == f
     monkeypatch.delenv("RAYTRACE_B200_BVH_NODES")
     assert probe()[1] == e[1]
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# experimental wide nodes for shadow queries (RAYTRACE_B200_BVH_WIDE=1; rt_types.h BvhWNode, rt_device.cuh trav_descend_wide)
+# ---------------------------------------------------------------------------------------------------------------------
+def _wide_scenes(rt, scenes):
+    S = rt.scene
+    out = [("random800", scenes.random_spheres(800, 5, 12.0, 8, 8))]
+    for n in (1, 2, 3, 5, 65):
+        out.append(("tiny%d" % n, scenes.random_spheres(n, 40 + n, 3.0, 8, 8)))
+    b = S.SceneBuilder()
+    m = b.add_material(S.PhongMaterial((0.5, 0.5, 0.5), (0, 0, 0), 1.0, (0, 0, 0)))
+    b.add_object(S.Plane((0, -1, 0), (0, 1, 0)), m)
+    rng = np.random.default_rng(11)
+    c = rng.uniform(-5, 5, size=(60, 3))
+    r = rng.uniform(0.05, 1.5, size=60)
+    data = np.concatenate([np.c_[c, r], np.c_[c, r], np.c_[c[:20], r[:20] * 0.5], [[0, 0, 0, 40.0], [0, 0, 0, 1e-3], [30.0, 0, 0, 1.0]]])
+    b.add_spheres(data, np.zeros(len(data), dtype=np.uint32))
+    b.camera = S.SimplePerspectiveCamera.new((0, 0, 20), (0, 0, -1), (0, 1, 0), 2.0)
+    b.background = S.SolidColorBackground((0, 0, 0))
+    b.options = S.Options(8, 8, 1)
+    out.append(("degenerate", b.build()))
+    return out
+
+
+def test_wide_shadow_walk_equals_scan_and_binary_walk(rt, orc, scenes, monkeypatch):
+    """the four-wide shadow walk answers every query like the linear scan (and like the binary walk it is derived from)"""
+    rng = np.random.default_rng(7)
+    for name, desc in _wide_scenes(rt, scenes):
+        rays = _rays(rng, 6000, 14.0, 8.0)
+        r2 = np.where(rng.uniform(size=6000) < 0.3, -1.0, rng.uniform(0.0, 30.0, 6000) ** 2)
+        monkeypatch.delenv("RAYTRACE_B200_BVH_WIDE", raising=False)
+        scan = emu.shadow_rays(emu.Scene(desc), rays, r2, accel=rt.ACCEL_LINEAR)
+        binary = emu.shadow_rays(emu.Scene(desc), rays, r2, accel=rt.ACCEL_BVH)
+        monkeypatch.setenv("RAYTRACE_B200_BVH_WIDE", "1")
+        wide = emu.shadow_rays(emu.Scene(desc), rays, r2, accel=rt.ACCEL_BVH)
+        assert np.array_equal(binary, scan), name
+        assert np.array_equal(wide, scan), name
+    monkeypatch.delenv("RAYTRACE_B200_BVH_WIDE")
+
+
+def test_wide_shadow_walk_renders_the_oracle_frame(rt, orc, scenes, monkeypatch):
+    desc = scenes.random_spheres(1500, 0x5EED0003, 25.0, 96, 54)
+    ref = orc.OracleScene(desc).render(max_depth=6, seed=3)
+    monkeypatch.setenv("RAYTRACE_B200_BVH_WIDE", "1")
+    got = emu.render(emu.Scene(desc), max_depth=6, seed=3, accel=rt.ACCEL_BVH)
+    check(got, ref, "spheres1500 wide")
+    assert ref["stats"]["shadow_rays"] > 96 * 54
+
+
+def test_wide_nodes_halve_the_dependent_fetches(rt, scenes, monkeypatch):
+    """what the wide nodes are for: about half as many node visits per shadow query (each one fetch of 64 bytes)"""
+    desc = scenes.random_spheres(1500, 0x5EED0003, 25.0, 96, 54)
+    monkeypatch.delenv("RAYTRACE_B200_BVH_WIDE", raising=False)
+    a = emu.render(emu.Scene(desc), max_depth=3, seed=3, accel=rt.ACCEL_BVH)
+    monkeypatch.setenv("RAYTRACE_B200_BVH_WIDE", "1")
+    b = emu.render(emu.Scene(desc), max_depth=3, seed=3, accel=rt.ACCEL_BVH)
+    va, vb = a["stats"]["bvh_nodes_visited"]["shadow"], b["stats"]["bvh_nodes_visited"]["shadow"]
+    assert a["stats"]["bvh_nodes_visited"]["closest"] == b["stats"]["bvh_nodes_visited"]["closest"] > 0
+    assert np.array_equal(a["bgr"], b["bgr"])
+    assert 0.35 * va < vb < 0.7 * va, (va, vb)
