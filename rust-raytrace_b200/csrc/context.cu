@@ -235,7 +235,7 @@ struct DeviceSceneHolder {
             CUDA_TRY(cudaEventRecord(e0, st));
             // experimental: shadow queries over four-wide nodes (rt_types.h BvhWNode); not the default until measured
             const char* wide_env = std::getenv("RAYTRACE_B200_BVH_WIDE");
-            const bool wide = wide_env && wide_env[0] == '1';
+            const bool wide = wide_env && (wide_env[0] == '1' || wide_env[0] == '2');  // 1: shadow queries, 2: closest-hit queries too
             cudaError_t e = bvh_build(st, ds.sph, ds.sph_obj, ds.n_spheres, clo, chi, f.quant ? f.q_org : nullptr, f.quant ? f.q_cell : nullptr, g_cache_allocator, &bvh,
                                       wide);
             if (e != cudaSuccess) { set_error(std::string("bvh_build: ") + cudaGetErrorString(e)); return RT_ERR_CUDA; }
@@ -245,7 +245,7 @@ struct DeviceSceneHolder {
             cudaEventElapsedTime(&ms, e0, e1);
             bvh_ms = ms;
             cudaEventDestroy(e0); cudaEventDestroy(e1);
-            ds.bvh_nodes = bvh.nodes; ds.bvh_qnodes = bvh.qnodes; ds.bvh_wnodes = bvh.wnodes; ds.bvh_sph = bvh.sph; ds.bvh_obj = bvh.obj; ds.n_bvh_nodes = bvh.n_nodes;
+            ds.bvh_nodes = bvh.nodes; ds.bvh_qnodes = bvh.qnodes; ds.bvh_wnodes = bvh.wnodes; ds.bvh_wide_closest = (bvh.wnodes && wide_env[0] == '2') ? 1u : 0u; ds.bvh_sph = bvh.sph; ds.bvh_obj = bvh.obj; ds.n_bvh_nodes = bvh.n_nodes;
             if ((rc = dev_alloc(&heavy, HEAVY_WORDS)) != RT_OK) return rc;
             allocs.push_back(heavy);
             CUDA_TRY(cudaMemsetAsync(heavy + HEAVY_CAP, 0, sizeof(HeavyScratch), st));

@@ -277,6 +277,7 @@ void fill_scene_header(const rt_scene* s, const FlatScene& f, DeviceScene* ds) {
     for (int a = 0; a < 3; a++) { ds->bvh_lo[a] = f.box_lo[a]; ds->bvh_hi[a] = f.box_hi[a]; }
     ds->bvh_qnodes = nullptr;  // set by the owner of the device buffers when f.quant
     ds->bvh_wnodes = nullptr;
+    ds->bvh_wide_closest = 0;
     for (int a = 0; a < 3; a++) { ds->q_org[a] = f.q_org[a]; ds->q_cell[a] = f.q_cell[a]; }
 }
 

@@ -320,7 +320,9 @@ __device__ __forceinline__ RayQ parked_ray(const TravSmem& sm) {
     return make_rayq(v3(sm.ray[0][t], sm.ray[1][t], sm.ray[2][t]), v3(sm.ray[3][t], sm.ray[4][t], sm.ray[5][t]));
 }
 
-template <bool QNODES>
+// WIDE (experimental, RAYTRACE_B200_BVH_WIDE=2): the walk goes over sc.bvh_wnodes, nearest of four boxes first
+// (rt_device.cuh trav_descend_wide_ordered); everything else is the same kernel.
+template <bool QNODES, bool WIDE = false>
 __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_closest_bvh(const __grid_constant__ DeviceScene sc, RayQueue q, uint32_t first, uint32_t n, Counters* counters,
                                                                 uint32_t* heavy, uint32_t heavy_walks, const uint32_t* n_dev) {
     __shared__ TravSmem sm;
@@ -328,7 +330,7 @@ __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_closest_bvh(
     uint32_t* cursor = &counters->cursor;
     uint32_t walks = 0;  // bounded walks spent on the current ray
     TraverseCount tc; tc.nodes = 0; tc.prims = 0;
-    TravStack st; int sp = 0;
+    typename std::conditional<WIDE, TravStackWideT, TravStack>::type st; int sp = 0;
     BoxRay32 br = boxray32_none();
     int32_t cur = TRAV_EMPTY;
     int32_t best_obj = 0x7FFFFFFF;  // the best hit's t is parked in sm.aux
@@ -368,7 +370,10 @@ __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_closest_bvh(
             if (exhausted) break;
             continue;
         }
-        if (active) cur = trav_descend<QNODES>(sc, br, cur, bound, st, sp, tc, RT_DESCEND_STEPS);
+        if (active) {
+            if constexpr (WIDE) cur = trav_descend_wide_ordered(sc, br, cur, bound, st, sp, tc, RT_DESCEND_STEPS / 2);
+            else cur = trav_descend<QNODES>(sc, br, cur, bound, st, sp, tc, RT_DESCEND_STEPS);
+        }
         __syncwarp();
         if (active) {
             if (cur == TRAV_EMPTY) {
@@ -799,7 +804,9 @@ static void l_closest(cudaStream_t st, const DeviceScene& sc, bool bvh, RayQueue
         uint32_t want = div_up(n, BVH_THREADS);
         uint32_t grid = (uint32_t)sm_count * (uint32_t)RT_BVH_MIN_BLOCKS;  // resident CTAs of 128 threads per SM
         if (!n_dev && want < grid) grid = want;
-        if (sc.bvh_qnodes) k_closest_bvh<true><<<grid, BVH_THREADS, 0, st>>>(sc, q, first, n, counters, heavy, heavy_walks(sc), n_dev);
+        if (sc.bvh_qnodes && sc.bvh_wnodes && sc.bvh_wide_closest)
+            k_closest_bvh<true, true><<<grid, BVH_THREADS, 0, st>>>(sc, q, first, n, counters, heavy, heavy_walks(sc), n_dev);
+        else if (sc.bvh_qnodes) k_closest_bvh<true><<<grid, BVH_THREADS, 0, st>>>(sc, q, first, n, counters, heavy, heavy_walks(sc), n_dev);
         else k_closest_bvh<false><<<grid, BVH_THREADS, 0, st>>>(sc, q, first, n, counters, heavy, heavy_walks(sc), n_dev);
         ShadowQueue none{};
         k_heavy_scan<false><<<(uint32_t)sm_count * 4u, HEAVY_THREADS, 0, st>>>(sc, q, none, first, nullptr, counters, heavy);

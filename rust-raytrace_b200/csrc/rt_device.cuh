@@ -546,6 +546,55 @@ RT_HD int32_t trav_descend_wide(const DeviceScene& sc, const BoxRay32& br, int32
     return cur;
 }
 
+// The same for closest-hit queries (experimental, RAYTRACE_B200_BVH_WIDE=2): the nearest of the hit children is walked
+// next, the others are postponed with their entry distances, so a pop can skip what the best hit so far has put out of
+// reach.  The order only decides how much is pruned; the answer is the leaf tests' (ties included: a box is walked
+// while its entry distance is <= the bound).
+struct TravStackWideT {
+    unsigned long long e[BVH_STACK_WIDE];
+};
+RT_HD void trav_push(TravStackWideT& st, int& sp, int32_t node, float t) {
+    if (sp < BVH_STACK_WIDE) st.e[sp++] = trav_pack(node, t);
+}
+RT_HD int32_t trav_pop(const TravStackWideT& st, int& sp, float bound) {
+    while (sp > 0) {
+        const unsigned long long e = st.e[--sp];
+        const uint32_t tb = (uint32_t)(e >> 32);
+        float t;
+        memcpy(&t, &tb, 4);
+        if (t <= bound) return (int32_t)(uint32_t)e;
+    }
+    return TRAV_EMPTY;
+}
+RT_HD void wide_take(bool hit, int32_t c, float t, int32_t& next, float& tn, TravStackWideT& st, int& sp) {
+    if (!hit) return;
+    if (next == TRAV_EMPTY) { next = c; tn = t; }
+    else if (t < tn) { trav_push(st, sp, next, tn); next = c; tn = t; }
+    else trav_push(st, sp, c, t);
+}
+RT_HD int32_t trav_descend_wide_ordered(const DeviceScene& sc, const BoxRay32& br, int32_t cur, float bound, TravStackWideT& st, int& sp,
+                                        TraverseCount& tc, int max_steps = 0x7FFFFFFF) {
+    while (cur >= 0 && max_steps-- > 0) {
+        const BvhQNode* p = sc.bvh_wnodes[cur].h;
+        const QNodeWords a = load_qnode(p), b = load_qnode(p + 1);
+        float t0, t1, t2, t3;
+        const int32_t c0 = (int32_t)a.w[6], c1 = (int32_t)a.w[7], c2 = (int32_t)b.w[6], c3 = (int32_t)b.w[7];
+        const bool h0 = box_hit_q(br, a.w[0], a.w[1], a.w[2], bound, t0) && c0 != TRAV_EMPTY;
+        const bool h1 = box_hit_q(br, a.w[3], a.w[4], a.w[5], bound, t1) && c1 != TRAV_EMPTY;
+        const bool h2 = box_hit_q(br, b.w[0], b.w[1], b.w[2], bound, t2) && c2 != TRAV_EMPTY;
+        const bool h3 = box_hit_q(br, b.w[3], b.w[4], b.w[5], bound, t3) && c3 != TRAV_EMPTY;
+        tc.nodes++;
+        int32_t next = TRAV_EMPTY;
+        float tn = 0.0f;
+        wide_take(h0, c0, t0, next, tn, st, sp);
+        wide_take(h1, c1, t1, next, tn, st, sp);
+        wide_take(h2, c2, t2, next, tn, st, sp);
+        wide_take(h3, c3, t3, next, tn, st, sp);
+        cur = next != TRAV_EMPTY ? next : trav_pop(st, sp, bound);
+    }
+    return cur;
+}
+
 #ifndef RT_DESCEND_MIN_LANES
 #define RT_DESCEND_MIN_LANES 0  // leave the bounded walk when fewer lanes are still in it; 8 / 12 / 16 measured: closest-hit launches
 #endif                          // 4.94 -> 5.02 / 5.12 / 5.28 ms (10k), 5.10 -> 5.75+ ms (1M); only the 1M shadow launch gained (7.73 -> 7.40)
@@ -614,7 +663,19 @@ RT_HD void closest_bvh(const DeviceScene& sc, const RayQ& r, int32_t& id, double
     planes_closest(sc, r, best);
     if (!best.nan && sc.n_spheres > 0) {
         const BoxRay32 br = make_boxray32(sc, r.o, r.d);
-        if (br.enter) {
+        if (br.enter && sc.bvh_wnodes && sc.bvh_wide_closest) {
+            TravStackWideT st;
+            int sp = 0;
+            int32_t cur = 0;
+            float bound = closest_bound32(best.t, br.t0);
+            while (true) {
+                cur = trav_descend_wide_ordered(sc, br, cur, bound, st, sp, tc);
+                if (cur == TRAV_EMPTY) break;
+                leaf_closest(sc, r, ~cur, best, tc);
+                bound = closest_bound32(best.t, br.t0);
+                cur = trav_pop(st, sp, bound);
+            }
+        } else if (br.enter) {
             TravStack st;
             int sp = 0;
             int32_t cur = 0;

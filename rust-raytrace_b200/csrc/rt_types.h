@@ -108,7 +108,7 @@ struct DeviceScene {
     const SphereRec* bvh_sph;  // Morton order
     const int32_t* bvh_obj;    // object index of Morton slot k
     uint32_t n_bvh_nodes;
-    uint32_t _pad0;
+    uint32_t bvh_wide_closest;  // 1: closest-hit queries walk bvh_wnodes too (experimental, RAYTRACE_B200_BVH_WIDE=2)
     double bvh_cmax;  // max over spheres of (|c|_inf + r): scale term of the per-ray box padding
     double bvh_rmin;  // min radius
     double bvh_inv2rmin;  // 0.5 / bvh_rmin, rounded up

@@ -127,10 +127,11 @@ int make_scene(const rt_scene* s, int accel, EmuScene* e) {
             for (size_t i = 0; i < e->nodes.size(); i++) e->qnodes[i] = quantise_node(e->nodes[i], e->flat.q_org, e->flat.q_cell, ok);
             if (ok) e->ds.bvh_qnodes = e->qnodes.data();
             const char* wide = std::getenv("RAYTRACE_B200_BVH_WIDE");
-            if (ok && wide && wide[0] == '1') {
+            if (ok && wide && (wide[0] == '1' || wide[0] == '2')) {
                 e->wnodes.resize(e->qnodes.size());
                 for (size_t i = 0; i < e->qnodes.size(); i++) e->wnodes[i] = widen_node(e->qnodes.data(), (uint32_t)i);
                 e->ds.bvh_wnodes = e->wnodes.data();
+                e->ds.bvh_wide_closest = wide[0] == '2' ? 1u : 0u;
             }
         }
     }

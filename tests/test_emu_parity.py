@@ -376,3 +376,33 @@ def test_wide_nodes_halve_the_dependent_fetches(rt, scenes, monkeypatch):
     assert a["stats"]["bvh_nodes_visited"]["closest"] == b["stats"]["bvh_nodes_visited"]["closest"] > 0
     assert np.array_equal(a["bgr"], b["bgr"])
     assert 0.35 * va < vb < 0.7 * va, (va, vb)
+
+
+def test_wide_closest_walk_equals_scan(rt, orc, scenes, monkeypatch):
+    """RAYTRACE_B200_BVH_WIDE=2: closest-hit queries over the wide nodes, nearest box first -- same object, same t,
+    ties and NaN rules included, as the linear scan"""
+    rng = np.random.default_rng(17)
+    for name, desc in _wide_scenes(rt, scenes):
+        rays = _rays(rng, 6000, 14.0, 8.0)
+        rays[:50, 3:] = 0.0                      # zero directions
+        rays[50:60, 0] = np.nan
+        rays[60:70, 4] = np.inf
+        monkeypatch.delenv("RAYTRACE_B200_BVH_WIDE", raising=False)
+        ids_s, t_s, _ = emu.trace_rays(emu.Scene(desc), rays, accel=rt.ACCEL_LINEAR)
+        monkeypatch.setenv("RAYTRACE_B200_BVH_WIDE", "2")
+        ids_w, t_w, _ = emu.trace_rays(emu.Scene(desc), rays, accel=rt.ACCEL_BVH)
+        assert np.array_equal(ids_w, ids_s), name
+        assert np.array_equal(t_w, t_s, equal_nan=True), name
+    monkeypatch.delenv("RAYTRACE_B200_BVH_WIDE")
+
+
+def test_wide_closest_walk_renders_the_oracle_frame(rt, orc, scenes, monkeypatch):
+    desc = scenes.random_spheres(1500, 0x5EED0003, 25.0, 96, 54)
+    ref = orc.OracleScene(desc).render(max_depth=6, seed=3)
+    monkeypatch.delenv("RAYTRACE_B200_BVH_WIDE", raising=False)
+    a = emu.render(emu.Scene(desc), max_depth=6, seed=3, accel=rt.ACCEL_BVH)
+    monkeypatch.setenv("RAYTRACE_B200_BVH_WIDE", "2")
+    b = emu.render(emu.Scene(desc), max_depth=6, seed=3, accel=rt.ACCEL_BVH)
+    check(b, ref, "spheres1500 wide closest")
+    va, vb = a["stats"]["bvh_nodes_visited"]["closest"], b["stats"]["bvh_nodes_visited"]["closest"]
+    assert 0.35 * va < vb < 0.75 * va, (va, vb)

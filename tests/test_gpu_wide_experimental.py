@@ -16,12 +16,13 @@ pytestmark = [pytest.mark.gpu,
               pytest.mark.skipif(os.environ.get("RAYTRACE_B200_TEST_WIDE") != "1", reason="opt-in: RAYTRACE_B200_TEST_WIDE=1")]
 
 
+@pytest.mark.parametrize("mode", ["1", "2"])  # 1: shadow queries over the wide nodes, 2: closest-hit queries too (never run on hardware yet)
 @pytest.mark.parametrize("n,extent", [(1, 3.0), (3, 3.0), (65, 5.0), (3000, 20.0), (60000, 90.0)])
-def test_wide_shadow_walk_renders_the_binary_walks_frame(gpu, scenes, monkeypatch, n, extent):
+def test_wide_shadow_walk_renders_the_binary_walks_frame(gpu, scenes, monkeypatch, n, extent, mode):
     desc = scenes.random_spheres(n, 100 + n, extent, 320, 180)
     monkeypatch.delenv("RAYTRACE_B200_BVH_WIDE", raising=False)
     a = gpu.raytrace.render(gpu.Scene(desc), max_depth=6, seed=9, accel=gpu.ACCEL_BVH)
-    monkeypatch.setenv("RAYTRACE_B200_BVH_WIDE", "1")
+    monkeypatch.setenv("RAYTRACE_B200_BVH_WIDE", mode)
     b = gpu.raytrace.render(gpu.Scene(desc), max_depth=6, seed=9, accel=gpu.ACCEL_BVH)
     assert np.array_equal(a.ids, b.ids)
     assert a.stats["rays_total"] == b.stats["rays_total"] and a.stats["rays_shadow"] == b.stats["rays_shadow"]
@@ -30,12 +31,15 @@ def test_wide_shadow_walk_renders_the_binary_walks_frame(gpu, scenes, monkeypatc
     if n >= 3000:
         va, vb = a.stats["bvh_nodes_visited"]["shadow"], b.stats["bvh_nodes_visited"]["shadow"]
         assert 0.35 * va < vb < 0.7 * va, (va, vb)
+        ca, cb = a.stats["bvh_nodes_visited"]["closest"], b.stats["bvh_nodes_visited"]["closest"]
+        assert (0.35 * ca < cb < 0.75 * ca) if mode == "2" else ca == cb, (ca, cb)
 
 
-def test_wide_shadow_walk_against_the_oracle(gpu, orc, scenes, monkeypatch):
+@pytest.mark.parametrize("mode", ["1", "2"])
+def test_wide_shadow_walk_against_the_oracle(gpu, orc, scenes, monkeypatch, mode):
     desc = scenes.random_spheres(1500, 0x5EED0003, 25.0, 160, 90)
     ref = orc.OracleScene(desc).render(max_depth=8, seed=3)
-    monkeypatch.setenv("RAYTRACE_B200_BVH_WIDE", "1")
+    monkeypatch.setenv("RAYTRACE_B200_BVH_WIDE", mode)
     fr = gpu.raytrace.render(gpu.Scene(desc), max_depth=8, seed=3, accel=gpu.ACCEL_BVH)
     assert np.array_equal(fr.ids, ref["ids"])
     diff = np.abs(fr.rows.astype(np.int16) - ref["bgr"].astype(np.int16))
