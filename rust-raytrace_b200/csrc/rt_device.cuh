@@ -512,8 +512,9 @@ RT_HD BvhWNode widen_node(const BvhQNode* qnodes, uint32_t i) {
     w.h[1] = widen_half(p, 1, qnodes);
     return w;
 }
-// up to three children postponed per visit and one visit per two binary levels: 3 * ceil(95 / 2)
-constexpr int BVH_STACK_WIDE = 144;
+// every hit child is pushed and one popped: up to three stay per visit, one visit per two binary levels (3 * ceil(95 / 2)),
+// plus the one in transit
+constexpr int BVH_STACK_WIDE = 148;
 struct TravStackWide {
     int32_t e[BVH_STACK_WIDE];
 };
@@ -521,6 +522,9 @@ RT_HD void trav_push(TravStackWide& st, int& sp, int32_t node, float) {
     if (sp < BVH_STACK_WIDE) st.e[sp++] = node;
 }
 RT_HD int32_t trav_pop(const TravStackWide& st, int& sp, float) { return sp > 0 ? st.e[--sp] : TRAV_EMPTY; }
+RT_HD void trav_push_if(TravStackWide& st, int& sp, bool hit, int32_t node) {
+    if (hit && sp < BVH_STACK_WIDE) st.e[sp++] = node;  // two predicated instructions, no branch
+}
 
 // The walk of a shadow query over wide nodes.  No order among the children: the query only asks whether anything is
 // hit within the bound, which never shrinks.  Returns like trav_descend (leaf to test, TRAV_EMPTY, or an unfinished walk).
@@ -536,12 +540,12 @@ RT_HD int32_t trav_descend_wide(const DeviceScene& sc, const BoxRay32& br, int32
         const bool h2 = box_hit_q(br, b.w[0], b.w[1], b.w[2], bound, t) && c2 != TRAV_EMPTY;
         const bool h3 = box_hit_q(br, b.w[3], b.w[4], b.w[5], bound, t) && c3 != TRAV_EMPTY;
         tc.nodes++;
-        int32_t next = TRAV_EMPTY;
-        if (h3) next = c3;
-        if (h2) { if (next != TRAV_EMPTY) trav_push(st, sp, next, 0.0f); next = c2; }
-        if (h1) { if (next != TRAV_EMPTY) trav_push(st, sp, next, 0.0f); next = c1; }
-        if (h0) { if (next != TRAV_EMPTY) trav_push(st, sp, next, 0.0f); next = c0; }
-        cur = next != TRAV_EMPTY ? next : trav_pop(st, sp, bound);
+        // every hit child goes on the stack and the top comes off again: no branch on which of the four were hit
+        trav_push_if(st, sp, h3, c3);
+        trav_push_if(st, sp, h2, c2);
+        trav_push_if(st, sp, h1, c1);
+        trav_push_if(st, sp, h0, c0);
+        cur = trav_pop(st, sp, bound);
     }
     return cur;
 }
@@ -566,11 +570,16 @@ RT_HD int32_t trav_pop(const TravStackWideT& st, int& sp, float bound) {
     }
     return TRAV_EMPTY;
 }
-RT_HD void wide_take(bool hit, int32_t c, float t, int32_t& next, float& tn, TravStackWideT& st, int& sp) {
-    if (!hit) return;
-    if (next == TRAV_EMPTY) { next = c; tn = t; }
-    else if (t < tn) { trav_push(st, sp, next, tn); next = c; tn = t; }
-    else trav_push(st, sp, c, t);
+// compare-exchange of two (entry distance, link) pairs: the farther one ends up in a
+RT_HD void wide_cx(float& ta, int32_t& ca, float& tb, int32_t& cb) {
+    const bool sw = ta < tb;
+    const float t = sw ? tb : ta;
+    const int32_t c = sw ? cb : ca;
+    tb = sw ? ta : tb; cb = sw ? ca : cb;
+    ta = t; ca = c;
+}
+RT_HD void trav_push_if(TravStackWideT& st, int& sp, bool hit, int32_t node, float t) {
+    if (hit && sp < BVH_STACK_WIDE) st.e[sp++] = trav_pack(node, t);
 }
 RT_HD int32_t trav_descend_wide_ordered(const DeviceScene& sc, const BoxRay32& br, int32_t cur, float bound, TravStackWideT& st, int& sp,
                                         TraverseCount& tc, int max_steps = 0x7FFFFFFF) {
@@ -578,19 +587,29 @@ RT_HD int32_t trav_descend_wide_ordered(const DeviceScene& sc, const BoxRay32& b
         const BvhQNode* p = sc.bvh_wnodes[cur].h;
         const QNodeWords a = load_qnode(p), b = load_qnode(p + 1);
         float t0, t1, t2, t3;
-        const int32_t c0 = (int32_t)a.w[6], c1 = (int32_t)a.w[7], c2 = (int32_t)b.w[6], c3 = (int32_t)b.w[7];
+        int32_t c0 = (int32_t)a.w[6], c1 = (int32_t)a.w[7], c2 = (int32_t)b.w[6], c3 = (int32_t)b.w[7];
         const bool h0 = box_hit_q(br, a.w[0], a.w[1], a.w[2], bound, t0) && c0 != TRAV_EMPTY;
         const bool h1 = box_hit_q(br, a.w[3], a.w[4], a.w[5], bound, t1) && c1 != TRAV_EMPTY;
         const bool h2 = box_hit_q(br, b.w[0], b.w[1], b.w[2], bound, t2) && c2 != TRAV_EMPTY;
         const bool h3 = box_hit_q(br, b.w[3], b.w[4], b.w[5], bound, t3) && c3 != TRAV_EMPTY;
         tc.nodes++;
-        int32_t next = TRAV_EMPTY;
-        float tn = 0.0f;
-        wide_take(h0, c0, t0, next, tn, st, sp);
-        wide_take(h1, c1, t1, next, tn, st, sp);
-        wide_take(h2, c2, t2, next, tn, st, sp);
-        wide_take(h3, c3, t3, next, tn, st, sp);
-        cur = next != TRAV_EMPTY ? next : trav_pop(st, sp, bound);
+        // A miss becomes (+inf, TRAV_EMPTY); a five-comparator network orders the four pairs far to near; the hits go on the
+        // stack in that order and the nearest comes straight off again -- no branch on which were hit, and later pops meet
+        // the postponed boxes nearest first.  (Entry distances are >= 0, never NaN: box_hit_q clamps them at 0.)
+        if (!h0) { t0 = INFINITY; c0 = TRAV_EMPTY; }
+        if (!h1) { t1 = INFINITY; c1 = TRAV_EMPTY; }
+        if (!h2) { t2 = INFINITY; c2 = TRAV_EMPTY; }
+        if (!h3) { t3 = INFINITY; c3 = TRAV_EMPTY; }
+        wide_cx(t0, c0, t1, c1);
+        wide_cx(t2, c2, t3, c3);
+        wide_cx(t0, c0, t2, c2);
+        wide_cx(t1, c1, t3, c3);
+        wide_cx(t1, c1, t2, c2);
+        trav_push_if(st, sp, c0 != TRAV_EMPTY, c0, t0);
+        trav_push_if(st, sp, c1 != TRAV_EMPTY, c1, t1);
+        trav_push_if(st, sp, c2 != TRAV_EMPTY, c2, t2);
+        trav_push_if(st, sp, c3 != TRAV_EMPTY, c3, t3);
+        cur = trav_pop(st, sp, bound);
     }
     return cur;
 }
