@@ -1,8 +1,9 @@
 """Opt-in GPU parity tests of the experimental four-wide shadow walk (RAYTRACE_B200_BVH_WIDE=1).
 
 The path is off by default: its arithmetic is covered on the CPU by tests/test_emu_parity.py::test_wide_*, and on a B200
-only the 65- and 3000-sphere cases below have run so far (both green, with the round's last GPU seconds); it has not been
-timed.  These tests only run with RAYTRACE_B200_TEST_WIDE=1, so that a fault in an unmeasured kernel cannot poison the
+only the 65- and 3000-sphere cases below have run so far, in mode 1 and with the first (branchy) formulation of the
+walk (both green, with the round's last GPU seconds); the branch-free walks and mode 2 have only run in the emulation, and
+nothing has been timed.  These tests only run with RAYTRACE_B200_TEST_WIDE=1, so that a fault in an unmeasured kernel cannot poison the
 CUDA context of the regular `-m gpu` run:
 
     RAYTRACE_B200_TEST_WIDE=1 python -m pytest tests/test_gpu_wide_experimental.py -m gpu -q
