@@ -130,7 +130,18 @@ typedef struct rt_render_opts {
     int32_t rank, world;       /* image-space shard: this context renders the row bands b with b % world == rank */
     uint32_t band_rows;        /* rows per band (multiple of 4); 0 = default (4) */
     uint64_t max_rays_in_flight; /* ray-queue capacity per wavefront level; 0 = default */
+    uint32_t tuning;           /* RT_TUNE_* bits, 0 = the measured defaults.  They choose between formulations that give
+                                  the SAME answers (tested); they exist for A/B measurements and the parity tests */
+    uint32_t _reserved;        /* must be 0 */
 } rt_render_opts;
+enum {
+    RT_TUNE_NODES_F32 = 1u,       /* BVH: keep the 64-byte f32 nodes even where the 16-bit grid is fine enough */
+    RT_TUNE_NODES_Q16 = 2u,       /* BVH: force the 32-byte grid nodes wherever the bounds allow a grid at all */
+    RT_TUNE_MORTON_AXIS = 4u,     /* BVH build: scale the Morton grid per axis instead of by the longest extent */
+    RT_TUNE_BINARY_SHADOW = 8u,   /* shadow queries walk the binary nodes instead of the four-wide ones */
+    RT_TUNE_HOST_LEVELS = 16u     /* the host reads every wavefront level's ray count back before it launches the next
+                                     level (no device-driven tail); results identical */
+};
 RT_API void rt_render_opts_default(rt_render_opts* opts);
 
 typedef struct rt_stats {
@@ -156,6 +167,9 @@ typedef struct rt_stats {
     uint64_t heavy_rays[2];
     /* bytes per BVH node in use: 32 (box planes on the scene's 16-bit grid), 64 (f32 planes; grid too coarse for the scene) or 0 */
     uint64_t bvh_node_bytes;
+    /* 1: the last frame was driven level by level from the host (RT_TUNE_HOST_LEVELS, or a queue overflowed in the
+     * device-driven frame, which is then redone); device_driven_overflows counts those redone frames of this context */
+    uint32_t host_levels, device_driven_overflows;
 } rt_stats;
 
 /* One-call frame render: upload, (build BVH), trace, resolve, copy back.
@@ -163,15 +177,17 @@ typedef struct rt_stats {
  *   primary_ids  optional host buffer of width*height int32: object index hit by the first sample's primary ray, -1 = miss
  *   accum        optional host buffer of width*height*3 doubles: per-pixel SUM of the sample colours in linear RGB;
  *                the value handed to the quantiser (src/main.rs:56) is (accum / camera_samples) / antialias
- * Requires world == 1 in opts. */
+ * Requires world == 1 in opts (rt_render_multi shards one frame over several GPUs).
+ * The device copy of the scene (flattened buffers + BVH) stays with the rt_scene between calls, per device, until a
+ * builder call changes the scene: a caller rendering frame after frame uploads and builds once. */
 RT_API int rt_render(const rt_scene*, const rt_render_opts*, uint8_t* bgr_rows, int32_t* primary_ids, double* accum, rt_stats* stats);
 
-/* Device-resident path (bench / multi-GPU): the scene and all buffers stay in HBM between frames.
- * rt_context_create (and rt_render, which calls it) uploads the scene and builds the BVH on the device every time; what
- * it keeps with the rt_scene between calls is host-side only: the flattened (structure-of-arrays) form of the objects,
- * page-locked in place for scenes above 4 MB so that the upload is one asynchronous DMA per buffer.  Any builder call
- * that changes objects, materials or skybox faces drops it; contexts may be created from one scene concurrently, but not
- * while another thread is changing that scene. */
+/* Device-resident path (bench / shards): the scene and all buffers stay in HBM between frames.
+ * The first rt_context_create (or rt_render, which calls it) for a scene on a device uploads the scene and builds the BVH
+ * there; that device copy, and the host-side flattened (structure-of-arrays) form it is uploaded from (page-locked in
+ * place for scenes above 4 MB), stay with the rt_scene for the next context.  Any builder call that changes objects,
+ * materials, lights or skybox faces drops both (stats.bvh_build_ms is 0 when the kept copy was reused).  Contexts may be
+ * created from one scene concurrently, but not while another thread is changing that scene. */
 RT_API int rt_context_create(const rt_scene*, const rt_render_opts*, rt_context** out);
 RT_API void rt_context_destroy(rt_context*);
 /* traces the shard and leaves quantised BGR rows (local_rows x bytewidth) in the context's device framebuffer */
@@ -190,6 +206,38 @@ RT_API int rt_context_synchronize(rt_context*);
  * context's own; pass NULL to go back.  The caller keeps the stream alive for as long as it is set. */
 RT_API int rt_context_set_stream(rt_context*, void* cuda_stream);
 RT_API int rt_context_set_profiling(rt_context*, int on);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * multi-GPU frames  (the same frame loop, src/main.rs:39-59, sharded over the GPUs of one node)
+ *
+ * The image is cut into bands of `band_rows` rows, band b rendered by device[b % n_devices] (scene replicated; with the
+ * counter RNG every pixel is independent, so tracing exchanges nothing).  One host thread and stream per device inside
+ * the library.  How the quantised BGR bands become one frame:
+ *   RT_GATHER_DIRECT  each device DMAs its bands to their rows of the host buffer (no device ever holds the frame)
+ *   RT_GATHER_PEER    each device's resolve kernel stores its rows into device[0]'s frame over NVLink peer access
+ *   RT_GATHER_NCCL    ncclAllGather of the shards + de-interleave on every device (libnccl.so.2 loaded at run time);
+ *                     every device ends up with the whole frame
+ *   RT_GATHER_AUTO    = DIRECT (the destination of rt_multi_render is host memory)
+ * opts->device / rank / world are ignored (set per device by the library).
+ * ------------------------------------------------------------------------------------------------------- */
+typedef struct rt_multi rt_multi;
+enum { RT_GATHER_AUTO = 0, RT_GATHER_DIRECT = 1, RT_GATHER_PEER = 2, RT_GATHER_NCCL = 3 };
+/* devices == NULL: ordinals 0 .. n_devices-1.  Uploads the scene and builds the BVH on every device (in parallel).
+ * DIRECT / PEER accept an ordinal more than once (those shards share the GPU); NCCL needs distinct devices. */
+RT_API int rt_multi_create(const rt_scene*, const rt_render_opts*, int n_devices, const int* devices, int gather, rt_multi** out);
+RT_API void rt_multi_destroy(rt_multi*);
+/* One frame.  bgr_rows: host buffer of bytewidth*height bytes (BMP row order) or NULL (PEER / NCCL: the frame stays on
+ * the device, see rt_multi_frame_device); primary_ids: optional host buffer of width*height int32.
+ * stats: sums over the devices; render_ms, bvh_build_ms and class_ms are the maximum over the devices. */
+RT_API int rt_multi_render(rt_multi*, uint8_t* bgr_rows, int32_t* primary_ids, rt_stats* stats);
+RT_API int rt_multi_device_stats(const rt_multi*, int index, rt_stats* stats);
+/* device pointer of the assembled frame on device[index]: PEER index 0, NCCL every index; else NULL */
+RT_API const void* rt_multi_frame_device(const rt_multi*, int index);
+RT_API int rt_multi_gather_used(const rt_multi*);
+/* rt_render for several GPUs: create, one frame, destroy.  Device memory, device scenes and NCCL communicators are
+ * cached between calls (rt_release_cached_memory). */
+RT_API int rt_render_multi(const rt_scene*, const rt_render_opts*, int n_devices, const int* devices, int gather, uint8_t* bgr_rows,
+                           int32_t* primary_ids, rt_stats* stats);
 
 /* Scene::intersect for a batch of rays (src/scene.rs:247-249): origin xyz + direction xyz per ray.
  * ids: object index or -1; t: hit distance (+inf on miss); normal: shape normal as upstream returns it. */

@@ -21,8 +21,9 @@ import os
 import numpy as np
 
 from . import _binding as B
-from ._binding import (ACCEL_AUTO, ACCEL_BVH, ACCEL_LINEAR, FP_FAST, FP_STRICT, RenderOpts, RtError, Stats,  # noqa: F401
-                       SyntaxError_)
+from ._binding import (ACCEL_AUTO, ACCEL_BVH, ACCEL_LINEAR, FP_FAST, FP_STRICT, GATHER_AUTO, GATHER_DIRECT, GATHER_NCCL,  # noqa: F401
+                       GATHER_PEER, TUNE_BINARY_SHADOW, TUNE_HOST_LEVELS, TUNE_MORTON_AXIS, TUNE_NODES_F32, TUNE_NODES_Q16, RenderOpts,
+                       RtError, Stats, SyntaxError_)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RAYTRACE_B200_LIB") or os.path.join(_HERE, "lib", "libraytrace_b200.so")  # env: development builds only
@@ -145,6 +146,60 @@ class Context:
         B.check(self._lib, self._lib.rt_context_set_profiling(self._h, 1 if on else 0))
 
 
+class MultiContext:
+    """`rt_multi`: one frame sharded by row bands over several GPUs of the node, inside the library (one host thread and
+    stream per device); `gather` picks how the BGR bands become one frame (GATHER_DIRECT / GATHER_PEER / GATHER_NCCL)."""
+
+    def __init__(self, scene, devices, gather=GATHER_AUTO, **opts):
+        self._lib = lib()
+        self.scene = scene
+        self.opts = B.make_opts(self._lib, **opts)
+        self.devices = list(range(devices)) if isinstance(devices, int) else list(devices)
+        arr = (C.c_int * len(self.devices))(*self.devices)
+        h = C.c_void_p()
+        B.check(self._lib, self._lib.rt_multi_create(scene.handle, C.byref(self.opts), len(self.devices), arr, int(gather), C.byref(h)))
+        self._h = h
+        w, hh, _ = scene.options()
+        self.width = self.opts.width or w
+        self.height = self.opts.height or hh
+        self.bytewidth = B.bmp_bytewidth(self._lib, self.width)
+        self.gather = int(self._lib.rt_multi_gather_used(self._h))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.rt_multi_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def render(self, want_ids=False):
+        rows = np.zeros((self.height, self.bytewidth), dtype=np.uint8)
+        ids = np.zeros((self.height, self.width), dtype=np.int32) if want_ids else None
+        st = Stats()
+        B.check(self._lib, self._lib.rt_multi_render(self._h, B.ptr(rows, C.c_uint8), B.ptr(ids, C.c_int32), C.byref(st)))
+        return Frame(self.width, self.height, rows, ids, None, st.as_dict())
+
+    def render_to(self, host_ptr):
+        """One frame into caller-owned host memory (bytewidth*height bytes, e.g. a pinned buffer); host_ptr None: the frame
+        stays in device memory (GATHER_PEER / GATHER_NCCL, see frame_device_ptr)."""
+        st = Stats()
+        dst = C.cast(C.c_void_p(host_ptr), C.POINTER(C.c_uint8)) if host_ptr else None
+        B.check(self._lib, self._lib.rt_multi_render(self._h, dst, None, C.byref(st)))
+        return st.as_dict()
+
+    def device_stats(self, index):
+        st = Stats()
+        B.check(self._lib, self._lib.rt_multi_device_stats(self._h, index, C.byref(st)))
+        return st.as_dict()
+
+    def frame_device_ptr(self, index=0):
+        return int(self._lib.rt_multi_frame_device(self._h, index) or 0)
+
+
 class _Serialize:
     """`serialize` module (src/serialize.rs)."""
 
@@ -174,6 +229,22 @@ class _Raytrace:
         st = Stats()
         B.check(L, L.rt_render(scene.handle, C.byref(o), B.ptr(rows, C.c_uint8), B.ptr(ids, C.c_int32), B.ptr(acc, C.c_double), C.byref(st)))
         return Frame(width, height, rows, ids, acc, st.as_dict())
+
+    @staticmethod
+    def render_multi(scene, devices, gather=GATHER_AUTO, want_ids=True, **opts):
+        """rt_render_multi: the same frame, sharded over `devices` (a count or a list of ordinals)."""
+        L = lib()
+        o = B.make_opts(L, **opts)
+        devs = list(range(devices)) if isinstance(devices, int) else list(devices)
+        w, h, _ = scene.options()
+        width, height = o.width or w, o.height or h
+        bw = B.bmp_bytewidth(L, width)
+        rows = np.zeros((height, bw), dtype=np.uint8)
+        ids = np.zeros((height, width), dtype=np.int32) if want_ids else None
+        st = Stats()
+        B.check(L, L.rt_render_multi(scene.handle, C.byref(o), len(devs), (C.c_int * len(devs))(*devs), int(gather), B.ptr(rows, C.c_uint8),
+                                     B.ptr(ids, C.c_int32), C.byref(st)))
+        return Frame(width, height, rows, ids, None, st.as_dict())
 
     @staticmethod
     def intersect(scene, origin_dir, **opts):

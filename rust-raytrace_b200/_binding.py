@@ -10,14 +10,16 @@ import numpy as np
 RT_OK, RT_ERR_INVALID, RT_ERR_SYNTAX, RT_ERR_IO, RT_ERR_CUDA, RT_ERR_UNSUPPORTED = 0, -1, -2, -3, -4, -5
 ACCEL_AUTO, ACCEL_LINEAR, ACCEL_BVH = 0, 1, 2
 FP_STRICT, FP_FAST = 0, 1
+GATHER_AUTO, GATHER_DIRECT, GATHER_PEER, GATHER_NCCL = 0, 1, 2, 3
 ANTIALIAS_FROM_SCENE = 0xFFFFFFFF
+TUNE_NODES_F32, TUNE_NODES_Q16, TUNE_MORTON_AXIS, TUNE_BINARY_SHADOW, TUNE_HOST_LEVELS = 1, 2, 4, 8, 16
 
 
 class RenderOpts(C.Structure):
     _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("antialias", C.c_uint32), ("max_depth", C.c_uint32),
                 ("min_significance", C.c_double), ("seed", C.c_uint64), ("accel", C.c_int32), ("fp_mode", C.c_int32),
                 ("device", C.c_int32), ("rank", C.c_int32), ("world", C.c_int32), ("band_rows", C.c_uint32),
-                ("max_rays_in_flight", C.c_uint64)]
+                ("max_rays_in_flight", C.c_uint64), ("tuning", C.c_uint32), ("_reserved", C.c_uint32)]
 
 
 class Stats(C.Structure):
@@ -25,7 +27,8 @@ class Stats(C.Structure):
                 ("paths", C.c_uint64), ("kernel_launches", C.c_uint64), ("render_ms", C.c_double), ("bvh_build_ms", C.c_double),
                 ("n_bvh_nodes", C.c_uint64), ("local_rows", C.c_uint32), ("bytewidth", C.c_uint32), ("accel_used", C.c_int32),
                 ("fp_mode_used", C.c_int32), ("bvh_nodes_visited", C.c_uint64 * 2), ("bvh_prims_tested", C.c_uint64 * 2),
-                ("class_ms", C.c_double * 5), ("class_launches", C.c_uint64 * 5), ("heavy_rays", C.c_uint64 * 2), ("bvh_node_bytes", C.c_uint64)]
+                ("class_ms", C.c_double * 5), ("class_launches", C.c_uint64 * 5), ("heavy_rays", C.c_uint64 * 2), ("bvh_node_bytes", C.c_uint64),
+                ("host_levels", C.c_uint32), ("device_driven_overflows", C.c_uint32)]
 
     CLASSES = ("primary", "closest", "shade", "shadow", "resolve")
 
@@ -103,6 +106,13 @@ API = {
     "rt_context_synchronize": (C.c_int, [C.c_void_p]),
     "rt_context_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "rt_context_set_profiling": (C.c_int, [C.c_void_p, C.c_int]),
+    "rt_multi_create": (C.c_int, [C.c_void_p, C.POINTER(RenderOpts), C.c_int, C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_void_p)]),
+    "rt_multi_destroy": (None, [C.c_void_p]),
+    "rt_multi_render": (C.c_int, [C.c_void_p, _u8p, _i32p, C.POINTER(Stats)]),
+    "rt_multi_device_stats": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(Stats)]),
+    "rt_multi_frame_device": (C.c_void_p, [C.c_void_p, C.c_int]),
+    "rt_multi_gather_used": (C.c_int, [C.c_void_p]),
+    "rt_render_multi": (C.c_int, [C.c_void_p, C.POINTER(RenderOpts), C.c_int, C.POINTER(C.c_int), C.c_int, _u8p, _i32p, C.POINTER(Stats)]),
     "rt_trace_rays": (C.c_int, [C.c_void_p, C.POINTER(RenderOpts), C.c_uint64, _dp, _i32p, _dp, _dp]),
     "rt_project": (C.c_int, [C.c_void_p, C.POINTER(RenderOpts), C.c_uint64, _dp, _dp]),
     "rt_quantize_bgr": (C.c_int, [_dp, C.c_uint64, _u8p, C.c_int]),

@@ -103,6 +103,17 @@ __global__ void k_hierarchy(const uint64_t* keys, uint32_t n, int32_t* child0, i
     if (i == 0) parent_internal[0] = -1;
 }
 
+// depth of the tree = most internal nodes above any leaf.  The traversal stacks are sized for it and the walks do not
+// check them (rt_device.cuh BVH_STACK): bvh_build refuses a deeper tree.
+__global__ void k_tree_depth(const int32_t* parent_internal, const int32_t* parent_leaf, uint32_t n, uint32_t* max_depth) {
+    const uint32_t leaf = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t d = 0;
+    if (leaf < n)
+        for (int32_t node = parent_leaf[leaf]; node >= 0; node = parent_internal[node]) d++;
+    for (int o = 16; o > 0; o >>= 1) d = max(d, __shfl_xor_sync(0xFFFFFFFFu, d, o));
+    if ((threadIdx.x & 31) == 0 && d) atomicMax(max_depth, d);
+}
+
 struct Box {
     float lo[3], hi[3];
 };
@@ -184,12 +195,14 @@ __global__ void k_untile(const uint32_t* gathered, uint32_t* out, uint32_t heigh
 #define BVH_CHECK(x)                         \
     do {                                     \
         cudaError_t e_ = (x);                \
-        if (e_ != cudaSuccess) { bvh_free(out, A); A.release(keys); A.release(idx); A.release(child0); A.release(child1); A.release(pint); A.release(pleaf); A.release(flags); A.release(boxes); return e_; } \
+        if (e_ != cudaSuccess) { bvh_free(out, A); A.release(keys); A.release(idx); A.release(child0); A.release(child1); A.release(pint); A.release(pleaf); A.release(flags); A.release(boxes); A.release(depth_dev); return e_; } \
     } while (0)
 
 cudaError_t bvh_build(cudaStream_t st, const SphereRec* sph, const int32_t* sph_obj, uint32_t n, const double* clo, const double* chi,
-                      const double* q_org, const double* q_cell, const DeviceAllocator& A, BvhBuildResult* out, bool wide) {
+                      const double* q_org, const double* q_cell, const DeviceAllocator& A, BvhBuildResult* out, bool wide, bool morton_per_axis) {
     out->nodes = nullptr; out->qnodes = nullptr; out->wnodes = nullptr; out->sph = nullptr; out->obj = nullptr; out->n_nodes = 0; out->launches = 0;
+    out->max_depth = n > 1 ? 0 : 1;
+    uint32_t* depth_dev = nullptr;
     uint64_t* keys = nullptr; uint32_t* idx = nullptr;
     int32_t *child0 = nullptr, *child1 = nullptr, *pint = nullptr, *pleaf = nullptr;
     uint32_t* flags = nullptr; Box* boxes = nullptr;
@@ -204,7 +217,7 @@ cudaError_t bvh_build(cudaStream_t st, const SphereRec* sph, const int32_t* sph_
     BVH_CHECK(A.alloc((void**)&out->obj, sizeof(int32_t) * n));
     out->n_nodes = n_nodes;
     double inv[3];
-    morton_scale(clo, chi, inv);
+    morton_scale(clo, chi, inv, morton_per_axis);
     const uint32_t T = 256;
     k_morton<<<(n_pow2 + T - 1) / T, T, 0, st>>>(sph, n, n_pow2, clo[0], clo[1], clo[2], inv[0], inv[1], inv[2], keys, idx);
     out->launches++;
@@ -235,7 +248,11 @@ cudaError_t bvh_build(cudaStream_t st, const SphereRec* sph, const int32_t* sph_
         BVH_CHECK(cudaMemsetAsync(flags, 0, sizeof(uint32_t) * n_nodes, st));
         k_hierarchy<<<(n_nodes + T - 1) / T, T, 0, st>>>(keys, n, child0, child1, pint, pleaf);
         k_refit_pack<<<(n + T - 1) / T, T, 0, st>>>(out->sph, n, child0, child1, pint, pleaf, flags, boxes, out->nodes);
-        out->launches += 2;
+        BVH_CHECK(A.alloc((void**)&depth_dev, sizeof(uint32_t)));
+        BVH_CHECK(cudaMemsetAsync(depth_dev, 0, sizeof(uint32_t), st));
+        k_tree_depth<<<(n + T - 1) / T, T, 0, st>>>(pint, pleaf, n, depth_dev);
+        BVH_CHECK(cudaMemcpyAsync(&out->max_depth, depth_dev, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+        out->launches += 3;
     }
     if (q_org && q_cell) {
         if (!flags) BVH_CHECK(A.alloc((void**)&flags, sizeof(uint32_t)));
@@ -259,6 +276,11 @@ cudaError_t bvh_build(cudaStream_t st, const SphereRec* sph, const int32_t* sph_
     }
     BVH_CHECK(cudaStreamSynchronize(st));
     BVH_CHECK(cudaGetLastError());
+    if (out->max_depth > (uint32_t)BVH_STACK || 3 * ((out->max_depth + 1) / 2) + 1 > (uint32_t)BVH_STACK_WIDE) {
+        // cannot happen for 95-bit keys; if it ever does the scene is refused instead of walked with a short stack
+        BVH_CHECK(cudaErrorInvalidValue);
+    }
+    A.release(depth_dev);
     A.release(keys); A.release(idx); A.release(child0); A.release(child1); A.release(pint); A.release(pleaf); A.release(flags); A.release(boxes);
     return cudaSuccess;
 }

@@ -1,8 +1,9 @@
 // raytrace_b200 -- the reference's binary (src/main.rs:13-60) over the C ABI of include/raytrace_b200.h.
 //
-// Same behaviour for a user of `cargo run`: reads "test_scene.txt" (src/main.rs:16), prints the scene's warnings and
-// a syntax error as "row:col: message" (src/main.rs:25-30), renders the frame at the scene's Options and writes
-// "out.bmp" (src/main.rs:34).  Everything between parsing and the file is the B200 path: this file only calls
+// Same behaviour for a user of `cargo run`: reads "test_scene.txt" (src/main.rs:16); an open / read / syntax error is ONE
+// line "error: <message>" on stdout and a normal return, exit status 0 (src/main.rs:18,23,28: `println!("error: {}", e);
+// return`), the message being the io::Error's or the SyntaxError's Display ("row:col: message"); warnings are printed as
+// the parser meets them; the frame is rendered at the scene's Options and written to "out.bmp" (src/main.rs:34).  Everything between parsing and the file is the B200 path: this file only calls
 // rt_scene_parse_file / rt_render / rt_bmp_write.  Positional arguments and flags are additions; with none given
 // the two file names are upstream's.
 #include <cstdint>
@@ -57,9 +58,9 @@ int main(int argc, char** argv) {
     char err[512] = {0};
     int rc = rt_scene_parse_file(scene_path.c_str(), &scene, err, sizeof err);
     if (rc != RT_OK) {
-        // src/main.rs:27-30: "Error parsing scene:" then the SyntaxError's Display ("row:col: message")
-        std::printf("Error parsing scene:\n%s\n", err[0] ? err : rt_last_error());
-        return 1;
+        // src/main.rs:18,23,28: println!("error: {}", e); return  -- one line on stdout, exit status 0
+        std::printf("error: %s\n", err[0] ? err : rt_last_error());
+        return 0;
     }
     const char* warnings = rt_scene_warnings(scene);
     if (warnings && warnings[0]) std::printf("%s", warnings);  // upstream println!s them while parsing (src/serialize.rs:452-464)

@@ -9,9 +9,16 @@
 //   process(level d, n rays):  for each slice:  closest-hit -> shade (emits shadow rays + level d+1 rays)
 //                                               -> shadow kernel -> process(level d+1)
 #include <cuda_runtime.h>
+#include <dlfcn.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
+#include <condition_variable>
+#include <cstddef>
+#include <functional>
+#include <memory>
+#include <thread>
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -100,29 +107,35 @@ private:
 };
 DeviceCache g_cache;
 
-// pinned read-back blocks (one Counters record per context), recycled for the same reason
+// pinned read-back blocks (Counters records of a context), recycled for the same reason
 class PinnedPool {
 public:
-    cudaError_t get(Counters** p) {
+    cudaError_t get(Counters** p, size_t* slots, size_t want) {
         {
             std::lock_guard<std::mutex> g(m_);
-            if (!free_.empty()) { *p = free_.back(); free_.pop_back(); return cudaSuccess; }
+            for (size_t i = 0; i < free_.size(); i++)
+                if (free_[i].second >= want) {
+                    *p = free_[i].first; *slots = free_[i].second;
+                    free_.erase(free_.begin() + i);
+                    return cudaSuccess;
+                }
         }
-        return cudaMallocHost((void**)p, sizeof(Counters));
+        *slots = want < 4 ? 4 : want;
+        return cudaMallocHost((void**)p, *slots * sizeof(Counters));
     }
-    void put(Counters* p) {
+    void put(Counters* p, size_t slots) {
         if (!p) return;
         std::lock_guard<std::mutex> g(m_);
-        free_.push_back(p);
+        free_.push_back({p, slots});
     }
     void trim() {
         std::lock_guard<std::mutex> g(m_);
-        for (Counters* p : free_) cudaFreeHost(p);
+        for (auto& b : free_) cudaFreeHost(b.first);
         free_.clear();
     }
 private:
     std::mutex m_;
-    std::vector<Counters*> free_;
+    std::vector<std::pair<Counters*, size_t>> free_;
 };
 PinnedPool g_pinned;
 const DeviceAllocator g_cache_allocator = {[](void** p, size_t bytes) { return g_cache.alloc(p, bytes); }, [](void* p) { g_cache.release(p); }};
@@ -170,14 +183,16 @@ void pin_flat_cache(const rt_scene* s, FlatCache* fc) {
     fc->pin = pins;
 }
 
-// device copy of a scene: flattened buffers + optional BVH
+// device copy of a scene: flattened buffers + optional BVH.  Shared (read-only) by every context created from the same
+// scene revision on the same device: rt_scene keeps the entries (host_scene.h DeviceSceneSlot).
 struct DeviceSceneHolder {
-    DeviceScene ds{};
+    DeviceScene ds{};  // the device pointers and BVH fields; the by-value header fields are refreshed per context
     std::vector<void*> allocs;
     BvhBuildResult bvh{};
     bool use_bvh = false;
     double bvh_ms = 0.0;
     uint32_t build_launches = 0;
+    int device = 0;
 
     ~DeviceSceneHolder() { release(); }
     void release() {
@@ -185,7 +200,6 @@ struct DeviceSceneHolder {
         allocs.clear();
         bvh_free(&bvh, g_cache_allocator);
     }
-    uint32_t* heavy = nullptr;  // list of rays handed from the BVH traversal to the block-wide scan (kernels.h HEAVY_CAP)
 
     // the flat buffers come from the scene's cache (host_scene.h FlatCache) and, for big scenes, from page-locked memory:
     // copies on the context's stream, the BVH build queued right behind them
@@ -202,9 +216,18 @@ struct DeviceSceneHolder {
         return RT_OK;
     }
 
-    int init(const rt_scene* s, int accel, cudaStream_t st) {
+    int init(const rt_scene* s, int accel, uint32_t tuning, cudaStream_t st) {
+        const int rc = init_queued(s, accel, tuning, st);
+        // nothing of this holder may still be in flight when its blocks go back to the cache (early return), and the flat
+        // cache entry the copies read from may go away (scene changed or freed) once this returns
+        cudaStreamSynchronize(st);
+        return rc;
+    }
+
+private:
+    int init_queued(const rt_scene* s, int accel, uint32_t tuning, cudaStream_t st) {
         std::shared_ptr<FlatCache> fc;
-        int rc = flatten_scene_cached(s, &fc);
+        int rc = flatten_scene_cached(s, tuning, &fc);
         if (rc != RT_OK) return rc;
         pin_flat_cache(s, fc.get());
         const FlatScene& f = fc->flat;
@@ -227,34 +250,65 @@ struct DeviceSceneHolder {
         std::vector<double> vals(SRGB_VALUES, SRGB_VALUES + 256), avg(SRGB_AVERAGE, SRGB_AVERAGE + 255);
         if ((rc = up_flat(vals, &ds.srgb_values, st)) != RT_OK) return rc;
         if ((rc = up_flat(avg, &ds.srgb_average, st)) != RT_OK) return rc;
+        CUDA_TRY(cudaStreamSynchronize(st));  // vals / avg are locals
         use_bvh = accel_uses_bvh(accel, ds.n_spheres);
         if (use_bvh) {
-            cudaEvent_t e0, e1;
-            CUDA_TRY(cudaEventCreate(&e0));
-            CUDA_TRY(cudaEventCreate(&e1));
-            CUDA_TRY(cudaEventRecord(e0, st));
-            // experimental: shadow queries over four-wide nodes (rt_types.h BvhWNode); not the default until measured
-            const char* wide_env = std::getenv("RAYTRACE_B200_BVH_WIDE");
-            const bool wide = wide_env && (wide_env[0] == '1' || wide_env[0] == '2');  // 1: shadow queries, 2: closest-hit queries too
-            cudaError_t e = bvh_build(st, ds.sph, ds.sph_obj, ds.n_spheres, clo, chi, f.quant ? f.q_org : nullptr, f.quant ? f.q_cell : nullptr, g_cache_allocator, &bvh,
-                                      wide);
-            if (e != cudaSuccess) { set_error(std::string("bvh_build: ") + cudaGetErrorString(e)); return RT_ERR_CUDA; }
-            CUDA_TRY(cudaEventRecord(e1, st));
-            CUDA_TRY(cudaEventSynchronize(e1));
+            cudaEvent_t e0 = nullptr, e1 = nullptr;
+            cudaError_t e = cudaEventCreate(&e0);
+            if (e == cudaSuccess) e = cudaEventCreate(&e1);
+            if (e == cudaSuccess) e = cudaEventRecord(e0, st);
+            // shadow queries walk four-wide nodes derived from the grid nodes (rt_types.h BvhWNode) unless tuned off
+            const bool wide = !(tuning & RT_TUNE_BINARY_SHADOW);
+            if (e == cudaSuccess)
+                e = bvh_build(st, ds.sph, ds.sph_obj, ds.n_spheres, clo, chi, f.quant ? f.q_org : nullptr, f.quant ? f.q_cell : nullptr, g_cache_allocator, &bvh,
+                              wide, (tuning & RT_TUNE_MORTON_AXIS) != 0);
+            if (e == cudaSuccess) e = cudaEventRecord(e1, st);
+            if (e == cudaSuccess) e = cudaEventSynchronize(e1);
             float ms = 0;
-            cudaEventElapsedTime(&ms, e0, e1);
+            if (e == cudaSuccess) cudaEventElapsedTime(&ms, e0, e1);
+            if (e0) cudaEventDestroy(e0);
+            if (e1) cudaEventDestroy(e1);
+            if (e != cudaSuccess) { set_error(std::string("bvh_build: ") + cudaGetErrorString(e)); return RT_ERR_CUDA; }
             bvh_ms = ms;
-            cudaEventDestroy(e0); cudaEventDestroy(e1);
-            ds.bvh_nodes = bvh.nodes; ds.bvh_qnodes = bvh.qnodes; ds.bvh_wnodes = bvh.wnodes; ds.bvh_wide_closest = (bvh.wnodes && wide_env[0] == '2') ? 1u : 0u; ds.bvh_sph = bvh.sph; ds.bvh_obj = bvh.obj; ds.n_bvh_nodes = bvh.n_nodes;
-            if ((rc = dev_alloc(&heavy, HEAVY_WORDS)) != RT_OK) return rc;
-            allocs.push_back(heavy);
-            CUDA_TRY(cudaMemsetAsync(heavy + HEAVY_CAP, 0, sizeof(HeavyScratch), st));
+            ds.bvh_nodes = bvh.nodes; ds.bvh_qnodes = bvh.qnodes; ds.bvh_wnodes = bvh.wnodes; ds.bvh_sph = bvh.sph; ds.bvh_obj = bvh.obj; ds.n_bvh_nodes = bvh.n_nodes;
             build_launches = bvh.launches;
         }
-        CUDA_TRY(cudaStreamSynchronize(st));  // the cache entry may go away (scene changed or freed) once this returns
         return RT_OK;
     }
 };
+
+constexpr uint32_t SCENE_TUNING = RT_TUNE_NODES_F32 | RT_TUNE_NODES_Q16 | RT_TUNE_MORTON_AXIS | RT_TUNE_BINARY_SHADOW;
+
+// The device copy of `s` for (device, accel, tuning): the one kept with the scene if its revision still matches, else a
+// fresh upload + BVH build (which then replaces it).  `fresh` tells the caller whether the build happened in this call.
+int acquire_device_scene(const rt_scene* s, int accel, uint32_t tuning, int device, cudaStream_t st, std::shared_ptr<DeviceSceneHolder>* out, bool* fresh) {
+    const uint32_t tn = tuning & SCENE_TUNING;
+    {
+        std::lock_guard<std::mutex> g(s->device_cache.m);
+        for (const DeviceSceneSlot::Entry& e : s->device_cache.entries)
+            if (e.device == device && e.accel == accel && e.tuning == tn && e.revision == s->revision) {
+                *out = std::static_pointer_cast<DeviceSceneHolder>(e.holder);
+                *fresh = false;
+                return RT_OK;
+            }
+    }
+    std::shared_ptr<DeviceSceneHolder> h = std::make_shared<DeviceSceneHolder>();
+    h->device = device;
+    const uint64_t rev = s->revision;
+    int rc = h->init(s, accel, tn, st);
+    if (rc != RT_OK) return rc;
+    {
+        std::lock_guard<std::mutex> g(s->device_cache.m);
+        auto& v = s->device_cache.entries;
+        for (size_t i = 0; i < v.size();)
+            if (v[i].revision != s->revision || (v[i].device == device && v[i].accel == accel && v[i].tuning == tn)) v.erase(v.begin() + i);
+            else i++;
+        if (rev == s->revision) v.push_back({device, accel, tn, rev, h});
+    }
+    *out = h;
+    *fresh = true;
+    return RT_OK;
+}
 
 int alloc_ray_queue(RayQueue* q, uint32_t cap, std::vector<void*>* allocs, bool full) {
     std::memset(q, 0, sizeof *q);
@@ -302,7 +356,10 @@ struct rt_context {
     int device = 0;
     cudaStream_t stream = nullptr;
     int sm_count = 148;
-    DeviceSceneHolder scene;
+    std::shared_ptr<DeviceSceneHolder> scene;  // shared, read-only
+    DeviceScene ds{};                          // the holder's pointers + this scene's by-value header (camera, background)
+    bool use_bvh = false;
+    uint32_t* heavy = nullptr;  // list of rays handed from the BVH traversal to the block-wide scan (kernels.h HEAVY_CAP)
     const KernelTable* k = nullptr;
     FrameParams fp{};
     rt_render_opts opts{};
@@ -312,14 +369,17 @@ struct rt_context {
     ShadowQueue shadowq{};
     RayQueue null_queue{};
     Counters* counters = nullptr;       // device
-    Counters* counters_host = nullptr;  // pinned
+    Counters* counters_host = nullptr;  // pinned: n_host_slots records (one per primary batch of a device-driven frame)
+    size_t n_host_slots = 0;
     double* accum = nullptr;
     int32_t* ids = nullptr;
     uint8_t* framebuffer = nullptr;
     size_t fb_bytes = 0;
+    uint8_t* final_out = nullptr;  // non-null: k_resolve writes BMP-ordered rows of the whole frame here (rt_multi peer gather)
     uint32_t slice = 0;
     uint32_t shadow_queued = 0;  // shadow rays appended since the last trace of the shadow queue
     uint64_t total_paths = 0;
+    bool host_levels = false;    // wavefront driven level by level from the host (RT_TUNE_HOST_LEVELS, or after an overflow)
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_counts = nullptr;
     rt_stats stats{};
     cudaStream_t own_stream = nullptr;
@@ -344,17 +404,23 @@ struct rt_context {
         cudaSetDevice(device);
         if (stream) cudaStreamSynchronize(stream);  // blocks go back to the cache: nothing may still be using them
         for (void* p : allocs) g_cache.release(p);
-        g_pinned.put(counters_host);
+        g_pinned.put(counters_host, n_host_slots);
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
         if (ev_counts) cudaEventDestroy(ev_counts);
         for (cudaEvent_t e : prof_events) cudaEventDestroy(e);
-        scene.release();
+        scene.reset();
         if (own_stream) cudaStreamDestroy(own_stream);
     }
 };
 
 namespace {
+
+// ---------------------------------------------------------------------------------------------------------
+// host-driven wavefront: the host reads every level's ray count back, slices levels that would not fit the next
+// queue, and flushes the shadow queue when it could overflow.  Never overflows by construction; it is the fallback of
+// the device-driven frame below and what RT_TUNE_HOST_LEVELS selects.
+// ---------------------------------------------------------------------------------------------------------
 
 // Count read-back in two halves: the copy is queued (with an event) right behind the kernel that produced the counts, the
 // host may queue more work behind it, and only then waits -- for the event, not for the stream.
@@ -365,19 +431,17 @@ int ctx_queue_counters(rt_context* c) {
 }
 int ctx_wait_counters(rt_context* c) {
     CUDA_TRY(cudaEventSynchronize(c->ev_counts));
-    if (c->counters_host->overflow) { set_error("internal error: ray queue overflow"); return RT_ERR_CUDA; }
+    if (c->counters_host->overflow) { set_error("internal error: ray queue or traversal stack overflow"); return RT_ERR_CUDA; }
     return RT_OK;
 }
 
-// The closest-hit pass over a whole level, queued BEFORE the host knows how many rays the level holds: the persistent
-// traversal kernel reads the count from the device counter its producer has just finished (stream order).  The GPU goes
-// from k_shade of level d straight into the traversal of level d + 1 while the host is still reading the counts back, so
-// the host round trip per wavefront level no longer idles it (a 1/8 shard of the 10k 4K frame: 2.85 ms, 0.07 ms of it
-// outside kernels; the whole frame 17.25 -> 17.22 ms).  BVH only: the scan kernel's grid depends on the count.
+// The closest-hit pass over a whole level, queued BEFORE the host knows how many rays the level holds: the kernel reads the
+// count from the device counter its producer has just finished (stream order).
 bool trace_level_ahead(rt_context* c, uint32_t d) {
-    if (!c->scene.use_bvh || d >= c->levels.size() || c->levels[d].cap == 0) return false;
+    if (!c->use_bvh || d >= c->levels.size() || c->levels[d].cap == 0) return false;
     c->prof_begin(1);
-    c->k->closest(c->stream, c->scene.ds, true, c->levels[d], 0, 0, c->counters, c->sm_count, c->scene.heavy, &c->counters->level_count[d]);
+    c->k->closest(c->stream, c->ds, true, c->levels[d], 0, c->levels[d].cap, c->counters, c->sm_count, c->heavy, &c->counters->level_count[d],
+                  &c->counters->lc[LC_SHARED], true);
     c->prof_end();
     return true;
 }
@@ -386,9 +450,10 @@ bool trace_level_ahead(rt_context* c, uint32_t d) {
 int flush_shadow(rt_context* c) {
     if (c->shadow_queued) {
         c->prof_begin(3);
-        c->k->shadow(c->stream, c->scene.ds, c->scene.use_bvh, c->shadowq, c->shadow_queued, c->accum, c->counters, c->sm_count, c->scene.heavy);
+        c->k->shadow(c->stream, c->ds, c->use_bvh, c->shadowq, c->shadow_queued, c->accum, c->counters, c->sm_count, c->heavy, nullptr,
+                     &c->counters->lc[LC_SHARED], true);
         c->prof_end();
-        c->stats.kernel_launches += c->scene.use_bvh ? 2 : 1;  // shadow (+ heavy scan)
+        c->stats.kernel_launches += c->use_bvh ? 2 : 1;  // shadow (+ heavy scan)
         c->shadow_queued = 0;
     }
     CUDA_TRY(cudaMemsetAsync(&c->counters->shadow_count, 0, sizeof(uint32_t), c->stream));
@@ -401,12 +466,12 @@ int process_level(rt_context* c, uint32_t d, uint32_t n, bool traced) {
     RayQueue& in = c->levels[d];
     RayQueue& out = last ? c->null_queue : c->levels[d + 1];
     uint32_t* next_count = &c->counters->level_count[last ? 63 : d + 1];
-    const uint64_t lights = std::max(1u, c->scene.ds.n_lights);
+    const uint64_t lights = std::max(1u, c->ds.n_lights);
     for (uint32_t first = 0; first < n; first += c->slice) {
         const uint32_t cnt = std::min(c->slice, n - first);
         if (!traced) {
             c->prof_begin(1);
-            c->k->closest(c->stream, c->scene.ds, c->scene.use_bvh, in, first, cnt, c->counters, c->sm_count, c->scene.heavy, nullptr);
+            c->k->closest(c->stream, c->ds, c->use_bvh, in, first, cnt, c->counters, c->sm_count, c->heavy, nullptr, &c->counters->lc[LC_SHARED], true);
             c->prof_end();
         }
         CUDA_TRY(cudaMemsetAsync(next_count, 0, sizeof(uint32_t), c->stream));
@@ -415,10 +480,10 @@ int process_level(rt_context* c, uint32_t d, uint32_t n, bool traced) {
             if (rc != RT_OK) return rc;
         }
         c->prof_begin(2);
-        c->k->shade(c->stream, c->scene.ds, c->fp, in, first, cnt, out, next_count, c->shadowq, &c->counters->shadow_count, &c->counters->overflow,
-                    c->accum, c->ids);
+        c->k->shade(c->stream, c->ds, c->fp, in, first, cnt, out, next_count, c->shadowq, &c->counters->shadow_count, &c->counters->overflow,
+                    c->accum, c->ids, c->sm_count, nullptr, nullptr);
         c->prof_end();
-        c->stats.kernel_launches += c->scene.use_bvh ? 3 : 2;  // closest (+ heavy scan), shade
+        c->stats.kernel_launches += c->use_bvh ? 3 : 2;  // closest (+ heavy scan), shade
         int rc = ctx_queue_counters(c);
         if (rc != RT_OK) return rc;
         const bool next_traced = !last && trace_level_ahead(c, d + 1);
@@ -439,6 +504,106 @@ int process_level(rt_context* c, uint32_t d, uint32_t n, bool traced) {
     return RT_OK;
 }
 
+int frame_host_levels(rt_context* c) {
+    c->shadow_queued = 0;
+    const uint64_t batch = c->levels[0].cap;
+    for (uint64_t base = 0; base < c->total_paths; base += batch) {
+        const uint32_t n = (uint32_t)std::min<uint64_t>(batch, c->total_paths - base);
+        CUDA_TRY(cudaMemsetAsync(&c->counters->level_count[0], 0, sizeof(uint32_t), c->stream));
+        c->prof_begin(0);
+        c->k->primary(c->stream, c->ds, c->fp, c->levels[0], &c->counters->level_count[0], &c->counters->overflow, base, n);
+        c->prof_end();
+        c->stats.kernel_launches += 1;
+        int rc = ctx_queue_counters(c);
+        if (rc != RT_OK) return rc;
+        const bool traced = trace_level_ahead(c, 0);
+        rc = ctx_wait_counters(c);
+        if (rc != RT_OK) return rc;
+        const uint32_t n0 = c->counters_host->level_count[0];
+        c->stats.paths += n0;
+        if (n0) {
+            rc = process_level(c, 0, n0, traced);
+            if (rc != RT_OK) return rc;
+        }
+    }
+    return flush_shadow(c);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// device-driven wavefront: every launch of the frame is queued without the host ever reading a count.  Each kernel takes
+// its ray count from the device counter its producer filled (stream order) and its grid is sized for an upper bound
+// (persistent kernels: the resident grid anyway).  A 4K frame's deep levels hold a few thousand rays; with a host round
+// trip per level they cost launch floor + read-back latency each, which does not shrink when the frame is sharded over
+// more GPUs (r01: 1 -> 8 GPU efficiency 0.65 on the default workload).
+//
+// The host cannot know in advance that a level fits its queue (a transparent hit spawns two rays), so the frame is
+// OPTIMISTIC: appends past a queue's capacity are dropped and flagged (Counters.overflow), every consumer clamps its
+// count to the capacity, and a flagged frame is simply traced again by the host-driven path above, which slices
+// levels and cannot overflow.  The context then stays host-driven.
+// Returns RT_OK with *overflowed set when the frame has to be redone.
+// ---------------------------------------------------------------------------------------------------------
+int frame_device_driven(rt_context* c, bool* overflowed) {
+    *overflowed = false;
+    const uint32_t n_levels = (uint32_t)c->levels.size();
+    const uint64_t cap = c->levels[0].cap;
+    const uint64_t branch = (uint64_t)std::max(1, c->ds.max_children);
+    // what a batch resets: shadow_count, level_count[], lc[] (contiguous in Counters)
+    char* batch_state = reinterpret_cast<char*>(&c->counters->shadow_count);
+    const size_t batch_state_bytes = sizeof(Counters) - offsetof(Counters, shadow_count);
+    size_t slot = 0;
+    for (uint64_t base = 0; base < c->total_paths; base += cap, slot++) {
+        const uint32_t n = (uint32_t)std::min<uint64_t>(cap, c->total_paths - base);
+        if (base) CUDA_TRY(cudaMemsetAsync(batch_state, 0, batch_state_bytes, c->stream));
+        c->prof_begin(0);
+        c->k->primary(c->stream, c->ds, c->fp, c->levels[0], &c->counters->level_count[0], &c->counters->overflow, base, n);
+        c->prof_end();
+        c->stats.kernel_launches += 1;
+        uint64_t bound = n;
+        for (uint32_t d = 0; d < n_levels; d++) {
+            const bool last = d + 1 >= n_levels;
+            RayQueue& in = c->levels[d];
+            const uint32_t* n_dev = &c->counters->level_count[d];
+            c->prof_begin(1);
+            c->k->closest(c->stream, c->ds, c->use_bvh, in, 0, (uint32_t)bound, c->counters, c->sm_count, c->heavy, n_dev, &c->counters->lc[d], false);
+            c->prof_end();
+            c->prof_begin(2);
+            c->k->shade(c->stream, c->ds, c->fp, in, 0, (uint32_t)bound, last ? c->null_queue : c->levels[d + 1], &c->counters->level_count[last ? 63 : d + 1],
+                        c->shadowq, &c->counters->shadow_count, &c->counters->overflow, c->accum, c->ids, c->sm_count, n_dev,
+                        d > 0 ? &c->counters->shade_cursor[d] : nullptr);
+            c->prof_end();
+            c->stats.kernel_launches += c->use_bvh ? 3 : 2;
+            bound = std::min<uint64_t>(cap, bound * branch);
+        }
+        c->prof_begin(3);
+        c->k->shadow(c->stream, c->ds, c->use_bvh, c->shadowq, c->shadowq.cap, c->accum, c->counters, c->sm_count, c->heavy, &c->counters->shadow_count,
+                     &c->counters->lc[LC_SHADOW], false);
+        c->prof_end();
+        c->stats.kernel_launches += c->use_bvh ? 2 : 1;
+        CUDA_TRY(cudaMemcpyAsync(&c->counters_host[slot], c->counters, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
+    }
+    CUDA_TRY(cudaEventRecord(c->ev_counts, c->stream));
+    CUDA_TRY(cudaEventSynchronize(c->ev_counts));
+    for (size_t b = 0; b < slot; b++) {
+        const Counters& h = c->counters_host[b];
+        if (h.overflow) { *overflowed = true; return RT_OK; }
+        c->stats.paths += h.level_count[0];
+        c->stats.rays_primary += h.level_count[0];
+        for (uint32_t d = 1; d < n_levels; d++) c->stats.rays_secondary += h.level_count[d];
+        c->stats.rays_shadow += h.shadow_count;
+    }
+    return RT_OK;
+}
+
+int frame_begin(rt_context* c) {
+    const size_t npix = (size_t)c->fp.local_rows * c->fp.width;
+    c->stats.rays_total = c->stats.rays_primary = c->stats.rays_secondary = c->stats.rays_shadow = 0;
+    c->stats.paths = 0;
+    CUDA_TRY(cudaMemsetAsync(c->accum, 0, npix * 3 * sizeof(double), c->stream));
+    CUDA_TRY(cudaMemsetAsync(c->ids, 0xFF, npix * sizeof(int32_t), c->stream));
+    CUDA_TRY(cudaMemsetAsync(c->counters, 0, sizeof(Counters), c->stream));
+    return RT_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -454,6 +619,7 @@ int rt_device_count(void) {
 int rt_context_create(const rt_scene* s, const rt_render_opts* o, rt_context** out) {
     if (!s || !o || !out) { set_error("rt_context_create: null argument"); return RT_ERR_INVALID; }
     *out = nullptr;
+    if (o->_reserved != 0) { set_error("rt_render_opts._reserved must be 0 (initialise with rt_render_opts_default)"); return RT_ERR_INVALID; }
     if (rt_device_count() <= 0) { set_error("no CUDA device: this library has no CPU fallback"); return RT_ERR_CUDA; }
     rt_context* c = new rt_context();
     c->device = o->device;
@@ -464,8 +630,15 @@ int rt_context_create(const rt_scene* s, const rt_render_opts* o, rt_context** o
     c->stream = c->own_stream;
     cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, o->device);
     c->k = o->fp_mode == RT_FP_FAST ? kernels_fast() : kernels_strict();
-    int rc = c->scene.init(s, o->accel, c->stream);
+    bool fresh = false;
+    int rc = acquire_device_scene(s, o->accel, o->tuning, o->device, c->stream, &c->scene, &fresh);
     if (rc != RT_OK) return fail(rc);
+    c->ds = c->scene->ds;
+    c->ds.camera = s->camera;           // by-value header fields that do not bump the scene's revision
+    c->ds.bg_kind = s->bg_kind;
+    std::memcpy(c->ds.bg_color, s->bg_color, sizeof c->ds.bg_color);
+    c->use_bvh = c->scene->use_bvh;
+    c->host_levels = (o->tuning & RT_TUNE_HOST_LEVELS) != 0;
 
     FrameParams& fp = c->fp;
     if ((rc = make_frame_params(s, o, &fp)) != RT_OK) return fail(rc);
@@ -473,8 +646,8 @@ int rt_context_create(const rt_scene* s, const rt_render_opts* o, rt_context** o
     c->total_paths = fp.npix_padded * fp.antialias * fp.cam_samples;
 
     // queue sizing
-    const uint32_t branch = (uint32_t)std::max(1, c->scene.ds.max_children);
-    const uint32_t lights = std::max(1u, c->scene.ds.n_lights);
+    const uint32_t branch = (uint32_t)std::max(1, c->ds.max_children);
+    const uint32_t lights = std::max(1u, c->ds.n_lights);
     uint64_t cap = o->max_rays_in_flight ? o->max_rays_in_flight : (1ull << 24);
     const uint64_t want = std::max<uint64_t>(c->total_paths * branch, 1024);
     cap = std::min(cap, want);
@@ -502,16 +675,22 @@ int rt_context_create(const rt_scene* s, const rt_render_opts* o, rt_context** o
     c->allocs.push_back(c->framebuffer);
     if ((rc = dev_alloc(&c->counters, 1)) != RT_OK) return fail(rc);
     c->allocs.push_back(c->counters);
-    if (g_pinned.get(&c->counters_host) != cudaSuccess) { set_error("cudaMallocHost failed"); return fail(RT_ERR_CUDA); }
+    if (c->use_bvh) {
+        if ((rc = dev_alloc(&c->heavy, HEAVY_WORDS)) != RT_OK) return fail(rc);
+        c->allocs.push_back(c->heavy);
+        // the split-scan scratch behind the list must start zeroed; its users leave it zeroed (k_heavy_scan)
+        if (cudaMemsetAsync(c->heavy + HEAVY_CAP, 0, sizeof(HeavyScratch), c->stream) != cudaSuccess) { set_error("cudaMemsetAsync failed"); return fail(RT_ERR_CUDA); }
+    }
+    if (g_pinned.get(&c->counters_host, &c->n_host_slots, (size_t)((c->total_paths + cap - 1) / cap) + 1) != cudaSuccess) { set_error("cudaMallocHost failed"); return fail(RT_ERR_CUDA); }
     if (cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_counts, cudaEventDisableTiming) != cudaSuccess) { set_error("cudaEventCreate failed"); return fail(RT_ERR_CUDA); }
     std::memset(&c->stats, 0, sizeof c->stats);
-    c->stats.bvh_build_ms = c->scene.bvh_ms;
-    c->stats.n_bvh_nodes = c->scene.ds.n_bvh_nodes;
-    c->stats.bvh_node_bytes = !c->scene.use_bvh ? 0 : (c->scene.ds.bvh_qnodes ? sizeof(BvhQNode) : sizeof(BvhNode));
+    c->stats.bvh_build_ms = fresh ? c->scene->bvh_ms : 0.0;  // 0: the device copy kept with the scene was reused
+    c->stats.n_bvh_nodes = c->ds.n_bvh_nodes;
+    c->stats.bvh_node_bytes = !c->use_bvh ? 0 : (c->ds.bvh_qnodes ? sizeof(BvhQNode) : sizeof(BvhNode));
     c->stats.local_rows = fp.local_rows;
     c->stats.bytewidth = c->bytewidth;
-    c->stats.accel_used = c->scene.use_bvh ? RT_ACCEL_BVH : RT_ACCEL_LINEAR;
+    c->stats.accel_used = c->use_bvh ? RT_ACCEL_BVH : RT_ACCEL_LINEAR;
     c->stats.fp_mode_used = o->fp_mode == RT_FP_FAST ? RT_FP_FAST : RT_FP_STRICT;
     *out = c;
     return RT_OK;
@@ -523,47 +702,33 @@ int rt_context_render(rt_context* c, rt_stats* stats) {
     if (!c) { set_error("null context"); return RT_ERR_INVALID; }
     CUDA_TRY(cudaSetDevice(c->device));
     const FrameParams& fp = c->fp;
-    const size_t npix = (size_t)fp.local_rows * fp.width;
-    c->stats.rays_total = c->stats.rays_primary = c->stats.rays_secondary = c->stats.rays_shadow = 0;
     c->stats.kernel_launches = 0;
-    c->stats.paths = 0;
     c->prof_class.clear();
     CUDA_TRY(cudaEventRecord(c->ev0, c->stream));
-    CUDA_TRY(cudaMemsetAsync(c->accum, 0, npix * 3 * sizeof(double), c->stream));
-    CUDA_TRY(cudaMemsetAsync(c->ids, 0xFF, npix * sizeof(int32_t), c->stream));
-    CUDA_TRY(cudaMemsetAsync(c->counters, 0, sizeof(Counters), c->stream));
-    c->shadow_queued = 0;
-    const uint64_t batch = c->levels[0].cap;
-    for (uint64_t base = 0; base < c->total_paths; base += batch) {
-        const uint32_t n = (uint32_t)std::min<uint64_t>(batch, c->total_paths - base);
-        CUDA_TRY(cudaMemsetAsync(&c->counters->level_count[0], 0, sizeof(uint32_t), c->stream));
-        c->prof_begin(0);
-        c->k->primary(c->stream, c->scene.ds, fp, c->levels[0], &c->counters->level_count[0], &c->counters->overflow, base, n);
-        c->prof_end();
-        c->stats.kernel_launches += 1;
-        int rc = ctx_queue_counters(c);
+    int rc = frame_begin(c);
+    if (rc != RT_OK) return rc;
+    bool redo = false;
+    if (!c->host_levels) {
+        rc = frame_device_driven(c, &redo);
         if (rc != RT_OK) return rc;
-        const bool traced = trace_level_ahead(c, 0);
-        rc = ctx_wait_counters(c);
-        if (rc != RT_OK) return rc;
-        const uint32_t n0 = c->counters_host->level_count[0];
-        c->stats.paths += n0;
-        if (n0) {
-            rc = process_level(c, 0, n0, traced);
-            if (rc != RT_OK) return rc;
+        if (redo) {  // a queue overflowed: this context goes level by level from now on
+            c->host_levels = true;
+            c->stats.device_driven_overflows += 1;
+            if ((rc = frame_begin(c)) != RT_OK) return rc;
         }
     }
-    {
-        int rc = flush_shadow(c);
+    if (c->host_levels) {
+        rc = frame_host_levels(c);
         if (rc != RT_OK) return rc;
     }
     c->prof_begin(4);
-    c->k->resolve(c->stream, c->scene.ds, fp, c->accum, c->framebuffer, c->bytewidth);
+    c->k->resolve(c->stream, c->ds, fp, c->accum, c->final_out ? c->final_out : c->framebuffer, c->bytewidth, c->final_out != nullptr);
     c->prof_end();
     c->stats.kernel_launches += 1;
     CUDA_TRY(cudaMemcpyAsync(c->counters_host, c->counters, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
     CUDA_TRY(cudaEventRecord(c->ev1, c->stream));
     CUDA_TRY(cudaEventSynchronize(c->ev1));
+    if (c->counters_host->overflow) { set_error("internal error: ray queue or traversal stack overflow"); return RT_ERR_CUDA; }
     for (int k = 0; k < 2; k++) {
         c->stats.bvh_nodes_visited[k] = c->counters_host->bvh_nodes[k];
         c->stats.bvh_prims_tested[k] = c->counters_host->bvh_prims[k];
@@ -582,6 +747,7 @@ int rt_context_render(rt_context* c, rt_stats* stats) {
     CUDA_TRY(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
     c->stats.render_ms = ms;
     c->stats.rays_total = c->stats.rays_primary + c->stats.rays_secondary + c->stats.rays_shadow;
+    c->stats.host_levels = c->host_levels ? 1u : 0u;
     if (stats) *stats = c->stats;
     return RT_OK;
 }
@@ -638,7 +804,7 @@ int rt_context_synchronize(rt_context* c) {
 
 int rt_render(const rt_scene* s, const rt_render_opts* o, uint8_t* bgr_rows, int32_t* primary_ids, double* accum, rt_stats* stats) {
     if (!s || !o) { set_error("rt_render: null argument"); return RT_ERR_INVALID; }
-    if (o->world != 1) { set_error("rt_render renders whole frames: world must be 1 (use rt_context_* for shards)"); return RT_ERR_INVALID; }
+    if (o->world != 1) { set_error("rt_render renders whole frames on one GPU: world must be 1 (rt_render_multi shards a frame over GPUs)"); return RT_ERR_INVALID; }
     rt_context* c = nullptr;
     int rc = rt_context_create(s, o, &c);
     if (rc != RT_OK) return rc;
@@ -654,6 +820,355 @@ int rt_render(const rt_scene* s, const rt_render_opts* o, uint8_t* bgr_rows, int
         if (e != cudaSuccess) { set_error(std::string("copy back: ") + cudaGetErrorString(e)); rc = RT_ERR_CUDA; }
     }
     rt_context_destroy(c);
+    return rc;
+}
+
+}  // extern "C"
+
+// =========================================================================================================
+// Multi-GPU frames inside the library: the frame loop of src/main.rs:39-59 with the image sharded by
+// interleaved row bands over the GPUs of one node.  One host thread and one stream per device; the scene is replicated
+// (each device keeps its copy with the rt_scene); every pixel is independent under the counter RNG, so tracing needs no
+// exchange.  What differs between the gather modes is only how the quantised BGR bands become one frame:
+//   DIRECT  every device DMAs its own bands straight to their rows of the caller's host buffer (one strided copy per
+//           device, all PCIe links in parallel) -- the frame is never assembled on a device;
+//   PEER    every device's k_resolve stores its rows into device[0]'s whole-frame buffer over NVLink peer access -- the
+//           gather is the resolve kernel's own 128-bit stores, no collective and no de-interleave pass;
+//   NCCL    ncclAllGather of the shards (single process, ncclCommInitAll) + k_untile on every device -- every GPU ends up
+//           with the whole frame.  NCCL is loaded at run time (dlopen libnccl.so.2): the library has no link-time
+//           dependency on it and fails loudly, for this mode only, where it is absent.
+// =========================================================================================================
+namespace {
+
+typedef struct ncclComm* nccl_comm_t;
+struct NcclApi {
+    void* so = nullptr;
+    int (*CommInitAll)(nccl_comm_t*, int, const int*) = nullptr;
+    int (*CommDestroy)(nccl_comm_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int /* ncclDataType_t */, nccl_comm_t, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    int (*GetVersion)(int*) = nullptr;
+    std::string error;
+    bool load() {
+        if (so) return true;
+        for (const char* name : {"libnccl.so.2", "libnccl.so"}) {
+            so = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
+            if (so) break;
+        }
+        if (!so) { error = "NCCL gather requested but libnccl.so.2 cannot be loaded"; return false; }
+        auto sym = [&](const char* n) { return dlsym(so, n); };
+        CommInitAll = (decltype(CommInitAll))sym("ncclCommInitAll");
+        CommDestroy = (decltype(CommDestroy))sym("ncclCommDestroy");
+        GroupStart = (decltype(GroupStart))sym("ncclGroupStart");
+        GroupEnd = (decltype(GroupEnd))sym("ncclGroupEnd");
+        AllGather = (decltype(AllGather))sym("ncclAllGather");
+        GetErrorString = (decltype(GetErrorString))sym("ncclGetErrorString");
+        GetVersion = (decltype(GetVersion))sym("ncclGetVersion");
+        if (!CommInitAll || !CommDestroy || !GroupStart || !GroupEnd || !AllGather || !GetErrorString) {
+            error = "libnccl.so.2 lacks an expected symbol";
+            so = nullptr;
+            return false;
+        }
+        return true;
+    }
+};
+constexpr int NCCL_UINT8 = 1;  // ncclUint8 (nccl.h ncclDataType_t)
+
+// communicators are expensive (ncclCommInitAll: ~1 s) and rt_render_multi is one-shot: keep them per device list
+struct NcclCache {
+    std::mutex m;
+    NcclApi api;
+    std::map<std::vector<int>, std::vector<nccl_comm_t>> comms;
+    int get(const std::vector<int>& devices, std::vector<nccl_comm_t>* out) {
+        std::lock_guard<std::mutex> g(m);
+        if (!api.load()) { set_error(api.error); return RT_ERR_UNSUPPORTED; }
+        auto it = comms.find(devices);
+        if (it == comms.end()) {
+            std::vector<nccl_comm_t> v(devices.size(), nullptr);
+            const int r = api.CommInitAll(v.data(), (int)devices.size(), devices.data());
+            if (r != 0) { set_error(std::string("ncclCommInitAll: ") + api.GetErrorString(r)); return RT_ERR_CUDA; }
+            it = comms.emplace(devices, v).first;
+        }
+        *out = it->second;
+        return RT_OK;
+    }
+};
+NcclCache g_nccl;
+
+}  // namespace
+
+struct rt_multi {
+    int n = 0;
+    std::vector<int> devices;
+    int gather = RT_GATHER_DIRECT;
+    rt_render_opts opts{};
+    const rt_scene* scene = nullptr;
+    std::vector<rt_context*> ctx;
+    uint32_t width = 0, height = 0, bytewidth = 0, band_rows = 4;
+    size_t frame_bytes = 0;
+    std::vector<uint8_t*> frames;    // PEER: [0] only; NCCL: one whole frame per device
+    std::vector<uint8_t*> gathered;  // NCCL: rank-major shards per device
+    std::vector<nccl_comm_t> comms;
+    rt_stats last{};
+    // workers: one per device, running whatever `job` is posted
+    std::vector<std::thread> threads;
+    std::mutex m;
+    std::condition_variable cv_go, cv_done;
+    uint64_t generation = 0;
+    int pending = 0;
+    bool quit = false;
+    std::function<int(int)> job;
+    std::vector<int> rc;
+    std::vector<std::string> err;
+    std::vector<rt_stats> st;
+
+    void worker(int i) {
+        uint64_t seen = 0;
+        for (;;) {
+            std::function<int(int)> j;
+            {
+                std::unique_lock<std::mutex> lk(m);
+                cv_go.wait(lk, [&] { return quit || generation != seen; });
+                if (quit) return;
+                seen = generation;
+                j = job;
+            }
+            const int r = j(i);
+            {
+                std::lock_guard<std::mutex> lk(m);
+                rc[i] = r;
+                if (r != RT_OK) err[i] = get_error();
+                if (--pending == 0) cv_done.notify_all();
+            }
+        }
+    }
+    // runs f(i) on every device's thread; returns the first failure (its message becomes the caller's rt_last_error)
+    int run(std::function<int(int)> f) {
+        {
+            std::lock_guard<std::mutex> lk(m);
+            job = std::move(f);
+            pending = n;
+            generation++;
+        }
+        cv_go.notify_all();
+        std::unique_lock<std::mutex> lk(m);
+        cv_done.wait(lk, [&] { return pending == 0; });
+        for (int i = 0; i < n; i++)
+            if (rc[i] != RT_OK) { set_error("device " + std::to_string(devices[i]) + ": " + err[i]); return rc[i]; }
+        return RT_OK;
+    }
+    ~rt_multi() {
+        if (!threads.empty()) {
+            run([&](int i) {
+                if (ctx[i]) { rt_context_destroy(ctx[i]); ctx[i] = nullptr; }
+                cudaSetDevice(devices[i]);
+                if (i < (int)frames.size()) g_cache.release(frames[i]);
+                if (i < (int)gathered.size()) g_cache.release(gathered[i]);
+                return (int)RT_OK;
+            });
+            {
+                std::lock_guard<std::mutex> lk(m);
+                quit = true;
+            }
+            cv_go.notify_all();
+            for (std::thread& t : threads) t.join();
+        }
+    }
+};
+
+namespace {
+
+// Copies the bands a shard holds (local row order, `row_bytes` per row) to their rows of a whole-frame host array: one strided
+// DMA for the whole bands plus one for a cut-off last band.
+cudaError_t copy_bands_to_host(const FrameParams& fp, const void* local, void* host, size_t row_bytes, cudaStream_t st) {
+    const uint32_t band = fp.band_rows;
+    const uint32_t n_bands = (fp.height + band - 1) / band;          // bands of the whole frame
+    const uint32_t mine = fp.rank < n_bands ? (n_bands - fp.rank + fp.world - 1) / fp.world : 0u;  // ... of this shard
+    if (!mine) return cudaSuccess;
+    const uint32_t last_rows = fp.height - (n_bands - 1) * band;     // rows of the frame's last band
+    const bool have_last = (n_bands - 1) % fp.world == fp.rank && last_rows != band;
+    const uint32_t whole = have_last ? mine - 1 : mine;
+    const size_t band_bytes = (size_t)band * row_bytes;
+    char* dst = (char*)host + (size_t)fp.rank * band_bytes;
+    cudaError_t e = cudaSuccess;
+    if (whole) e = cudaMemcpy2DAsync(dst, (size_t)fp.world * band_bytes, local, band_bytes, band_bytes, whole, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess && have_last)
+        e = cudaMemcpyAsync(dst + (size_t)whole * fp.world * band_bytes, (const char*)local + (size_t)whole * band_bytes, (size_t)last_rows * row_bytes,
+                            cudaMemcpyDeviceToHost, st);
+    return e;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rt_multi_create(const rt_scene* s, const rt_render_opts* o, int n_devices, const int* devices, int gather, rt_multi** out) {
+    if (!s || !o || !out || n_devices < 1) { set_error("rt_multi_create: bad argument"); return RT_ERR_INVALID; }
+    *out = nullptr;
+    const int have = rt_device_count();
+    if (have <= 0) { set_error("no CUDA device: this library has no CPU fallback"); return RT_ERR_CUDA; }
+    if (gather < RT_GATHER_AUTO || gather > RT_GATHER_NCCL) { set_error("rt_multi_create: unknown gather mode"); return RT_ERR_INVALID; }
+    std::unique_ptr<rt_multi> m(new rt_multi());
+    m->n = n_devices;
+    for (int i = 0; i < n_devices; i++) {
+        const int d = devices ? devices[i] : i;
+        if (d < 0 || d >= have) { set_error("rt_multi_create: device ordinal out of range"); return RT_ERR_INVALID; }
+        // DIRECT / PEER: an ordinal may appear more than once (its shards then share that GPU -- how the sharding and the
+        // gather are exercised on a one-GPU machine); NCCL wants one rank per GPU
+        if (gather == RT_GATHER_NCCL)
+            for (int k : m->devices)
+                if (k == d) { set_error("rt_multi_create: RT_GATHER_NCCL needs distinct devices"); return RT_ERR_INVALID; }
+        m->devices.push_back(d);
+    }
+    m->gather = gather == RT_GATHER_AUTO ? RT_GATHER_DIRECT : gather;
+    m->opts = *o;
+    m->scene = s;
+    m->ctx.assign(n_devices, nullptr);
+    m->rc.assign(n_devices, RT_OK);
+    m->err.assign(n_devices, std::string());
+    m->st.assign(n_devices, rt_stats{});
+    FrameParams fp{};
+    rt_render_opts probe = *o;
+    probe.rank = 0; probe.world = n_devices;
+    int rc = make_frame_params(s, &probe, &fp);
+    if (rc != RT_OK) return rc;
+    m->width = fp.width; m->height = fp.height; m->band_rows = fp.band_rows;
+    m->bytewidth = rt_bmp_bytewidth(fp.width);
+    m->frame_bytes = (size_t)m->bytewidth * fp.height;
+    if (m->gather == RT_GATHER_NCCL && n_devices > 1) {
+        if ((rc = g_nccl.get(m->devices, &m->comms)) != RT_OK) return rc;
+    }
+    if (m->gather == RT_GATHER_PEER) m->frames.assign(1, nullptr);
+    if (m->gather == RT_GATHER_NCCL) { m->frames.assign(n_devices, nullptr); m->gathered.assign(n_devices, nullptr); }
+    for (int i = 0; i < n_devices; i++) m->threads.emplace_back([p = m.get(), i] { p->worker(i); });
+    rt_multi* M = m.get();
+    // device 0 first: in PEER mode the others store into its frame buffer
+    if (M->gather == RT_GATHER_PEER) {
+        if (cudaSetDevice(M->devices[0]) != cudaSuccess || g_cache.alloc((void**)&M->frames[0], M->frame_bytes + 16) != cudaSuccess) {
+            set_error("rt_multi_create: cannot allocate the frame on the first device");
+            return RT_ERR_CUDA;
+        }
+    }
+    rc = M->run([M](int i) {
+        if (cudaSetDevice(M->devices[i]) != cudaSuccess) { set_error("cudaSetDevice failed"); return (int)RT_ERR_CUDA; }
+        rt_render_opts oi = M->opts;
+        oi.device = M->devices[i]; oi.rank = i; oi.world = M->n;
+        int r = rt_context_create(M->scene, &oi, &M->ctx[i]);
+        if (r != RT_OK) return r;
+        if (M->gather == RT_GATHER_PEER) {
+            if (M->devices[i] != M->devices[0]) {
+                int can = 0;
+                cudaDeviceCanAccessPeer(&can, M->devices[i], M->devices[0]);
+                if (!can) { set_error("no peer access to device " + std::to_string(M->devices[0]) + " (RT_GATHER_PEER needs NVLink/PCIe P2P)"); return (int)RT_ERR_UNSUPPORTED; }
+                const cudaError_t e = cudaDeviceEnablePeerAccess(M->devices[0], 0);
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { set_error(std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(e)); return (int)RT_ERR_CUDA; }
+                cudaGetLastError();
+            }
+            M->ctx[i]->final_out = M->frames[0];
+        } else if (M->gather == RT_GATHER_NCCL) {
+            if (g_cache.alloc((void**)&M->frames[i], M->frame_bytes + 16) != cudaSuccess ||
+                g_cache.alloc((void**)&M->gathered[i], (size_t)M->n * M->ctx[i]->fb_bytes + 16) != cudaSuccess) {
+                set_error("rt_multi_create: cannot allocate the gather buffers");
+                return (int)RT_ERR_CUDA;
+            }
+        }
+        return (int)RT_OK;
+    });
+    if (rc != RT_OK) return rc;  // ~rt_multi destroys what was created
+    *out = m.release();
+    return RT_OK;
+}
+
+void rt_multi_destroy(rt_multi* m) { delete m; }
+
+int rt_multi_gather_used(const rt_multi* m) { return m ? m->gather : RT_ERR_INVALID; }
+
+int rt_multi_render(rt_multi* m, uint8_t* bgr_rows, int32_t* primary_ids, rt_stats* stats) {
+    if (!m) { set_error("null rt_multi"); return RT_ERR_INVALID; }
+    const auto t0 = std::chrono::steady_clock::now();
+    int rc = m->run([m, bgr_rows, primary_ids](int i) {
+        rt_context* c = m->ctx[i];
+        int r = rt_context_render(c, &m->st[i]);  // returns with the device idle: peer stores of k_resolve have landed
+        if (r != RT_OK) return r;
+        cudaError_t e = cudaSuccess;
+        if (bgr_rows && m->gather == RT_GATHER_DIRECT) e = copy_bands_to_host(c->fp, c->framebuffer, bgr_rows, m->bytewidth, c->stream);
+        if (e == cudaSuccess && primary_ids) e = copy_bands_to_host(c->fp, c->ids, primary_ids, (size_t)c->fp.width * sizeof(int32_t), c->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) { set_error(std::string("copy back: ") + cudaGetErrorString(e)); return (int)RT_ERR_CUDA; }
+        return (int)RT_OK;
+    });
+    if (rc != RT_OK) return rc;
+    if (m->gather == RT_GATHER_NCCL) {
+        if (m->n > 1) {
+            NcclApi& N = g_nccl.api;
+            int r = N.GroupStart();
+            for (int i = 0; i < m->n && r == 0; i++)
+                r = N.AllGather(m->ctx[i]->framebuffer, m->gathered[i], m->ctx[i]->fb_bytes, NCCL_UINT8, m->comms[i], m->ctx[i]->stream);
+            const int r2 = N.GroupEnd();
+            if (r == 0) r = r2;
+            if (r != 0) { set_error(std::string("ncclAllGather: ") + N.GetErrorString(r)); return RT_ERR_CUDA; }
+        }
+        for (int i = 0; i < m->n; i++) {
+            rt_context* c = m->ctx[i];
+            CUDA_TRY(cudaSetDevice(m->devices[i]));
+            if (m->n > 1) {
+                launch_untile(c->stream, (const uint32_t*)m->gathered[i], (uint32_t*)m->frames[i], c->fp.height, m->bytewidth / 4, c->fp.band_rows, c->fp.world,
+                              c->fp.local_rows);
+            } else {
+                CUDA_TRY(cudaMemcpyAsync(m->frames[i], c->framebuffer, m->frame_bytes, cudaMemcpyDeviceToDevice, c->stream));
+            }
+        }
+        for (int i = 0; i < m->n; i++) {
+            CUDA_TRY(cudaSetDevice(m->devices[i]));
+            CUDA_TRY(cudaStreamSynchronize(m->ctx[i]->stream));
+        }
+    }
+    if (bgr_rows && m->gather != RT_GATHER_DIRECT) {
+        CUDA_TRY(cudaSetDevice(m->devices[0]));
+        CUDA_TRY(cudaMemcpyAsync(bgr_rows, m->frames[0], m->frame_bytes, cudaMemcpyDeviceToHost, m->ctx[0]->stream));
+        CUDA_TRY(cudaStreamSynchronize(m->ctx[0]->stream));
+    }
+    rt_stats sum = m->st[0];
+    for (int i = 1; i < m->n; i++) {
+        const rt_stats& a = m->st[i];
+        sum.rays_total += a.rays_total; sum.rays_primary += a.rays_primary; sum.rays_secondary += a.rays_secondary; sum.rays_shadow += a.rays_shadow;
+        sum.paths += a.paths; sum.kernel_launches += a.kernel_launches;
+        sum.render_ms = std::max(sum.render_ms, a.render_ms);
+        sum.bvh_build_ms = std::max(sum.bvh_build_ms, a.bvh_build_ms);
+        sum.local_rows += a.local_rows;
+        for (int k = 0; k < 2; k++) { sum.bvh_nodes_visited[k] += a.bvh_nodes_visited[k]; sum.bvh_prims_tested[k] += a.bvh_prims_tested[k]; sum.heavy_rays[k] += a.heavy_rays[k]; }
+        for (int k = 0; k < 5; k++) { sum.class_ms[k] = std::max(sum.class_ms[k], a.class_ms[k]); sum.class_launches[k] += a.class_launches[k]; }
+        sum.host_levels |= a.host_levels; sum.device_driven_overflows += a.device_driven_overflows;
+    }
+    if (m->gather == RT_GATHER_NCCL && m->n > 1) sum.kernel_launches += (uint64_t)m->n;  // k_untile per device
+    (void)t0;
+    m->last = sum;
+    if (stats) *stats = sum;
+    return RT_OK;
+}
+
+int rt_multi_device_stats(const rt_multi* m, int index, rt_stats* stats) {
+    if (!m || !stats || index < 0 || index >= m->n) { set_error("rt_multi_device_stats: bad argument"); return RT_ERR_INVALID; }
+    *stats = m->st[index];
+    return RT_OK;
+}
+
+const void* rt_multi_frame_device(const rt_multi* m, int index) {
+    if (!m || index < 0 || index >= (int)m->frames.size()) return nullptr;
+    return m->frames[index];
+}
+
+int rt_render_multi(const rt_scene* s, const rt_render_opts* o, int n_devices, const int* devices, int gather, uint8_t* bgr_rows, int32_t* primary_ids,
+                    rt_stats* stats) {
+    rt_multi* m = nullptr;
+    int rc = rt_multi_create(s, o, n_devices, devices, gather, &m);
+    if (rc != RT_OK) return rc;
+    rc = rt_multi_render(m, bgr_rows, primary_ids, stats);
+    std::string keep = rc != RT_OK ? get_error() : "";
+    rt_multi_destroy(m);
+    if (rc != RT_OK) set_error(keep);
     return rc;
 }
 
@@ -673,6 +1188,7 @@ int rt_trace_rays(const rt_scene* s, const rt_render_opts* o, uint64_t n, const 
     int rc = RT_OK;
     {
         DeviceSceneHolder holder;
+        uint32_t* heavy = nullptr;
         const rt_scene* use = s;  // scenes used only for intersection tests may lack camera/background
         rt_scene patched;
         if (!s->camera_set || !s->background_set) {
@@ -680,7 +1196,8 @@ int rt_trace_rays(const rt_scene* s, const rt_render_opts* o, uint64_t n, const 
             patched.camera_set = true; patched.background_set = true; patched.bg_kind = BG_SOLID;
             use = &patched;
         }
-        rc = holder.init(use, o->accel, st);
+        rc = holder.init(use, o->accel, o->tuning & SCENE_TUNING, st);
+        if (rc == RT_OK && holder.use_bvh) rc = dev_alloc(&heavy, HEAVY_WORDS);
         std::vector<void*> allocs;
         RayQueue q{};
         double *d_t = nullptr, *d_n = nullptr;
@@ -695,10 +1212,11 @@ int rt_trace_rays(const rt_scene* s, const rt_render_opts* o, uint64_t n, const 
                 for (int k = 0; k < 6; k++) soa[(size_t)k * n + i] = origin_dir[6 * i + k];
             cudaError_t e = cudaMemcpyAsync(q.ox, soa.data(), sizeof(double) * 6 * n, cudaMemcpyHostToDevice, st);
             if (e == cudaSuccess) e = cudaMemsetAsync(cursor, 0, sizeof(Counters), st);
+            if (e == cudaSuccess && heavy) e = cudaMemsetAsync(heavy + HEAVY_CAP, 0, sizeof(HeavyScratch), st);
             if (e == cudaSuccess) e = cudaStreamSynchronize(st);
             const KernelTable* k = o->fp_mode == RT_FP_FAST ? kernels_fast() : kernels_strict();
             if (e == cudaSuccess) {
-                k->closest(st, holder.ds, holder.use_bvh, q, 0, (uint32_t)n, cursor, sm_count, holder.heavy, nullptr);
+                k->closest(st, holder.ds, holder.use_bvh, q, 0, (uint32_t)n, cursor, sm_count, heavy, nullptr, &cursor->lc[LC_SHARED], false);
                 k->hit_normals(st, holder.ds, q, (uint32_t)n, d_t, d_n);
                 e = cudaMemcpyAsync(ids, q.hit_id, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, st);
             }
@@ -709,7 +1227,7 @@ int rt_trace_rays(const rt_scene* s, const rt_render_opts* o, uint64_t n, const 
             if (e != cudaSuccess) { set_error(std::string("rt_trace_rays: ") + cudaGetErrorString(e)); rc = RT_ERR_CUDA; }
         }
         for (void* p : allocs) g_cache.release(p);
-        g_cache.release(d_t); g_cache.release(d_n); g_cache.release(cursor);
+        g_cache.release(d_t); g_cache.release(d_n); g_cache.release(cursor); g_cache.release(heavy);
     }
     cudaStreamDestroy(st);
     return rc;

@@ -133,9 +133,9 @@ bool load_texture_file(const std::string& path, HostTexture* out, std::string* e
     return false;
 }
 
-static void choose_quantisation(const rt_scene* s, FlatScene* f);
+static void choose_quantisation(const rt_scene* s, FlatScene* f, uint32_t tuning);
 
-int flatten_scene(const rt_scene* s, FlatScene* f) {
+int flatten_scene(const rt_scene* s, FlatScene* f, uint32_t tuning) {
     if (!s->camera_set) { set_error("scene has no camera"); return RT_ERR_INVALID; }
     if (!s->background_set) { set_error("scene has no background"); return RT_ERR_INVALID; }
     if (s->bg_kind == BG_SKYBOX)
@@ -182,7 +182,7 @@ int flatten_scene(const rt_scene* s, FlatScene* f) {
         for (int a = 0; a < 3; a++) { f->box_lo[a] = -INFINITY; f->box_hi[a] = INFINITY; }
     f->cmax = cmax;
     f->rmin = (rmin > 0.0 && std::isfinite(rmin)) ? rmin : 1e-300;
-    choose_quantisation(s, f);
+    choose_quantisation(s, f, tuning);
     int mc = 0;
     for (const MaterialRec& m : s->materials) {
         int c = m.kind == MAT_INDIRECT ? (int)m.samples : (m.kind == MAT_TRANSPARENT ? 2 : 1);
@@ -193,17 +193,20 @@ int flatten_scene(const rt_scene* s, FlatScene* f) {
 }
 
 void scene_touch(rt_scene* s) {
-    std::lock_guard<std::mutex> g(s->flat_cache.m);
-    s->flat_cache.p.reset();
-    s->revision++;
+    {
+        std::lock_guard<std::mutex> g(s->flat_cache.m);
+        s->flat_cache.p.reset();
+        s->revision++;
+    }
+    std::lock_guard<std::mutex> g(s->device_cache.m);
+    s->device_cache.entries.clear();
 }
 
-int flatten_scene_cached(const rt_scene* s, std::shared_ptr<FlatCache>* out) {
-    const char* e = std::getenv("RAYTRACE_B200_BVH_NODES");
-    const std::string quant_override = e ? e : "";
+int flatten_scene_cached(const rt_scene* s, uint32_t tuning, std::shared_ptr<FlatCache>* out) {
+    const uint32_t node_tuning = tuning & (RT_TUNE_NODES_F32 | RT_TUNE_NODES_Q16);
     std::lock_guard<std::mutex> g(s->flat_cache.m);
     std::shared_ptr<FlatCache>& c = s->flat_cache.p;
-    if (c && c->revision == s->revision && c->quant_override == quant_override && c->flat.obj_shape.size() == s->objects.size()) {
+    if (c && c->revision == s->revision && c->node_tuning == node_tuning && c->flat.obj_shape.size() == s->objects.size()) {
         // what flatten_scene checks without looking at the objects
         if (!s->camera_set) { set_error("scene has no camera"); return RT_ERR_INVALID; }
         if (!s->background_set) { set_error("scene has no background"); return RT_ERR_INVALID; }
@@ -214,10 +217,10 @@ int flatten_scene_cached(const rt_scene* s, std::shared_ptr<FlatCache>* out) {
         return RT_OK;
     }
     std::shared_ptr<FlatCache> fresh = std::make_shared<FlatCache>();
-    int rc = flatten_scene(s, &fresh->flat);
+    int rc = flatten_scene(s, &fresh->flat, node_tuning);
     if (rc != RT_OK) return rc;
     fresh->revision = s->revision;
-    fresh->quant_override = quant_override;
+    fresh->node_tuning = node_tuning;
     c = fresh;
     *out = c;
     return RT_OK;
@@ -226,9 +229,9 @@ int flatten_scene_cached(const rt_scene* s, std::shared_ptr<FlatCache>* out) {
 // The 32-byte nodes store box planes on a 65535-step grid over the sphere bounds.  A box grows by up to one cell from
 // the rounding and the filter pads it by another 1.25 cells (rt_device.cuh make_boxray32), so the grid is used only
 // when 2.25 cells stay under a quarter of the mean radius on every axis and the bounds are small enough for the f32
-// filter terms (2^23 * cell / |d|, |d| clamped at 1e-30) not to overflow.  RAYTRACE_B200_BVH_NODES=f32|q16 overrides the
-// size test (development / A-B measurements); unusable bounds always mean f32 nodes.
-static void choose_quantisation(const rt_scene* s, FlatScene* f) {
+// filter terms (2^23 * cell / |d|, |d| clamped at 1e-30) not to overflow.  RT_TUNE_NODES_F32 / RT_TUNE_NODES_Q16 override the
+// size test (A-B measurements, parity tests); unusable bounds always mean f32 nodes.
+static void choose_quantisation(const rt_scene* s, FlatScene* f, uint32_t tuning) {
     f->quant = false;
     for (int a = 0; a < 3; a++) { f->q_org[a] = 0.0; f->q_cell[a] = 0.0; }
     if (f->sph.empty()) return;
@@ -250,10 +253,8 @@ static void choose_quantisation(const rt_scene* s, FlatScene* f) {
     }
     if (!std::isfinite(rmean) || !(ext_max <= 1e6) || !(f->cmax <= 1e6)) return;
     bool fine = 2.25 * cell_max <= 0.25 * rmean;
-    if (const char* e = std::getenv("RAYTRACE_B200_BVH_NODES")) {
-        if (!std::strcmp(e, "f32")) fine = false;
-        else if (!std::strcmp(e, "q16")) fine = true;
-    }
+    if (tuning & RT_TUNE_NODES_F32) fine = false;
+    else if (tuning & RT_TUNE_NODES_Q16) fine = true;
     f->quant = fine;
 }
 
@@ -277,7 +278,7 @@ void fill_scene_header(const rt_scene* s, const FlatScene& f, DeviceScene* ds) {
     for (int a = 0; a < 3; a++) { ds->bvh_lo[a] = f.box_lo[a]; ds->bvh_hi[a] = f.box_hi[a]; }
     ds->bvh_qnodes = nullptr;  // set by the owner of the device buffers when f.quant
     ds->bvh_wnodes = nullptr;
-    ds->bvh_wide_closest = 0;
+    ds->_pad_bvh = 0;
     for (int a = 0; a < 3; a++) { ds->q_org[a] = f.q_org[a]; ds->q_cell[a] = f.q_cell[a]; }
 }
 
@@ -388,6 +389,7 @@ static int add_light(rt_scene* s, int32_t kind, const double* a, const double* s
     LightRec l{};
     l.kind = kind;
     for (int i = 0; i < 3; i++) { l.a[i] = a[i]; l.s1[i] = s1 ? s1[i] : 0.0; l.s2[i] = s2 ? s2[i] : 0.0; l.color[i] = color[i]; }
+    scene_touch(s);  // the device copy kept with the scene (DeviceSceneSlot) holds the light records
     s->lights.push_back(l);
     return RT_OK;
 }

@@ -48,7 +48,7 @@ struct FlatScene {
 struct FlatCache {
     FlatScene flat;
     uint64_t revision = 0;
-    std::string quant_override;  // RAYTRACE_B200_BVH_NODES at the time of flattening
+    uint32_t node_tuning = 0;  // RT_TUNE_NODES_* bits the grid decision was taken under
     std::shared_ptr<void> pin;
 };
 // the scene's slot for it; copying a scene does not copy the cache
@@ -58,6 +58,24 @@ struct FlatCacheSlot {
     FlatCacheSlot() = default;
     FlatCacheSlot(const FlatCacheSlot&) {}
     FlatCacheSlot& operator=(const FlatCacheSlot&) { p.reset(); return *this; }
+};
+
+// Device copies of the scene (flattened buffers + BVH), one per (device, accel, tuning), kept with the scene so that a
+// caller rendering frame after frame through rt_render -- a context per call, as the reference's main would -- uploads and
+// builds once.  Entries are owned by context.cu (type-erased here: this header stays free of CUDA); scene_touch drops them.
+struct DeviceSceneSlot {
+    struct Entry {
+        int device;
+        int accel;
+        uint32_t tuning;
+        uint64_t revision;
+        std::shared_ptr<void> holder;
+    };
+    std::mutex m;
+    std::vector<Entry> entries;
+    DeviceSceneSlot() = default;
+    DeviceSceneSlot(const DeviceSceneSlot&) {}
+    DeviceSceneSlot& operator=(const DeviceSceneSlot&) { entries.clear(); return *this; }
 };
 
 }  // namespace rt
@@ -79,6 +97,7 @@ struct rt_scene {
     uint64_t n_spheres = 0, n_planes = 0;
     uint64_t revision = 0;  // bumped by rt::scene_touch
     mutable rt::FlatCacheSlot flat_cache;
+    mutable rt::DeviceSceneSlot device_cache;
 };
 
 namespace rt {
@@ -101,9 +120,9 @@ int parse_scene_text(const char* text, size_t len, rt_scene* scene, std::string*
 // page-lock on the vectors about to be reallocated) and bumps the revision.
 void scene_touch(rt_scene* s);
 // returns RT_OK or RT_ERR_INVALID (missing camera/background/skybox face)
-int flatten_scene(const rt_scene* s, FlatScene* out);
+int flatten_scene(const rt_scene* s, FlatScene* out, uint32_t tuning = 0);
 // the same through the scene's cache: flattens on the first call after a change, validates every time
-int flatten_scene_cached(const rt_scene* s, std::shared_ptr<FlatCache>* out);
+int flatten_scene_cached(const rt_scene* s, uint32_t tuning, std::shared_ptr<FlatCache>* out);
 // fills the fields of DeviceScene that do not point into device memory
 void fill_scene_header(const rt_scene* s, const FlatScene& f, DeviceScene* ds);
 // image-space shard + frame parameters from the scene's Options and the render options

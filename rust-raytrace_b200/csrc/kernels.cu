@@ -199,9 +199,13 @@ __device__ __forceinline__ void scan_spheres(const DeviceScene& sc, ScanSmem* sm
     }
 }
 
-__global__ void __launch_bounds__(SCAN_THREADS) k_closest_scan(const __grid_constant__ DeviceScene sc, RayQueue q, uint32_t first, uint32_t n) {
+// n_dev (both scan kernels): the ray count is read on the device and the grid was sized for an upper bound -- CTAs past
+// the end leave before they touch a barrier
+__global__ void __launch_bounds__(SCAN_THREADS) k_closest_scan(const __grid_constant__ DeviceScene sc, RayQueue q, uint32_t first, uint32_t n,
+                                                               const uint32_t* n_dev) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     ScanSmem* sm = reinterpret_cast<ScanSmem*>(smem_raw);
+    if (n_dev) { n = *n_dev < q.cap ? *n_dev : q.cap; if (blockIdx.x * SCAN_THREADS >= n) return; }
     const uint32_t li = blockIdx.x * SCAN_THREADS + threadIdx.x;
     const bool active = li < n;
     const uint32_t i = first + (active ? li : 0);
@@ -216,9 +220,11 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_closest_scan(const __grid_cons
     }
 }
 
-__global__ void __launch_bounds__(SCAN_THREADS) k_shadow_scan(const __grid_constant__ DeviceScene sc, ShadowQueue sq, uint32_t n, double* accum) {
+__global__ void __launch_bounds__(SCAN_THREADS) k_shadow_scan(const __grid_constant__ DeviceScene sc, ShadowQueue sq, uint32_t n, double* accum,
+                                                              const uint32_t* n_dev) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     ScanSmem* sm = reinterpret_cast<ScanSmem*>(smem_raw);
+    if (n_dev) { n = *n_dev < sq.cap ? *n_dev : sq.cap; if (blockIdx.x * SCAN_THREADS >= n) return; }
     const uint32_t li = blockIdx.x * SCAN_THREADS + threadIdx.x;
     const bool active = li < n;
     const uint32_t i = active ? li : 0;
@@ -320,17 +326,19 @@ __device__ __forceinline__ RayQ parked_ray(const TravSmem& sm) {
     return make_rayq(v3(sm.ray[0][t], sm.ray[1][t], sm.ray[2][t]), v3(sm.ray[3][t], sm.ray[4][t], sm.ray[5][t]));
 }
 
-// WIDE (experimental, RAYTRACE_B200_BVH_WIDE=2): the walk goes over sc.bvh_wnodes, nearest of four boxes first
-// (rt_device.cuh trav_descend_wide_ordered); everything else is the same kernel.
-template <bool QNODES, bool WIDE = false>
+template <bool QNODES>
 __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_closest_bvh(const __grid_constant__ DeviceScene sc, RayQueue q, uint32_t first, uint32_t n, Counters* counters,
-                                                                uint32_t* heavy, uint32_t heavy_walks, const uint32_t* n_dev) {
+                                                                uint32_t* heavy, uint32_t heavy_walks, const uint32_t* n_dev, uint32_t lc_index) {
     __shared__ TravSmem sm;
-    if (n_dev) n = *n_dev;  // launched ahead of the host's count read-back (context.cu process_level)
-    uint32_t* cursor = &counters->cursor;
+    // launched ahead of the host's count read-back (context.cu).  The producer's counter runs past the capacity when its
+    // queue overflows (the appends are dropped and the frame fails): never index beyond what the queue holds.
+    // The count lives in shared memory: it is only looked at when lanes are refilled, and the walk has no register to spare.
+    __shared__ uint32_t n_s;
+    if (threadIdx.x == 0) n_s = n_dev ? (*n_dev < q.cap ? *n_dev : q.cap) : n;
+    __syncthreads();
     uint32_t walks = 0;  // bounded walks spent on the current ray
-    TraverseCount tc; tc.nodes = 0; tc.prims = 0;
-    typename std::conditional<WIDE, TravStackWideT, TravStack>::type st; int sp = 0;
+    TraverseCount tc = traverse_count_zero();
+    TravStack st; int sp = 0;
     BoxRay32 br = boxray32_none();
     int32_t cur = TRAV_EMPTY;
     int32_t best_obj = 0x7FFFFFFF;  // the best hit's t is parked in sm.aux
@@ -342,9 +350,10 @@ __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_closest_bvh(
     while (true) {
         const unsigned idle = __ballot_sync(0xFFFFFFFFu, !active);
         if (idle != 0u && !exhausted && (__popc(idle) >= FETCH_MIN_IDLE || idle == 0xFFFFFFFFu)) {
-            const uint32_t li = warp_fetch_each(idle, cursor);
+            const uint32_t li = warp_fetch_each(idle, &counters->lc[lc_index].cursor);
+            const uint32_t n_now = n_s;
             if (!active) {
-                if (li < n) {
+                if (li < n_now) {
                     ray = first + li;
                     const RayQ r = make_rayq(v3(q.ox[ray], q.oy[ray], q.oz[ray]), v3(q.dx[ray], q.dy[ray], q.dz[ray]));
                     Closest best = closest_none();
@@ -364,15 +373,14 @@ __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_closest_bvh(
                 }
             }
             // the cursor only grows: once any lane is handed an index past the end, the queue is drained
-            exhausted = __any_sync(0xFFFFFFFFu, li >= n && (idle >> (threadIdx.x & 31) & 1u));
+            exhausted = __any_sync(0xFFFFFFFFu, li >= n_now && (idle >> (threadIdx.x & 31) & 1u));
         }
         if (__all_sync(0xFFFFFFFFu, !active)) {
             if (exhausted) break;
             continue;
         }
         if (active) {
-            if constexpr (WIDE) cur = trav_descend_wide_ordered(sc, br, cur, bound, st, sp, tc, RT_DESCEND_STEPS / 2);
-            else cur = trav_descend<QNODES>(sc, br, cur, bound, st, sp, tc, RT_DESCEND_STEPS);
+            cur = trav_descend<QNODES>(sc, br, cur, bound, st, sp, tc, RT_DESCEND_STEPS);
         }
         __syncwarp();
         if (active) {
@@ -390,7 +398,7 @@ __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_closest_bvh(
             }
             if (active && ++walks > heavy_walks) {
                 // runaway traversal: hand the ray to the block-wide scan (k_heavy_scan), which redoes it from scratch
-                const uint32_t slot = atomicAdd(&counters->heavy_count, 1u);
+                const uint32_t slot = atomicAdd(&counters->lc[lc_index].heavy, 1u);
                 if (slot < HEAVY_CAP) { heavy[slot] = ray; active = false; }
                 else walks = 0;  // list full: keep traversing
             }
@@ -399,17 +407,18 @@ __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_closest_bvh(
     flush_traverse_count(tc, counters, 0);
 }
 
-// WIDE (experimental, RAYTRACE_B200_BVH_WIDE=1): the walk goes over sc.bvh_wnodes, four boxes per visit (rt_device.cuh
-// trav_descend_wide); everything else is the same kernel.
+// WIDE: the walk goes over sc.bvh_wnodes, four boxes per visit (rt_device.cuh trav_descend_wide); everything else is the
+// same kernel.
 template <bool QNODES, bool WIDE = false>
 __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_shadow_bvh(const __grid_constant__ DeviceScene sc, ShadowQueue sq, uint32_t n, double* accum, Counters* counters,
-                                                               uint32_t* heavy, uint32_t heavy_walks) {
+                                                               uint32_t* heavy, uint32_t heavy_walks, const uint32_t* n_dev, uint32_t lc_index) {
     __shared__ TravSmem sm;
-    uint32_t* cursor = &counters->cursor;
+    __shared__ uint32_t n_s;  // see k_closest_bvh
+    if (threadIdx.x == 0) n_s = n_dev ? (*n_dev < sq.cap ? *n_dev : sq.cap) : n;
+    __syncthreads();
     uint32_t range_next = FETCH_NONE;
-    const uint32_t chunk = fetch_chunk(n);
     uint32_t walks = 0;
-    TraverseCount tc; tc.nodes = 0; tc.prims = 0;
+    TraverseCount tc = traverse_count_zero();
 #ifdef RT_SHADOW_STACK64
     TravStack st; int sp = 0;
 #else
@@ -423,9 +432,10 @@ __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_shadow_bvh(c
     while (true) {
         const unsigned idle = __ballot_sync(0xFFFFFFFFu, !active);
         if (idle != 0u && !exhausted && (__popc(idle) >= FETCH_MIN_IDLE || idle == 0xFFFFFFFFu)) {
-            const uint32_t li = warp_fetch(idle, cursor, range_next, chunk);
+            const uint32_t n_now = n_s;
+            const uint32_t li = warp_fetch(idle, &counters->lc[lc_index].cursor, range_next, fetch_chunk(n_now));
             if (!active) {
-                if (li < n) {
+                if (li < n_now) {
                     ray = li;
                     const RayQ r = make_rayq(v3(sq.ox[ray], sq.oy[ray], sq.oz[ray]), v3(sq.dx[ray], sq.dy[ray], sq.dz[ray]));
                     const double range2 = sq.r2[ray];
@@ -443,7 +453,7 @@ __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_shadow_bvh(c
                     active = true;
                 }
             }
-            exhausted = __any_sync(0xFFFFFFFFu, li >= n && (idle >> (threadIdx.x & 31) & 1u));
+            exhausted = __any_sync(0xFFFFFFFFu, li >= n_now && (idle >> (threadIdx.x & 31) & 1u));
         }
         if (__all_sync(0xFFFFFFFFu, !active)) {
             if (exhausted) break;
@@ -463,7 +473,7 @@ __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_shadow_bvh(c
                 if (!occluded) accum_add(accum, sq.pixel[ray], c3(sq.cr[ray], sq.cg[ray], sq.cb[ray]));
                 active = false;
             } else if (++walks > heavy_walks) {
-                const uint32_t slot = atomicAdd(&counters->heavy_count, 1u);
+                const uint32_t slot = atomicAdd(&counters->lc[lc_index].heavy, 1u);
                 if (slot < HEAVY_CAP) { heavy[slot] = ray; active = false; }
                 else walks = 0;
             }
@@ -534,8 +544,8 @@ __device__ __forceinline__ bool heavy_scan_range(const DeviceScene& sc, const Ra
 // it does not depend on which CTA comes last.
 template <bool SHADOW>
 __global__ void __launch_bounds__(HEAVY_THREADS) k_heavy_scan(const __grid_constant__ DeviceScene sc, RayQueue q, ShadowQueue sq, uint32_t first,
-                                                              double* accum, Counters* counters, uint32_t* heavy) {
-    const uint32_t count = counters->heavy_count < HEAVY_CAP ? counters->heavy_count : HEAVY_CAP;
+                                                              double* accum, Counters* counters, uint32_t* heavy, uint32_t lc_index) {
+    const uint32_t count = counters->lc[lc_index].heavy < HEAVY_CAP ? counters->lc[lc_index].heavy : HEAVY_CAP;
     if (count == 0) return;
     HeavyScratch* hs = reinterpret_cast<HeavyScratch*>(heavy + HEAVY_CAP);
     uint32_t G = 1;
@@ -603,125 +613,170 @@ __global__ void __launch_bounds__(HEAVY_THREADS) k_heavy_scan(const __grid_const
 #ifndef RT_SHADE_MIN_BLOCKS
 #define RT_SHADE_MIN_BLOCKS 4
 #endif
+#ifndef RT_SHADE_WAVES
+#define RT_SHADE_WAVES 1  // LOOP grid = SMs x resident CTAs x this (tiles come off a cursor: the resident grid is enough)
+#endif
+// n_dev: the count is read on the device (clamped to the queue's capacity), so the launch can be queued before the host
+// knows it.  Two shapes of the same body:
+//   LOOP = false  one tile of SHADE_THREADS hits per CTA; with n_dev the grid was sized for an upper bound and CTAs past
+//                 the end leave at once -- right when the bound is tight (level 0: the bound is the path count);
+//   LOOP = true   a resident grid pulls tiles off a cursor -- for the deeper levels of a device-driven frame, whose bound
+//                 (capacity of the queue) can be hundreds of times the actual count.  Tiles are handed out in order, one
+//                 atomic each, so the rays a level appends keep the order of the level that spawned them, as with one CTA
+//                 per tile (blocks start in index order); a strided loop scrambles it, and the next level's traversal and
+//                 gathers pay for the lost coherence.
+template <bool LOOP>
 __global__ void __launch_bounds__(SHADE_THREADS, RT_SHADE_MIN_BLOCKS) k_shade(const __grid_constant__ DeviceScene sc, const __grid_constant__ FrameParams fp, RayQueue in,
                                                          uint32_t first, uint32_t n, RayQueue out, uint32_t* out_count, ShadowQueue sq,
-                                                         uint32_t* sq_count, uint32_t* overflow, double* accum, int32_t* ids) {
-    const uint32_t li = blockIdx.x * SHADE_THREADS + threadIdx.x;
-    const bool active = li < n;
-    ShadeCtx s;
-    s.alive = false; s.lit = false;
-    uint32_t pixel = 0, depth = 0;
-    if (active) {
-        const uint32_t i = first + li;
-        const V3 o = v3(in.ox[i], in.oy[i], in.oz[i]);
-        const V3 d = v3(in.dx[i], in.dy[i], in.dz[i]);
-        const C3 T = c3(in.tr[i], in.tg[i], in.tb[i]);
-        const uint32_t meta = in.meta[i];
-        const int32_t hid = in.hit_id[i];
-        pixel = in.pixel[i];
-        depth = meta & META_DEPTH_MASK;
-        if ((meta & META_RECORD_ID) && ids) ids[pixel] = hid;
-        const C3 add = shade_begin(sc, fp, o, d, T, in.sig[i], in.key[i], depth, hid, in.hit_t[i], s);
-        accum_add(accum, pixel, add);
+                                                         uint32_t* sq_count, uint32_t* overflow, double* accum, int32_t* ids, const uint32_t* n_dev, uint32_t* tile_cursor) {
+    constexpr int SHADE_WARPS = SHADE_THREADS / 32;
+    // double-buffered by tile parity: a warp that is one tile ahead writes the other half (it cannot get two ahead: both
+    // barriers of the tile in between need every warp)
+    __shared__ uint32_t w_shadow[2][SHADE_WARPS], w_child[2][SHADE_WARPS], cta_base[2][2];
+    __shared__ uint32_t n_s;  // LOOP: the count stays out of the registers (128 of the 176 this kernel wants)
+    __shared__ uint32_t tile_s[2];
+    if (LOOP) {
+        if (threadIdx.x == 0) {
+            n_s = n_dev ? (*n_dev < in.cap ? *n_dev : in.cap) : n;
+            tile_s[0] = atomicAdd(tile_cursor, 1u);
+        }
+        __syncthreads();
     }
-    // Queue slots for everything this CTA will emit are reserved up front with ONE atomic per queue.  (One per warp was a
-    // third of this kernel's stall samples: 2 x 260k returning atomics per 4K level on the same line of Counters queue up
-    // in one L2 slice; ncu source view, profiles/r01_v17_ncu_k_shade_stalls.md.)  The warps leave their counts in
-    // shared memory, thread 0 reserves for all of them, and every warp takes its share in warp order.
-    // Every lit hit casts a shadow ray at every light (src/scene.rs:117-155 tests occlusion only), so the count is known.
     const unsigned FULL = 0xFFFFFFFFu;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned below = (1u << lane) - 1u;
-    const bool lit = s.alive && s.lit;
-    const unsigned lit_m = __ballot_sync(FULL, lit);
-    const uint32_t n_lit = (uint32_t)__popc(lit_m);
-    uint32_t n_child = 0;
-    for (uint32_t k = 0; k < (uint32_t)sc.max_children; k++) n_child += (uint32_t)__popc(__ballot_sync(FULL, shade_child_wanted(s, k)));
-    constexpr int SHADE_WARPS = SHADE_THREADS / 32;
-    __shared__ uint32_t w_shadow[SHADE_WARPS], w_child[SHADE_WARPS], cta_base[2];
-    if (lane == 0) { w_shadow[warp] = n_lit * sc.n_lights; w_child[warp] = n_child; }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t ts = 0, tc = 0;
-#pragma unroll
-        for (int k = 0; k < SHADE_WARPS; k++) { ts += w_shadow[k]; tc += w_child[k]; }
-        uint32_t bs = 0, bc = 0;
-        if (ts) bs = atomicAdd(sq_count, ts);
-        if (tc) bc = atomicAdd(out_count, tc);
-        cta_base[0] = bs; cta_base[1] = bc;
-    }
-    __syncthreads();
-    uint32_t sbase = cta_base[0], cbase = cta_base[1];
-#pragma unroll
-    for (int k = 0; k < SHADE_WARPS; k++)
-        if (k < warp) { sbase += w_shadow[k]; cbase += w_child[k]; }
-    // light loop: light-major slots, so the lanes of a warp store side by side and rays to one light stay together
-    const uint32_t lit_rank = (uint32_t)__popc(lit_m & below);
-    for (uint32_t li2 = 0; li2 < sc.n_lights; li2++) {
-        ShadowRay sr;
-        if (shade_light(sc, s, li2, sr)) {
-            const uint32_t slot = sbase + li2 * n_lit + lit_rank;
-            if (slot >= sq.cap) { *overflow = 1u; continue; }
-            sq.ox[slot] = sr.o.x; sq.oy[slot] = sr.o.y; sq.oz[slot] = sr.o.z;
-            sq.dx[slot] = sr.d.x; sq.dy[slot] = sr.d.y; sq.dz[slot] = sr.d.z;
-            sq.r2[slot] = sr.range2;
-            sq.cr[slot] = sr.c.r; sq.cg[slot] = sr.c.g; sq.cb[slot] = sr.c.b;
-            sq.pixel[slot] = pixel;
+    uint32_t par = 0;
+    while (true) {
+        const uint32_t tile = LOOP ? tile_s[par] : blockIdx.x;
+        const uint32_t nn = LOOP ? n_s : (n_dev ? (*n_dev < in.cap ? *n_dev : in.cap) : n);
+        if ((uint64_t)tile * SHADE_THREADS >= nn) break;
+        if (LOOP && threadIdx.x == 0) tile_s[par ^ 1u] = atomicAdd(tile_cursor, 1u);  // next tile; published by this tile's barriers
+        const uint32_t li = tile * SHADE_THREADS + threadIdx.x;
+        const bool active = li < nn;
+        ShadeCtx s;
+        s.alive = false; s.lit = false;
+        uint32_t pixel = 0, depth = 0;
+        if (active) {
+            const uint32_t i = first + li;
+            const V3 o = v3(in.ox[i], in.oy[i], in.oz[i]);
+            const V3 d = v3(in.dx[i], in.dy[i], in.dz[i]);
+            const C3 T = c3(in.tr[i], in.tg[i], in.tb[i]);
+            const uint32_t meta = in.meta[i];
+            const int32_t hid = in.hit_id[i];
+            pixel = in.pixel[i];
+            depth = meta & META_DEPTH_MASK;
+            if ((meta & META_RECORD_ID) && ids) ids[pixel] = hid;
+            const C3 add = shade_begin(sc, fp, o, d, T, in.sig[i], in.key[i], depth, hid, in.hit_t[i], s);
+            accum_add(accum, pixel, add);
         }
-    }
-    // spawned rays: slot k of every lane in lock step
-    for (uint32_t k = 0; k < (uint32_t)sc.max_children; k++) {
-        ChildRay cr;
-        const bool want = shade_child(sc, s, k, cr);
-        const unsigned m = __ballot_sync(FULL, want);
-        const uint32_t slot = cbase + (uint32_t)__popc(m & below);
-        cbase += (uint32_t)__popc(m);
-        if (!want) continue;
-        if (slot >= out.cap) { *overflow = 1u; continue; }
-        out.ox[slot] = cr.o.x; out.oy[slot] = cr.o.y; out.oz[slot] = cr.o.z;
-        out.dx[slot] = cr.d.x; out.dy[slot] = cr.d.y; out.dz[slot] = cr.d.z;
-        out.tr[slot] = cr.T.r; out.tg[slot] = cr.T.g; out.tb[slot] = cr.T.b;
-        out.sig[slot] = cr.sig;
-        out.key[slot] = cr.key;
-        out.pixel[slot] = pixel;
-        out.meta[slot] = depth + 1u;
+        // Queue slots for everything this tile will emit are reserved up front with ONE atomic per queue.  (One per warp was
+        // a third of this kernel's stall samples: 2 x 260k returning atomics per 4K level on the same line of Counters queue
+        // up in one L2 slice; ncu source view, profiles/r01_v17_ncu_k_shade_stalls.md.)  The warps leave their counts in
+        // shared memory, thread 0 reserves for all of them, and every warp takes its share in warp order.
+        // Every lit hit casts a shadow ray at every light (src/scene.rs:117-155 tests occlusion only), so the count is known.
+        const bool lit = s.alive && s.lit;
+        const unsigned lit_m = __ballot_sync(FULL, lit);
+        const uint32_t n_lit = (uint32_t)__popc(lit_m);
+        uint32_t n_child = 0;
+        for (uint32_t k = 0; k < (uint32_t)sc.max_children; k++) n_child += (uint32_t)__popc(__ballot_sync(FULL, shade_child_wanted(s, k)));
+        if (lane == 0) { w_shadow[par][warp] = n_lit * sc.n_lights; w_child[par][warp] = n_child; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t ts = 0, tc = 0;
+#pragma unroll
+            for (int k = 0; k < SHADE_WARPS; k++) { ts += w_shadow[par][k]; tc += w_child[par][k]; }
+            uint32_t bs = 0, bc = 0;
+            if (ts) bs = atomicAdd(sq_count, ts);
+            if (tc) bc = atomicAdd(out_count, tc);
+            cta_base[par][0] = bs; cta_base[par][1] = bc;
+        }
+        __syncthreads();
+        uint32_t sbase = cta_base[par][0], cbase = cta_base[par][1];
+#pragma unroll
+        for (int k = 0; k < SHADE_WARPS; k++)
+            if (k < warp) { sbase += w_shadow[par][k]; cbase += w_child[par][k]; }
+        // light loop: light-major slots, so the lanes of a warp store side by side and rays to one light stay together
+        const uint32_t lit_rank = (uint32_t)__popc(lit_m & below);
+        for (uint32_t li2 = 0; li2 < sc.n_lights; li2++) {
+            ShadowRay sr;
+            if (shade_light(sc, s, li2, sr)) {
+                const uint32_t slot = sbase + li2 * n_lit + lit_rank;
+                if (slot >= sq.cap) { *overflow = 1u; continue; }
+                sq.ox[slot] = sr.o.x; sq.oy[slot] = sr.o.y; sq.oz[slot] = sr.o.z;
+                sq.dx[slot] = sr.d.x; sq.dy[slot] = sr.d.y; sq.dz[slot] = sr.d.z;
+                sq.r2[slot] = sr.range2;
+                sq.cr[slot] = sr.c.r; sq.cg[slot] = sr.c.g; sq.cb[slot] = sr.c.b;
+                sq.pixel[slot] = pixel;
+            }
+        }
+        // spawned rays: slot k of every lane in lock step
+        for (uint32_t k = 0; k < (uint32_t)sc.max_children; k++) {
+            ChildRay cr;
+            const bool want = shade_child(sc, s, k, cr);
+            const unsigned m = __ballot_sync(FULL, want);
+            const uint32_t slot = cbase + (uint32_t)__popc(m & below);
+            cbase += (uint32_t)__popc(m);
+            if (!want) continue;
+            if (slot >= out.cap) { *overflow = 1u; continue; }
+            out.ox[slot] = cr.o.x; out.oy[slot] = cr.o.y; out.oz[slot] = cr.o.z;
+            out.dx[slot] = cr.d.x; out.dy[slot] = cr.d.y; out.dz[slot] = cr.d.z;
+            out.tr[slot] = cr.T.r; out.tg[slot] = cr.T.g; out.tb[slot] = cr.T.b;
+            out.sig[slot] = cr.sig;
+            out.key[slot] = cr.key;
+            out.pixel[slot] = pixel;
+            out.meta[slot] = depth + 1u;
+        }
+        if (!LOOP) break;
+        par ^= 1u;
     }
 }
 
 // ---------------------------------------------------------------------------------------------------------
 // k_resolve: each thread produces 16 consecutive output bytes (one 128-bit store)
 // ---------------------------------------------------------------------------------------------------------
+// One thread per 16-byte piece of an output row (rows are padded to a multiple of 4 bytes, so a row's last piece may be
+// short).  final_rows: local row yl goes to its row of the whole frame (BMP order), `out` then being a whole-frame buffer --
+// the shard's own, or device 0's over NVLink peer access (context.cu rt_multi_*), which is what makes the gather a plain
+// store instead of a collective followed by a de-interleave.
 __global__ void __launch_bounds__(256) k_resolve(const __grid_constant__ DeviceScene sc, const __grid_constant__ FrameParams fp, const double* accum,
-                                                 uint8_t* out, uint32_t bytewidth, uint64_t total_bytes) {
+                                                 uint8_t* out, uint32_t bytewidth, uint32_t pieces_per_row, uint32_t final_rows) {
     __shared__ double avg[255];
     for (int i = threadIdx.x; i < 255; i += blockDim.x) avg[i] = sc.srgb_average[i];
     __syncthreads();
-    const uint64_t chunk = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const uint64_t b0 = chunk * 16;
-    if (b0 >= total_bytes) return;
+    const uint64_t piece = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t row = (uint32_t)(piece / pieces_per_row);
+    if (row >= fp.local_rows) return;
+    const uint32_t col0 = (uint32_t)(piece - (uint64_t)row * pieces_per_row) * 16u;
+    uint32_t out_row = row;
+    if (final_rows) {
+        const uint32_t band = row / fp.band_rows;
+        out_row = (band * fp.world + fp.rank) * fp.band_rows + row % fp.band_rows;
+        if (out_row >= fp.height) return;  // padding rows of the last band
+    }
     const double cam_div = (double)fp.cam_samples;
     const double aa_div = (double)fp.antialias;
-    uint32_t row = (uint32_t)(b0 / bytewidth);
-    uint32_t col = (uint32_t)(b0 - (uint64_t)row * bytewidth);
+    uint32_t col = col0;
     uint32_t px = col / 3, ch = col - px * 3;
     uint32_t words[4] = {0, 0, 0, 0};
     const uint32_t rowbytes = fp.width * 3;
 #pragma unroll
     for (int k = 0; k < 16; k++) {
         uint32_t v = 0;
-        if (b0 + k < total_bytes && col < rowbytes) {
+        if (col < rowbytes) {
             const double a = accum[((size_t)row * fp.width + px) * 3 + (2 - ch)];
             v = to_srgb(avg, (a / cam_div) / aa_div);  // raytrace(): res / samples (src/raytrace.rs:275); main: res / aa (src/main.rs:56)
         }
         words[k >> 2] |= v << (8 * (k & 3));
         col++; ch++;
         if (ch == 3) { ch = 0; px++; }
-        if (col == bytewidth) { col = 0; px = 0; ch = 0; row++; }
     }
-    if (b0 + 16 <= total_bytes) {
-        *reinterpret_cast<uint4*>(out + b0) = make_uint4(words[0], words[1], words[2], words[3]);
+    uint8_t* dst = out + (size_t)out_row * bytewidth + col0;
+    if ((bytewidth & 15u) == 0u) {  // every piece whole and 16-byte aligned
+        *reinterpret_cast<uint4*>(dst) = make_uint4(words[0], words[1], words[2], words[3]);
     } else {
-        for (int k = 0; b0 + k < total_bytes; k++) out[b0 + k] = (uint8_t)(words[k >> 2] >> (8 * (k & 3)));
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            if (col0 + 4 * k < bytewidth) reinterpret_cast<uint32_t*>(dst)[k] = words[k];
     }
 }
 
@@ -797,53 +852,59 @@ static uint32_t heavy_walks(const DeviceScene& sc) {
 }
 
 static void l_closest(cudaStream_t st, const DeviceScene& sc, bool bvh, RayQueue q, uint32_t first, uint32_t n, Counters* counters, int sm_count,
-                      uint32_t* heavy, const uint32_t* n_dev) {
-    if (!n && !n_dev) return;
+                      uint32_t* heavy, const uint32_t* n_dev, LaunchCursor* lc, bool reset_lc) {
+    if (!n) return;  // with n_dev, n is the upper bound the grid is sized for
     if (bvh) {
-        cudaMemsetAsync(&counters->cursor, 0, 2 * sizeof(uint32_t), st);  // cursor + heavy_count
+        if (reset_lc) cudaMemsetAsync(lc, 0, sizeof(LaunchCursor), st);
+        const uint32_t lci = (uint32_t)(lc - counters->lc);  // host arithmetic on device addresses only
         uint32_t want = div_up(n, BVH_THREADS);
         uint32_t grid = (uint32_t)sm_count * (uint32_t)RT_BVH_MIN_BLOCKS;  // resident CTAs of 128 threads per SM
-        if (!n_dev && want < grid) grid = want;
-        if (sc.bvh_qnodes && sc.bvh_wnodes && sc.bvh_wide_closest)
-            k_closest_bvh<true, true><<<grid, BVH_THREADS, 0, st>>>(sc, q, first, n, counters, heavy, heavy_walks(sc), n_dev);
-        else if (sc.bvh_qnodes) k_closest_bvh<true><<<grid, BVH_THREADS, 0, st>>>(sc, q, first, n, counters, heavy, heavy_walks(sc), n_dev);
-        else k_closest_bvh<false><<<grid, BVH_THREADS, 0, st>>>(sc, q, first, n, counters, heavy, heavy_walks(sc), n_dev);
+        if (want < grid) grid = want;
+        if (sc.bvh_qnodes) k_closest_bvh<true><<<grid, BVH_THREADS, 0, st>>>(sc, q, first, n, counters, heavy, heavy_walks(sc), n_dev, lci);
+        else k_closest_bvh<false><<<grid, BVH_THREADS, 0, st>>>(sc, q, first, n, counters, heavy, heavy_walks(sc), n_dev, lci);
         ShadowQueue none{};
-        k_heavy_scan<false><<<(uint32_t)sm_count * 4u, HEAVY_THREADS, 0, st>>>(sc, q, none, first, nullptr, counters, heavy);
+        k_heavy_scan<false><<<(uint32_t)sm_count * 4u, HEAVY_THREADS, 0, st>>>(sc, q, none, first, nullptr, counters, heavy, lci);
     } else {
         scan_attr_once();
-        k_closest_scan<<<div_up(n, SCAN_THREADS), SCAN_THREADS, sizeof(ScanSmem), st>>>(sc, q, first, n);
+        k_closest_scan<<<div_up(n, SCAN_THREADS), SCAN_THREADS, sizeof(ScanSmem), st>>>(sc, q, first, n, n_dev);
     }
 }
 
 static void l_shade(cudaStream_t st, const DeviceScene& sc, const FrameParams& fp, RayQueue in, uint32_t first, uint32_t n, RayQueue out,
-                    uint32_t* out_count, ShadowQueue sq, uint32_t* sq_count, uint32_t* overflow, double* accum, int32_t* ids) {
+                    uint32_t* out_count, ShadowQueue sq, uint32_t* sq_count, uint32_t* overflow, double* accum, int32_t* ids, int sm_count,
+                    const uint32_t* n_dev, uint32_t* tile_cursor) {
     if (!n) return;
-    k_shade<<<div_up(n, SHADE_THREADS), SHADE_THREADS, 0, st>>>(sc, fp, in, first, n, out, out_count, sq, sq_count, overflow, accum, ids);
+    const uint32_t want = div_up(n, SHADE_THREADS);
+    const uint32_t grid = (uint32_t)sm_count * (uint32_t)RT_SHADE_MIN_BLOCKS * (uint32_t)RT_SHADE_WAVES;
+    if (!tile_cursor || want <= grid) k_shade<false><<<want, SHADE_THREADS, 0, st>>>(sc, fp, in, first, n, out, out_count, sq, sq_count, overflow, accum, ids, n_dev, nullptr);
+    else k_shade<true><<<grid, SHADE_THREADS, 0, st>>>(sc, fp, in, first, n, out, out_count, sq, sq_count, overflow, accum, ids, n_dev, tile_cursor);
 }
 
 static void l_shadow(cudaStream_t st, const DeviceScene& sc, bool bvh, ShadowQueue sq, uint32_t n, double* accum, Counters* counters, int sm_count,
-                     uint32_t* heavy) {
+                     uint32_t* heavy, const uint32_t* n_dev, LaunchCursor* lc, bool reset_lc) {
     if (!n) return;
     if (bvh) {
-        cudaMemsetAsync(&counters->cursor, 0, 2 * sizeof(uint32_t), st);
+        if (reset_lc) cudaMemsetAsync(lc, 0, sizeof(LaunchCursor), st);
+        const uint32_t lci = (uint32_t)(lc - counters->lc);
         uint32_t want = div_up(n, BVH_THREADS);
         uint32_t grid = (uint32_t)sm_count * (uint32_t)RT_BVH_MIN_BLOCKS;
-        if (sc.bvh_qnodes && sc.bvh_wnodes) k_shadow_bvh<true, true><<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters, heavy, heavy_walks(sc));
-        else if (sc.bvh_qnodes) k_shadow_bvh<true><<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters, heavy, heavy_walks(sc));
-        else k_shadow_bvh<false><<<want < grid ? want : grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters, heavy, heavy_walks(sc));
+        if (want < grid) grid = want;
+        if (sc.bvh_qnodes && sc.bvh_wnodes) k_shadow_bvh<true, true><<<grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters, heavy, heavy_walks(sc), n_dev, lci);
+        else if (sc.bvh_qnodes) k_shadow_bvh<true><<<grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters, heavy, heavy_walks(sc), n_dev, lci);
+        else k_shadow_bvh<false><<<grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters, heavy, heavy_walks(sc), n_dev, lci);
         RayQueue none{};
-        k_heavy_scan<true><<<(uint32_t)sm_count * 4u, HEAVY_THREADS, 0, st>>>(sc, none, sq, 0u, accum, counters, heavy);
+        k_heavy_scan<true><<<(uint32_t)sm_count * 4u, HEAVY_THREADS, 0, st>>>(sc, none, sq, 0u, accum, counters, heavy, lci);
     } else {
         scan_attr_once();
-        k_shadow_scan<<<div_up(n, SCAN_THREADS), SCAN_THREADS, sizeof(ScanSmem), st>>>(sc, sq, n, accum);
+        k_shadow_scan<<<div_up(n, SCAN_THREADS), SCAN_THREADS, sizeof(ScanSmem), st>>>(sc, sq, n, accum, n_dev);
     }
 }
 
-static void l_resolve(cudaStream_t st, const DeviceScene& sc, const FrameParams& fp, const double* accum, uint8_t* out, uint32_t bytewidth) {
-    const uint64_t total = (uint64_t)bytewidth * fp.local_rows;
+static void l_resolve(cudaStream_t st, const DeviceScene& sc, const FrameParams& fp, const double* accum, uint8_t* out, uint32_t bytewidth, bool final_rows) {
+    const uint32_t pieces_per_row = (bytewidth + 15u) / 16u;
+    const uint64_t total = (uint64_t)pieces_per_row * fp.local_rows;
     if (!total) return;
-    k_resolve<<<div_up((total + 15) / 16, 256), 256, 0, st>>>(sc, fp, accum, out, bytewidth, total);
+    k_resolve<<<div_up(total, 256), 256, 0, st>>>(sc, fp, accum, out, bytewidth, pieces_per_row, final_rows ? 1u : 0u);
 }
 
 static void l_hit_normals(cudaStream_t st, const DeviceScene& sc, RayQueue q, uint32_t n, double* t_out, double* normal_out) {

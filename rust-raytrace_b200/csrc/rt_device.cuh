@@ -233,12 +233,18 @@ RT_HD bool shadow_result(const Shadow& s, double range2) { return s.nan ? (range
 // ---------------------------------------------------------------------------------------------------------
 #define RT_BVH_TSLACK 1.000000000001   // relative slack when a t of the exact test bounds the filter
 
+// Traversal stacks cannot overflow, and the walks do not spend instructions checking: a walk postpones at most one
+// child per level of the path it is on (binary) / three per two levels (wide), the Karras tree over 63 Morton bits +
+// 32 tie-break bits is at most 95 levels deep, and the build MEASURES the depth of the tree it made and refuses a tree
+// deeper than BVH_STACK (bvh_build.cu k_tree_depth -> rt_context_create fails) -- so a full stack is a build-time error,
+// never a silently pruned walk.
 constexpr int BVH_STACK = 96;          // >= 63 Morton bits + 32 tie-break bits
 constexpr int32_t TRAV_EMPTY = (int32_t)0x80000000;  // "no node left"; never a valid ~leaf (n_spheres < 2^31 - 16)
 
 struct TraverseCount {
-    uint32_t nodes, prims;  // 64-byte nodes fetched, exact sphere tests done
+    uint32_t nodes, prims;  // nodes fetched, exact sphere tests done
 };
+RT_HD TraverseCount traverse_count_zero() { TraverseCount t; t.nodes = 0; t.prims = 0; return t; }
 
 struct BoxRay32 {
     // slab distance of a box plane at coordinate v: v * s - off, with one slope per axis and two offsets:
@@ -488,7 +494,11 @@ RT_HD int32_t trav_pop(const TravStackFixed& st, int& sp, float) { return sp > 0
 // (returns ~slot < 0) or nothing is left (TRAV_EMPTY).  Leaves are NOT tested here: postponing them keeps the lanes
 // of a warp in the same code (box tests together, sphere tests together).
 // `max_steps` bounds the walk (the kernels come back to refill finished lanes; an unfinished walk returns cur >= 0).
-// ---- wide nodes (experimental, shadow queries) ----------------------------------------------------------
+// ---- wide nodes (shadow queries) --------------------------------------------------------------------------
+// Measured on the B200 (profiles/r02_v1_wide_ab.txt): 9.0 instead of 16.5 visits per shadow ray at 10k spheres, 14.9
+// instead of 26.2 at 1M; k_shadow_bvh 6.37 -> 6.19 ms and 7.72 -> 7.47 ms.  The closest-hit counterpart (nearest of four
+// boxes first, entry distances on the stack) halved the visits too but its sorting network made the launches SLOWER
+// (4.96 -> 5.40 ms, 5.12 -> 5.28 ms): removed.
 // One half of wide node i from binary node `parent`: the child `which` of it is either an internal node (its own two
 // children become the half) or a leaf (the half holds the leaf itself and an empty slot that no ray can hit).
 RT_HD BvhQNode widen_half(const BvhQNode& parent, int which, const BvhQNode* qnodes) {
@@ -518,12 +528,9 @@ constexpr int BVH_STACK_WIDE = 148;
 struct TravStackWide {
     int32_t e[BVH_STACK_WIDE];
 };
-RT_HD void trav_push(TravStackWide& st, int& sp, int32_t node, float) {
-    if (sp < BVH_STACK_WIDE) st.e[sp++] = node;
-}
 RT_HD int32_t trav_pop(const TravStackWide& st, int& sp, float) { return sp > 0 ? st.e[--sp] : TRAV_EMPTY; }
 RT_HD void trav_push_if(TravStackWide& st, int& sp, bool hit, int32_t node) {
-    if (hit && sp < BVH_STACK_WIDE) st.e[sp++] = node;  // two predicated instructions, no branch
+    if (hit) st.e[sp++] = node;  // two predicated instructions, no branch
 }
 
 // The walk of a shadow query over wide nodes.  No order among the children: the query only asks whether anything is
@@ -545,70 +552,6 @@ RT_HD int32_t trav_descend_wide(const DeviceScene& sc, const BoxRay32& br, int32
         trav_push_if(st, sp, h2, c2);
         trav_push_if(st, sp, h1, c1);
         trav_push_if(st, sp, h0, c0);
-        cur = trav_pop(st, sp, bound);
-    }
-    return cur;
-}
-
-// The same for closest-hit queries (experimental, RAYTRACE_B200_BVH_WIDE=2): the nearest of the hit children is walked
-// next, the others are postponed with their entry distances, so a pop can skip what the best hit so far has put out of
-// reach.  The order only decides how much is pruned; the answer is the leaf tests' (ties included: a box is walked
-// while its entry distance is <= the bound).
-struct TravStackWideT {
-    unsigned long long e[BVH_STACK_WIDE];
-};
-RT_HD void trav_push(TravStackWideT& st, int& sp, int32_t node, float t) {
-    if (sp < BVH_STACK_WIDE) st.e[sp++] = trav_pack(node, t);
-}
-RT_HD int32_t trav_pop(const TravStackWideT& st, int& sp, float bound) {
-    while (sp > 0) {
-        const unsigned long long e = st.e[--sp];
-        const uint32_t tb = (uint32_t)(e >> 32);
-        float t;
-        memcpy(&t, &tb, 4);
-        if (t <= bound) return (int32_t)(uint32_t)e;
-    }
-    return TRAV_EMPTY;
-}
-// compare-exchange of two (entry distance, link) pairs: the farther one ends up in a
-RT_HD void wide_cx(float& ta, int32_t& ca, float& tb, int32_t& cb) {
-    const bool sw = ta < tb;
-    const float t = sw ? tb : ta;
-    const int32_t c = sw ? cb : ca;
-    tb = sw ? ta : tb; cb = sw ? ca : cb;
-    ta = t; ca = c;
-}
-RT_HD void trav_push_if(TravStackWideT& st, int& sp, bool hit, int32_t node, float t) {
-    if (hit && sp < BVH_STACK_WIDE) st.e[sp++] = trav_pack(node, t);
-}
-RT_HD int32_t trav_descend_wide_ordered(const DeviceScene& sc, const BoxRay32& br, int32_t cur, float bound, TravStackWideT& st, int& sp,
-                                        TraverseCount& tc, int max_steps = 0x7FFFFFFF) {
-    while (cur >= 0 && max_steps-- > 0) {
-        const BvhQNode* p = sc.bvh_wnodes[cur].h;
-        const QNodeWords a = load_qnode(p), b = load_qnode(p + 1);
-        float t0, t1, t2, t3;
-        int32_t c0 = (int32_t)a.w[6], c1 = (int32_t)a.w[7], c2 = (int32_t)b.w[6], c3 = (int32_t)b.w[7];
-        const bool h0 = box_hit_q(br, a.w[0], a.w[1], a.w[2], bound, t0) && c0 != TRAV_EMPTY;
-        const bool h1 = box_hit_q(br, a.w[3], a.w[4], a.w[5], bound, t1) && c1 != TRAV_EMPTY;
-        const bool h2 = box_hit_q(br, b.w[0], b.w[1], b.w[2], bound, t2) && c2 != TRAV_EMPTY;
-        const bool h3 = box_hit_q(br, b.w[3], b.w[4], b.w[5], bound, t3) && c3 != TRAV_EMPTY;
-        tc.nodes++;
-        // A miss becomes (+inf, TRAV_EMPTY); a five-comparator network orders the four pairs far to near; the hits go on the
-        // stack in that order and the nearest comes straight off again -- no branch on which were hit, and later pops meet
-        // the postponed boxes nearest first.  (Entry distances are >= 0, never NaN: box_hit_q clamps them at 0.)
-        if (!h0) { t0 = INFINITY; c0 = TRAV_EMPTY; }
-        if (!h1) { t1 = INFINITY; c1 = TRAV_EMPTY; }
-        if (!h2) { t2 = INFINITY; c2 = TRAV_EMPTY; }
-        if (!h3) { t3 = INFINITY; c3 = TRAV_EMPTY; }
-        wide_cx(t0, c0, t1, c1);
-        wide_cx(t2, c2, t3, c3);
-        wide_cx(t0, c0, t2, c2);
-        wide_cx(t1, c1, t3, c3);
-        wide_cx(t1, c1, t2, c2);
-        trav_push_if(st, sp, c0 != TRAV_EMPTY, c0, t0);
-        trav_push_if(st, sp, c1 != TRAV_EMPTY, c1, t1);
-        trav_push_if(st, sp, c2 != TRAV_EMPTY, c2, t2);
-        trav_push_if(st, sp, c3 != TRAV_EMPTY, c3, t3);
         cur = trav_pop(st, sp, bound);
     }
     return cur;
@@ -641,7 +584,7 @@ RT_HD int32_t trav_descend(const DeviceScene& sc, const BoxRay32& br, int32_t cu
         const bool both = h0 && h1;
         const bool second = h1 && (!h0 || t1 < t0);
         const int32_t nearc = second ? c1 : c0;
-        if (both && sp < BVH_STACK) trav_push(st, sp, second ? c0 : c1, second ? t0 : t1);
+        if (both) trav_push(st, sp, second ? c0 : c1, second ? t0 : t1);
         if (h0 || h1) cur = nearc;
         else cur = trav_pop(st, sp, bound);
 #if defined(__CUDA_ARCH__) && RT_DESCEND_MIN_LANES > 0
@@ -682,19 +625,7 @@ RT_HD void closest_bvh(const DeviceScene& sc, const RayQ& r, int32_t& id, double
     planes_closest(sc, r, best);
     if (!best.nan && sc.n_spheres > 0) {
         const BoxRay32 br = make_boxray32(sc, r.o, r.d);
-        if (br.enter && sc.bvh_wnodes && sc.bvh_wide_closest) {
-            TravStackWideT st;
-            int sp = 0;
-            int32_t cur = 0;
-            float bound = closest_bound32(best.t, br.t0);
-            while (true) {
-                cur = trav_descend_wide_ordered(sc, br, cur, bound, st, sp, tc);
-                if (cur == TRAV_EMPTY) break;
-                leaf_closest(sc, r, ~cur, best, tc);
-                bound = closest_bound32(best.t, br.t0);
-                cur = trav_pop(st, sp, bound);
-            }
-        } else if (br.enter) {
+        if (br.enter) {
             TravStack st;
             int sp = 0;
             int32_t cur = 0;
@@ -1086,17 +1017,16 @@ RT_HD uint64_t spread21(uint64_t v) {
     return v;
 }
 // Scale of the Morton grid: the SAME step on all three axes (1 / longest centroid extent), so that the tree splits the
-// long axes of a flat scene first and its boxes stay near-cubical; per-axis scaling (RAYTRACE_B200_MORTON=axis, kept for
+// long axes of a flat scene first and its boxes stay near-cubical; per-axis scaling (RT_TUNE_MORTON_AXIS, kept for
 // A/B runs) splits a 120 x 7 x 120 field as often in y as in x and z and yields pancake boxes.
-inline void morton_scale(const double* lo, const double* hi, double* inv_ext) {
+inline void morton_scale(const double* lo, const double* hi, double* inv_ext, bool per_axis = false) {
     double longest = 0.0;
     for (int a = 0; a < 3; a++) {
         const double ext = hi[a] - lo[a];
         inv_ext[a] = ext > 0.0 ? 1.0 / ext : 0.0;
         if (ext > longest) longest = ext;   // NaN / inf extents never win; their axis keeps inv = 0 or 1/inf = 0
     }
-    const char* e = getenv("RAYTRACE_B200_MORTON");
-    if (e && !strcmp(e, "axis")) return;
+    if (per_axis) return;
     if (longest > 0.0 && longest < (double)INFINITY)
         for (int a = 0; a < 3; a++)
             if (inv_ext[a] > 0.0) inv_ext[a] = 1.0 / longest;

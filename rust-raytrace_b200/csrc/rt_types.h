@@ -76,7 +76,7 @@ struct alignas(32) BvhQNode {
     int32_t c0, c1;
 };
 
-// 64-byte wide node (experimental; shadow queries only, RAYTRACE_B200_BVH_WIDE=1): the four grandchildren of binary node i
+// 64-byte wide node (shadow queries; off with RT_TUNE_BINARY_SHADOW): the four grandchildren of binary node i
 // as two BvhQNode halves -- h[0] = the two children of node i's child 0, h[1] = those of its child 1 -- so a visit tests four
 // boxes behind one dependent fetch (two 256-bit loads of one 64-byte line) instead of two.  A child of node i that is a
 // leaf fills slot 0 of its half with its own box and link; slot 1 is then empty: link TRAV_EMPTY, box inside out.
@@ -108,7 +108,7 @@ struct DeviceScene {
     const SphereRec* bvh_sph;  // Morton order
     const int32_t* bvh_obj;    // object index of Morton slot k
     uint32_t n_bvh_nodes;
-    uint32_t bvh_wide_closest;  // 1: closest-hit queries walk bvh_wnodes too (experimental, RAYTRACE_B200_BVH_WIDE=2)
+    uint32_t _pad_bvh;
     double bvh_cmax;  // max over spheres of (|c|_inf + r): scale term of the per-ray box padding
     double bvh_rmin;  // min radius
     double bvh_inv2rmin;  // 0.5 / bvh_rmin, rounded up

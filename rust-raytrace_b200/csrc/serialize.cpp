@@ -11,6 +11,7 @@
 //
 // Deliberate deviation: an unterminated `/*` comment spins forever upstream (src/serialize.rs:395-399);
 // here it is reported as "invalid token".
+#include <cerrno>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -642,20 +643,60 @@ int rt_scene_parse(const char* text, size_t len, rt_scene** out, char* err, size
     return RT_OK;
 }
 
+// std::str::from_utf8's acceptance test (read_to_string fails on anything else, src/main.rs:22-25): shortest forms only,
+// no surrogates, nothing above U+10FFFF
+static bool valid_utf8(const std::string& s) {
+    const unsigned char* p = (const unsigned char*)s.data();
+    const unsigned char* e = p + s.size();
+    while (p < e) {
+        const unsigned char c = *p;
+        if (c < 0x80) { p++; continue; }
+        int n;
+        unsigned lo = 0x80, hi = 0xBF;
+        if (c >= 0xC2 && c <= 0xDF) n = 1;
+        else if (c == 0xE0) { n = 2; lo = 0xA0; }
+        else if (c >= 0xE1 && c <= 0xEC) n = 2;
+        else if (c == 0xED) { n = 2; hi = 0x9F; }
+        else if (c >= 0xEE && c <= 0xEF) n = 2;
+        else if (c == 0xF0) { n = 3; lo = 0x90; }
+        else if (c >= 0xF1 && c <= 0xF3) n = 3;
+        else if (c == 0xF4) { n = 3; hi = 0x8F; }
+        else return false;
+        if (e - p <= n) return false;
+        if (p[1] < lo || p[1] > hi) return false;
+        for (int k = 2; k <= n; k++)
+            if (p[k] < 0x80 || p[k] > 0xBF) return false;
+        p += n + 1;
+    }
+    return true;
+}
+
+// File::open + read_to_string + deserialize (src/main.rs:16-29).  RT_ERR_IO messages are what `println!("error: {}", e)`
+// shows for the io::Error upstream: "<strerror> (os error <errno>)", or "stream did not contain valid UTF-8".
 int rt_scene_parse_file(const char* path, rt_scene** out, char* err, size_t errcap) {
     if (!path || !out) { rt::set_error("rt_scene_parse_file: null argument"); return RT_ERR_INVALID; }
-    FILE* f = std::fopen(path, "rb");
-    if (!f) {
-        std::string m = std::string("cannot open ") + path;
+    auto io_fail = [&](const std::string& m) {
         rt::set_error(m);
         if (err && errcap) std::snprintf(err, errcap, "%s", m.c_str());
         return RT_ERR_IO;
+    };
+    errno = 0;
+    FILE* f = std::fopen(path, "rb");
+    if (!f) {
+        const int en = errno;
+        return io_fail(std::string(std::strerror(en)) + " (os error " + std::to_string(en) + ")");
     }
     std::string buf;
     char tmp[65536];
     size_t n;
     while ((n = std::fread(tmp, 1, sizeof tmp, f)) > 0) buf.append(tmp, n);
+    if (std::ferror(f)) {
+        const int en = errno;
+        std::fclose(f);
+        return io_fail(std::string(std::strerror(en)) + " (os error " + std::to_string(en) + ")");
+    }
     std::fclose(f);
+    if (!valid_utf8(buf)) return io_fail("stream did not contain valid UTF-8");
     return rt_scene_parse(buf.data(), buf.size(), out, err, errcap);
 }
 

@@ -52,7 +52,7 @@ def lib():
         L.emu_quantize_bgr.argtypes = [dp, C.c_uint64, u8p]
         L.emu_quantize_bgr.restype = None
         L.emu_bvh_stats.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]
-        L.emu_flat_cache_probe.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
+        L.emu_flat_cache_probe.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_uint64)]
         _lib = L
     return _lib
 
@@ -135,8 +135,8 @@ def bvh_stats(scene):
     return n.value, d.value
 
 
-def bvh_node_bytes(scene):
+def bvh_node_bytes(scene, tuning=0):
     """bytes per BVH node the product would use for this scene: 32 = grid form, 64 = f32 planes"""
     b = C.c_uint32()
-    B.check(lib(), lib().emu_bvh_node_bytes(scene.handle, C.byref(b)))
+    B.check(lib(), lib().emu_bvh_node_bytes(scene.handle, C.c_uint32(tuning), C.byref(b)))
     return b.value

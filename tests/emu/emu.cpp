@@ -28,7 +28,7 @@ struct EmuScene {
     DeviceScene ds{};
     std::vector<BvhNode> nodes;
     std::vector<BvhQNode> qnodes;  // grid form, when the scene's grid is fine enough (host_scene.cpp choose_quantisation)
-    std::vector<BvhWNode> wnodes;  // wide form for shadow queries, when RAYTRACE_B200_BVH_WIDE=1 (as in context.cu)
+    std::vector<BvhWNode> wnodes;  // wide form for shadow queries, unless RT_TUNE_BINARY_SHADOW (as in context.cu)
     std::vector<SphereRec> bvh_sph;
     std::vector<int32_t> bvh_obj;
     bool use_bvh = false;
@@ -48,11 +48,11 @@ Box leaf_box(const SphereRec& s) {
 }
 
 // the device build's algorithm, serially: same Morton codes, same (code, index) order, same Karras nodes
-void build_bvh(EmuScene& e) {
+void build_bvh(EmuScene& e, bool morton_per_axis) {
     const uint32_t n = (uint32_t)e.flat.sph.size();
     if (n == 0) return;
     double inv[3];
-    morton_scale(e.flat.centroid_lo, e.flat.centroid_hi, inv);
+    morton_scale(e.flat.centroid_lo, e.flat.centroid_hi, inv, morton_per_axis);
     std::vector<std::pair<uint64_t, uint32_t>> keyed(n);
     for (uint32_t i = 0; i < n; i++) keyed[i] = {morton63(e.flat.sph[i].cx, e.flat.sph[i].cy, e.flat.sph[i].cz, e.flat.centroid_lo, inv), i};
     std::sort(keyed.begin(), keyed.end());
@@ -100,7 +100,7 @@ void build_bvh(EmuScene& e) {
     }
 }
 
-int make_scene(const rt_scene* s, int accel, EmuScene* e) {
+int make_scene(const rt_scene* s, int accel, uint32_t tuning, EmuScene* e) {
     const rt_scene* use = s;
     rt_scene patched;
     if (!s->camera_set || !s->background_set) {
@@ -108,7 +108,7 @@ int make_scene(const rt_scene* s, int accel, EmuScene* e) {
         patched.camera_set = true; patched.background_set = true; patched.bg_kind = BG_SOLID;
         use = &patched;
     }
-    int rc = flatten_scene(use, &e->flat);
+    int rc = flatten_scene(use, &e->flat, tuning);
     if (rc != RT_OK) return rc;
     fill_scene_header(use, e->flat, &e->ds);
     e->ds.sph = e->flat.sph.data(); e->ds.sph_obj = e->flat.sph_obj.data(); e->ds.planes = e->flat.planes.data();
@@ -118,7 +118,7 @@ int make_scene(const rt_scene* s, int accel, EmuScene* e) {
     e->ds.srgb_values = SRGB_VALUES; e->ds.srgb_average = SRGB_AVERAGE;
     e->use_bvh = accel_uses_bvh(accel, e->ds.n_spheres);
     if (e->use_bvh) {
-        build_bvh(*e);
+        build_bvh(*e, (tuning & RT_TUNE_MORTON_AXIS) != 0);
         e->ds.bvh_nodes = e->nodes.data(); e->ds.bvh_sph = e->bvh_sph.data(); e->ds.bvh_obj = e->bvh_obj.data();
         e->ds.n_bvh_nodes = (uint32_t)e->nodes.size();
         if (e->flat.quant) {
@@ -126,12 +126,10 @@ int make_scene(const rt_scene* s, int accel, EmuScene* e) {
             e->qnodes.resize(e->nodes.size());
             for (size_t i = 0; i < e->nodes.size(); i++) e->qnodes[i] = quantise_node(e->nodes[i], e->flat.q_org, e->flat.q_cell, ok);
             if (ok) e->ds.bvh_qnodes = e->qnodes.data();
-            const char* wide = std::getenv("RAYTRACE_B200_BVH_WIDE");
-            if (ok && wide && (wide[0] == '1' || wide[0] == '2')) {
+            if (ok && !(tuning & RT_TUNE_BINARY_SHADOW)) {  // as context.cu: shadow queries walk the four-wide nodes
                 e->wnodes.resize(e->qnodes.size());
                 for (size_t i = 0; i < e->qnodes.size(); i++) e->wnodes[i] = widen_node(e->qnodes.data(), (uint32_t)i);
                 e->ds.bvh_wnodes = e->wnodes.data();
-                e->ds.bvh_wide_closest = wide[0] == '2' ? 1u : 0u;
             }
         }
     }
@@ -155,7 +153,7 @@ extern "C" {
 // same contract as rt_context_render + rt_context_download for one shard (local row order)
 RT_API int emu_render_shard(const rt_scene* s, const rt_render_opts* o, uint8_t* bgr_rows, int32_t* ids, double* accum_out, rt_stats* stats) {
     EmuScene e;
-    int rc = make_scene(s, o->accel, &e);
+    int rc = make_scene(s, o->accel, o->tuning, &e);
     if (rc != RT_OK) return rc;
     FrameParams fp{};
     if ((rc = make_frame_params(s, o, &fp)) != RT_OK) return rc;
@@ -252,7 +250,7 @@ RT_API int emu_render_shard(const rt_scene* s, const rt_render_opts* o, uint8_t*
 
 RT_API int emu_trace_rays(const rt_scene* s, const rt_render_opts* o, uint64_t n, const double* od, int32_t* ids, double* t_out, double* normal) {
     EmuScene e;
-    int rc = make_scene(s, o->accel, &e);
+    int rc = make_scene(s, o->accel, o->tuning, &e);
     if (rc != RT_OK) return rc;
     for (uint64_t i = 0; i < n; i++) {
         V3 org = v3(od + 6 * i), dir = v3(od + 6 * i + 3);
@@ -272,7 +270,7 @@ RT_API int emu_trace_rays(const rt_scene* s, const rt_render_opts* o, uint64_t n
 // shadow queries: occluded[i] for ray i with squared range r2[i] (< 0 = none)
 RT_API int emu_shadow_rays(const rt_scene* s, const rt_render_opts* o, uint64_t n, const double* od, const double* r2, uint8_t* occluded) {
     EmuScene e;
-    int rc = make_scene(s, o->accel, &e);
+    int rc = make_scene(s, o->accel, o->tuning, &e);
     if (rc != RT_OK) return rc;
     for (uint64_t i = 0; i < n; i++) {
         RayQ rq = make_rayq(v3(od + 6 * i), v3(od + 6 * i + 3));
@@ -297,9 +295,7 @@ RT_API void emu_quantize_bgr(const double* rgb, uint64_t n, uint8_t* bgr) {
 
 RT_API int emu_bvh_stats(const rt_scene* s, uint64_t* n_nodes, uint32_t* max_depth) {
     EmuScene e;
-    rt_render_opts o{};
-    int rc = make_scene(s, RT_ACCEL_BVH, &e);
-    (void)o;
+    int rc = make_scene(s, RT_ACCEL_BVH, 0, &e);
     if (rc != RT_OK) return rc;
     *n_nodes = e.nodes.size();
     uint32_t md = 0;
@@ -319,9 +315,9 @@ RT_API int emu_bvh_stats(const rt_scene* s, uint64_t* n_nodes, uint32_t* max_dep
 
 // the scene's flatten cache (host_scene.h FlatCache), as rt_context_create sees it: out = {entry identity, revision,
 // spheres, planes, objects, max_children}
-RT_API int emu_flat_cache_probe(const rt_scene* s, uint64_t* out) {
+RT_API int emu_flat_cache_probe(const rt_scene* s, uint32_t tuning, uint64_t* out) {
     std::shared_ptr<FlatCache> fc;
-    int rc = flatten_scene_cached(s, &fc);
+    int rc = flatten_scene_cached(s, tuning, &fc);
     if (rc != RT_OK) return rc;
     out[0] = (uint64_t)(uintptr_t)fc.get();
     out[1] = fc->revision;
@@ -332,9 +328,9 @@ RT_API int emu_flat_cache_probe(const rt_scene* s, uint64_t* out) {
     return RT_OK;
 }
 
-RT_API int emu_bvh_node_bytes(const rt_scene* s, uint32_t* bytes) {
+RT_API int emu_bvh_node_bytes(const rt_scene* s, uint32_t tuning, uint32_t* bytes) {
     EmuScene e;
-    int rc = make_scene(s, RT_ACCEL_BVH, &e);
+    int rc = make_scene(s, RT_ACCEL_BVH, tuning, &e);
     if (rc != RT_OK) return rc;
     *bytes = !e.use_bvh ? 0u : (e.ds.bvh_qnodes ? (uint32_t)sizeof(BvhQNode) : (uint32_t)sizeof(BvhNode));
     return RT_OK;

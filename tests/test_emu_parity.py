@@ -191,34 +191,33 @@ def test_far_origins_advance_to_the_scene(rt, orc, scenes, accel):
 def test_both_node_formats_equal_the_scan(rt, orc, scenes, nodes, monkeypatch):
     """32-byte grid nodes (boxes rounded outward to a 16-bit grid, padded 1.25 cells) and 64-byte f32 nodes are both only
     a conservative filter in front of the scan's exact test: ids, t and normals bit-identical with either"""
-    monkeypatch.setenv("RAYTRACE_B200_BVH_NODES", nodes)
+    tune = rt.TUNE_NODES_Q16 if nodes == "q16" else rt.TUNE_NODES_F32
     desc = scenes.random_spheres(3000, 31, 40.0, 8, 8)
-    assert emu.bvh_node_bytes(emu.Scene(desc)) == (32 if nodes == "q16" else 64)
+    assert emu.bvh_node_bytes(emu.Scene(desc), tune) == (32 if nodes == "q16" else 64)
     rng = np.random.default_rng(12)
     rays = _rays(rng, 40000, 45.0, 8.0)
     rays[:2000, 3:] = np.array([1.0, 0.0, 0.0]) * rng.choice([-1.0, 1.0], 2000)[:, None]   # axis-parallel: clamped reciprocals
     rays[2000:4000, 4] = 0.0
     rays[4000:5000, 3] = 1e-35
-    ids, t, nrm = emu.trace_rays(emu.Scene(desc), rays, accel=rt.ACCEL_BVH)
+    ids, t, nrm = emu.trace_rays(emu.Scene(desc), rays, accel=rt.ACCEL_BVH, tuning=tune)
     rid, rt_, rn = orc.OracleScene(desc).trace_rays(rays)
     assert np.array_equal(ids, rid) and np.array_equal(t, rt_) and np.array_equal(nrm, rn)
     r2 = np.where(rng.uniform(size=len(rays)) < 0.3, -1.0, rng.uniform(0.0, 60.0, len(rays)) ** 2)
-    occ = emu.shadow_rays(emu.Scene(desc), rays, r2, accel=rt.ACCEL_BVH)
-    with np.errstate(invalid="ignore"):
-        assert np.array_equal(occ, (rid >= 0) & ((r2 < 0) | (rt_ * rt_ < r2)))
+    for shadow_tune in (tune, tune | rt.TUNE_BINARY_SHADOW):   # four-wide walk (grid nodes only) and binary walk
+        occ = emu.shadow_rays(emu.Scene(desc), rays, r2, accel=rt.ACCEL_BVH, tuning=shadow_tune)
+        with np.errstate(invalid="ignore"):
+            assert np.array_equal(occ, (rid >= 0) & ((r2 < 0) | (rt_ * rt_ < r2)))
 
 
-def test_node_format_follows_the_grid_resolution(rt, scenes, monkeypatch):
-    monkeypatch.delenv("RAYTRACE_B200_BVH_NODES", raising=False)
+def test_node_format_follows_the_grid_resolution(rt, scenes):
     assert emu.bvh_node_bytes(emu.Scene(scenes.random_spheres(500, 3, 60.0, 8, 8))) == 32       # cell 0.002 vs radius 0.5
     assert emu.bvh_node_bytes(emu.Scene(scenes.random_spheres(500, 3, 30000.0, 8, 8))) == 64    # cell 0.9: too coarse
 
 
 def test_coarse_grid_is_still_conservative(rt, orc, scenes, monkeypatch):
     """forcing the grid on a scene it is far too coarse for (cells larger than the spheres) may only cost time"""
-    monkeypatch.setenv("RAYTRACE_B200_BVH_NODES", "q16")
     desc = scenes.random_spheres(800, 9, 30000.0, 8, 8)
-    assert emu.bvh_node_bytes(emu.Scene(desc)) == 32
+    assert emu.bvh_node_bytes(emu.Scene(desc), rt.TUNE_NODES_Q16) == 32
     data = desc["objects"][1]["data"]
     rng = np.random.default_rng(2)
     k = rng.integers(0, len(data), 6000)
@@ -282,7 +281,7 @@ def test_filter_is_conservative_on_odd_scenes(rt, orc, case):
     assert emu.bvh_node_bytes(emu.Scene(desc)) == (64 if case in (2, 7) else 32)   # 4000- and 60000-wide fields: grid too coarse
 
 
-def test_flatten_cache_follows_scene_edits(scenes, monkeypatch):
+def test_flatten_cache_follows_scene_edits(rt, scenes):
     """rt_context_create flattens a scene once and keeps the result with the rt_scene (host_scene.h FlatCache); every
     builder call that changes objects, materials or skybox faces must drop it (it may be page-locked in place)."""
     import ctypes as C
@@ -290,9 +289,9 @@ def test_flatten_cache_follows_scene_edits(scenes, monkeypatch):
     L = emu.lib()
     sc = emu.Scene(scenes.random_spheres(50, 3, 10.0, 32, 24))
 
-    def probe():
+    def probe(tuning=0):
         out = (C.c_uint64 * 6)()
-        assert L.emu_flat_cache_probe(sc.handle, out) == 0
+        assert L.emu_flat_cache_probe(sc.handle, tuning, out) == 0
         return list(out)
 
     a, b = probe(), probe()
@@ -310,15 +309,15 @@ def test_flatten_cache_follows_scene_edits(scenes, monkeypatch):
     e = probe()
     assert e[1] > d[1] and e[2:5] == [51, 2, 53]
     # the node-format override is part of the key (A/B runs switch it between contexts of one scene)
-    monkeypatch.setenv("RAYTRACE_B200_BVH_NODES", "f32")
-    f = probe()
-    assert f[1] == e[1] and probe() == f
-    monkeypatch.delenv("RAYTRACE_B200_BVH_NODES")
+    f = probe(rt.TUNE_NODES_F32)
+    assert f[1] == e[1] and f[0] != e[0] and probe(rt.TUNE_NODES_F32) == f
+    assert probe(rt.TUNE_NODES_F32 | rt.TUNE_MORTON_AXIS) == f      # only the node bits decide the flattened form
     assert probe()[1] == e[1]
 
 
 # ---------------------------------------------------------------------------------------------------------------------
-# experimental wide nodes for shadow queries (RAYTRACE_B200_BVH_WIDE=1; rt_types.h BvhWNode, rt_device.cuh trav_descend_wide)
+# four-wide nodes for shadow queries (default where the grid nodes are in use; rt_types.h BvhWNode, rt_device.cuh
+# trav_descend_wide); RT_TUNE_BINARY_SHADOW selects the binary walk they are derived from
 # ---------------------------------------------------------------------------------------------------------------------
 def _wide_scenes(rt, scenes):
     S = rt.scene
@@ -340,69 +339,34 @@ def _wide_scenes(rt, scenes):
     return out
 
 
-def test_wide_shadow_walk_equals_scan_and_binary_walk(rt, orc, scenes, monkeypatch):
+def test_wide_shadow_walk_equals_scan_and_binary_walk(rt, orc, scenes):
     """the four-wide shadow walk answers every query like the linear scan (and like the binary walk it is derived from)"""
     rng = np.random.default_rng(7)
     for name, desc in _wide_scenes(rt, scenes):
         rays = _rays(rng, 6000, 14.0, 8.0)
         r2 = np.where(rng.uniform(size=6000) < 0.3, -1.0, rng.uniform(0.0, 30.0, 6000) ** 2)
-        monkeypatch.delenv("RAYTRACE_B200_BVH_WIDE", raising=False)
         scan = emu.shadow_rays(emu.Scene(desc), rays, r2, accel=rt.ACCEL_LINEAR)
-        binary = emu.shadow_rays(emu.Scene(desc), rays, r2, accel=rt.ACCEL_BVH)
-        monkeypatch.setenv("RAYTRACE_B200_BVH_WIDE", "1")
-        wide = emu.shadow_rays(emu.Scene(desc), rays, r2, accel=rt.ACCEL_BVH)
+        binary = emu.shadow_rays(emu.Scene(desc), rays, r2, accel=rt.ACCEL_BVH, tuning=rt.TUNE_NODES_Q16 | rt.TUNE_BINARY_SHADOW)
+        wide = emu.shadow_rays(emu.Scene(desc), rays, r2, accel=rt.ACCEL_BVH, tuning=rt.TUNE_NODES_Q16)
         assert np.array_equal(binary, scan), name
         assert np.array_equal(wide, scan), name
-    monkeypatch.delenv("RAYTRACE_B200_BVH_WIDE")
 
 
-def test_wide_shadow_walk_renders_the_oracle_frame(rt, orc, scenes, monkeypatch):
+def test_wide_shadow_walk_renders_the_oracle_frame(rt, orc, scenes):
     desc = scenes.random_spheres(1500, 0x5EED0003, 25.0, 96, 54)
     ref = orc.OracleScene(desc).render(max_depth=6, seed=3)
-    monkeypatch.setenv("RAYTRACE_B200_BVH_WIDE", "1")
+    assert emu.bvh_node_bytes(emu.Scene(desc)) == 32      # grid nodes, hence wide shadow nodes, by default
     got = emu.render(emu.Scene(desc), max_depth=6, seed=3, accel=rt.ACCEL_BVH)
     check(got, ref, "spheres1500 wide")
     assert ref["stats"]["shadow_rays"] > 96 * 54
 
 
-def test_wide_nodes_halve_the_dependent_fetches(rt, scenes, monkeypatch):
+def test_wide_nodes_halve_the_dependent_fetches(rt, scenes):
     """what the wide nodes are for: about half as many node visits per shadow query (each one fetch of 64 bytes)"""
     desc = scenes.random_spheres(1500, 0x5EED0003, 25.0, 96, 54)
-    monkeypatch.delenv("RAYTRACE_B200_BVH_WIDE", raising=False)
-    a = emu.render(emu.Scene(desc), max_depth=3, seed=3, accel=rt.ACCEL_BVH)
-    monkeypatch.setenv("RAYTRACE_B200_BVH_WIDE", "1")
+    a = emu.render(emu.Scene(desc), max_depth=3, seed=3, accel=rt.ACCEL_BVH, tuning=rt.TUNE_BINARY_SHADOW)
     b = emu.render(emu.Scene(desc), max_depth=3, seed=3, accel=rt.ACCEL_BVH)
     va, vb = a["stats"]["bvh_nodes_visited"]["shadow"], b["stats"]["bvh_nodes_visited"]["shadow"]
     assert a["stats"]["bvh_nodes_visited"]["closest"] == b["stats"]["bvh_nodes_visited"]["closest"] > 0
     assert np.array_equal(a["bgr"], b["bgr"])
     assert 0.35 * va < vb < 0.7 * va, (va, vb)
-
-
-def test_wide_closest_walk_equals_scan(rt, orc, scenes, monkeypatch):
-    """RAYTRACE_B200_BVH_WIDE=2: closest-hit queries over the wide nodes, nearest box first -- same object, same t,
-    ties and NaN rules included, as the linear scan"""
-    rng = np.random.default_rng(17)
-    for name, desc in _wide_scenes(rt, scenes):
-        rays = _rays(rng, 6000, 14.0, 8.0)
-        rays[:50, 3:] = 0.0                      # zero directions
-        rays[50:60, 0] = np.nan
-        rays[60:70, 4] = np.inf
-        monkeypatch.delenv("RAYTRACE_B200_BVH_WIDE", raising=False)
-        ids_s, t_s, _ = emu.trace_rays(emu.Scene(desc), rays, accel=rt.ACCEL_LINEAR)
-        monkeypatch.setenv("RAYTRACE_B200_BVH_WIDE", "2")
-        ids_w, t_w, _ = emu.trace_rays(emu.Scene(desc), rays, accel=rt.ACCEL_BVH)
-        assert np.array_equal(ids_w, ids_s), name
-        assert np.array_equal(t_w, t_s, equal_nan=True), name
-    monkeypatch.delenv("RAYTRACE_B200_BVH_WIDE")
-
-
-def test_wide_closest_walk_renders_the_oracle_frame(rt, orc, scenes, monkeypatch):
-    desc = scenes.random_spheres(1500, 0x5EED0003, 25.0, 96, 54)
-    ref = orc.OracleScene(desc).render(max_depth=6, seed=3)
-    monkeypatch.delenv("RAYTRACE_B200_BVH_WIDE", raising=False)
-    a = emu.render(emu.Scene(desc), max_depth=6, seed=3, accel=rt.ACCEL_BVH)
-    monkeypatch.setenv("RAYTRACE_B200_BVH_WIDE", "2")
-    b = emu.render(emu.Scene(desc), max_depth=6, seed=3, accel=rt.ACCEL_BVH)
-    check(b, ref, "spheres1500 wide closest")
-    va, vb = a["stats"]["bvh_nodes_visited"]["closest"], b["stats"]["bvh_nodes_visited"]["closest"]
-    assert 0.35 * va < vb < 0.75 * va, (va, vb)

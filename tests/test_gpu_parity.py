@@ -124,11 +124,10 @@ def test_intersect_far_origins(gpu, orc, scenes, accel):
 
 
 @pytest.mark.parametrize("nodes,morton", [("q16", "cubic"), ("f32", "cubic"), ("q16", "axis")])
-def test_bvh_node_formats_and_morton_grids(gpu, orc, scenes, nodes, morton, monkeypatch):
+def test_bvh_node_formats_and_morton_grids(gpu, orc, scenes, nodes, morton):
     """the 32-byte grid nodes, the 64-byte f32 nodes and either Morton scaling are only different conservative filters /
     different trees in front of the same exact test: ids, t, normals bit-identical, a whole frame byte-identical in ids"""
-    monkeypatch.setenv("RAYTRACE_B200_BVH_NODES", nodes)
-    monkeypatch.setenv("RAYTRACE_B200_MORTON", morton)
+    tune = (gpu.TUNE_NODES_Q16 if nodes == "q16" else gpu.TUNE_NODES_F32) | (gpu.TUNE_MORTON_AXIS if morton == "axis" else 0)
     desc = scenes.random_spheres(8000, 13, 50.0, 320, 200)
     sc = gpu.Scene(desc)
     rng = np.random.default_rng(9)
@@ -136,10 +135,10 @@ def test_bvh_node_formats_and_morton_grids(gpu, orc, scenes, nodes, morton, monk
     rays[:3000, 3:] = np.array([0.0, 0.0, 1.0]) * rng.choice([-1.0, 1.0], 3000)[:, None]   # axis-parallel: clamped reciprocals
     rays[3000:6000, 4] = 0.0
     rays[6000:7000, 3] = 1e-35
-    ids, t, nrm = gpu.raytrace.intersect(sc, rays, accel=gpu.ACCEL_BVH)
+    ids, t, nrm = gpu.raytrace.intersect(sc, rays, accel=gpu.ACCEL_BVH, tuning=tune)
     rid, rt_, rn = orc.OracleScene(desc).trace_rays(rays)
     assert np.array_equal(ids, rid) and np.array_equal(t, rt_) and np.array_equal(nrm, rn)
-    bvh = gpu.raytrace.render(sc, max_depth=4, seed=2, accel=gpu.ACCEL_BVH)
+    bvh = gpu.raytrace.render(sc, max_depth=4, seed=2, accel=gpu.ACCEL_BVH, tuning=tune)
     assert bvh.stats["bvh_node_bytes"] == (32 if nodes == "q16" else 64)
     lin = gpu.raytrace.render(sc, max_depth=4, seed=2, accel=gpu.ACCEL_LINEAR)
     assert np.array_equal(bvh.ids, lin.ids)
@@ -266,6 +265,72 @@ def test_queue_slicing_is_invisible(gpu, scenes):
     assert big.stats["rays_total"] == small.stats["rays_total"]
     assert (big.rows != small.rows).mean() < 1e-5
     assert small.stats["kernel_launches"] > big.stats["kernel_launches"]
+
+
+def test_device_driven_and_host_driven_frames_agree(gpu, orc, scenes):
+    """The default frame queues every launch without reading a count back (context.cu frame_device_driven); RT_TUNE_HOST_LEVELS
+    reads every level's count on the host.  Same rays, same frame.  A queue that overflows in the device-driven frame makes
+    the context redo it level by level (sliced): results unchanged, and the stats say so."""
+    desc = scenes.random_spheres(400, 21, 12.0, 160, 120, antialias=2)   # 10 % transparent spheres: levels branch a little
+    sc = gpu.Scene(desc)
+    ref = orc.OracleScene(desc).render(max_depth=6, seed=2)
+    dd = gpu.raytrace.render(sc, max_depth=6, seed=2)
+    hl = gpu.raytrace.render(sc, max_depth=6, seed=2, tuning=gpu.TUNE_HOST_LEVELS)
+    assert dd.stats["host_levels"] == 0 and dd.stats["device_driven_overflows"] == 0 and hl.stats["host_levels"] == 1
+    for fr in (dd, hl):
+        assert np.array_equal(fr.ids, ref["ids"])
+        assert fr.stats["rays_total"] == ref["stats"]["rays"]
+        for k in ("rays_primary", "rays_secondary", "rays_shadow", "paths"):
+            assert fr.stats[k] == hl.stats[k]
+    assert (dd.rows != hl.rows).mean() < 1e-5
+    # every hit of the showcase scene's IndirectPhong ball spawns three rays and its glass balls two: deep levels outgrow a
+    # queue sized for the paths, the optimistic frame overflows and is redone level by level
+    desc = scenes.materials_showcase(160, 120, 2)
+    sc = gpu.Scene(desc)
+    ref = orc.OracleScene(desc).render(max_depth=6, seed=2)
+    whole = gpu.raytrace.render(sc, max_depth=6, seed=2, tuning=gpu.TUNE_HOST_LEVELS)
+    ctx = gpu.Context(sc, max_depth=6, seed=2, max_rays_in_flight=2048)   # several primary batches, levels that outgrow the queue
+    first = ctx.render()
+    again = ctx.render()
+    assert first["device_driven_overflows"] == 1 and first["host_levels"] == 1
+    assert again["device_driven_overflows"] == 1 and again["host_levels"] == 1       # stays host-driven: no second wasted attempt
+    assert first["rays_total"] == again["rays_total"] == ref["stats"]["rays"]
+    rows, ids, _ = ctx.download(want_ids=True)
+    assert np.array_equal(ids[:120], ref["ids"]) and (rows[:120] != whole.rows).mean() < 1e-5
+    ctx.close()
+    # 16 samples per pixel in batches of 8192 paths, single-child materials: every batch device-driven, nothing overflows
+    desc2 = scenes.random_spheres(300, 7, 12.0, 64, 48, antialias=16, transparent=False)
+    ref2 = orc.OracleScene(desc2).render(max_depth=4, seed=5)
+    fr2 = gpu.raytrace.render(gpu.Scene(desc2), max_depth=4, seed=5, max_rays_in_flight=8192)
+    assert fr2.stats["host_levels"] == 0 and fr2.stats["rays_total"] == ref2["stats"]["rays"]
+    assert np.array_equal(fr2.ids, ref2["ids"])
+    d = np.abs(fr2.rows.astype(np.int16) - ref2["bgr"].astype(np.int16))
+    assert d.max() <= 1 and (d == 0).mean() >= 0.999
+
+
+def test_device_scene_stays_with_the_scene(gpu, scenes):
+    """rt_render builds a context per call; the device copy of the scene (buffers + BVH) is kept with the rt_scene per device
+    and reused until the scene changes (host_scene.h DeviceSceneSlot): the second call reports no BVH build"""
+    desc = scenes.random_spheres(5000, 3, 40.0, 96, 64)
+    sc = gpu.Scene(desc)
+    a = gpu.raytrace.render(sc, max_depth=3, seed=1, accel=gpu.ACCEL_BVH)
+    b = gpu.raytrace.render(sc, max_depth=3, seed=1, accel=gpu.ACCEL_BVH)
+    c = gpu.raytrace.render(sc, max_depth=3, seed=1, accel=gpu.ACCEL_BVH, tuning=gpu.TUNE_NODES_F32)   # another tree: built
+    d = gpu.raytrace.render(sc, max_depth=3, seed=1, accel=gpu.ACCEL_LINEAR)
+    assert a.stats["bvh_build_ms"] > 0 and b.stats["bvh_build_ms"] == 0 and c.stats["bvh_build_ms"] > 0 and d.stats["bvh_build_ms"] == 0
+    assert c.stats["bvh_node_bytes"] == 64 and a.stats["bvh_node_bytes"] == 32
+    for fr in (b, c, d):
+        assert np.array_equal(fr.ids, a.ids) and (fr.rows != a.rows).mean() < 1e-5
+    # camera and background are read per context (they do not drop the device copy)
+    import ctypes as C
+    L = gpu.lib()
+    assert L.rt_scene_set_background_solid(sc.handle, (C.c_double * 3)(1.0, 0.0, 0.0)) == 0
+    e = gpu.raytrace.render(sc, max_depth=3, seed=1, accel=gpu.ACCEL_BVH)
+    assert e.stats["bvh_build_ms"] == 0 and (e.rows != a.rows).mean() > 0.01
+    # a new light drops it
+    assert L.rt_scene_add_light_point(sc.handle, (C.c_double * 3)(0.0, 50.0, 0.0), (C.c_double * 3)(1.0, 1.0, 1.0)) == 0
+    f = gpu.raytrace.render(sc, max_depth=3, seed=1, accel=gpu.ACCEL_BVH)
+    assert f.stats["bvh_build_ms"] > 0 and f.stats["rays_shadow"] > e.stats["rays_shadow"]
 
 
 def test_scene_cache_follows_edits(gpu, scenes):
