@@ -2,20 +2,27 @@
 """bench.py -- measures the tracing hot path on N B200s of one node (contract: task prompt, section 4).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl ours|reference] [--fp strict|fast]
+                    [--gather peer|nccl] [--no-also] [--no-e2e] [--no-cpu-baseline]
 
-A step = one frame of the workload: primary-ray generation -> wavefront (closest-hit, shade, shadow kernels) ->
-resolve, on a device-resident scene (inputs already in HBM).  With N > 1 the frame is sharded by interleaved row
-bands (one process per GPU), every rank traces its bands, the quantised BGR bands are all-gathered over NCCL and
-de-interleaved into BMP row order: strong scaling of one frame.
+A step = one frame of the workload: primary-ray generation -> wavefront (closest-hit, shade, shadow kernels) -> resolve,
+on a device-resident scene (inputs already in HBM).  With N > 1 the frame is sharded by interleaved row bands, one process
+per GPU (torchrun); every rank traces its bands and its resolve kernel stores the quantised BGR rows straight into rank 0's
+whole-frame buffer over NVLink (CUDA IPC peer memory: the gather is fused into the kernel that produces the bytes).
+`--gather nccl` assembles the frame with an NCCL all-gather + de-interleave instead; at N > 1 the default line reports that
+variant beside the headline (`also.gather_nccl`).  Strong scaling of one frame.
 
-metric  Mrays/s, primary + secondary + shadow: 1 ray = one Scene::intersect call upstream (src/scene.rs:247),
-        counted exactly from the wavefront queue lengths.
-value   whole-job rays of K frames / device time of K frames (max over ranks).
-e2e     the same metric through the user-facing call with HOST buffers: host scene -> upload -> device BVH build ->
-        trace -> framebuffer copied back to host memory, every step.
+metric  Mrays/s, primary + secondary + shadow: 1 ray = one Scene::intersect call upstream (src/scene.rs:247), counted
+        exactly from the wavefront queue lengths.
+value   whole-job rays of K frames / device time of K frames (CUDA events on the launching stream, max over ranks); no
+        per-launch profiling events inside the timed region (kernel-class times come from a separate pass).
+e2e     the same metric through the user-facing call with HOST buffers, every step: the caller moves its spheres
+        (rt_scene_update_spheres from host memory) -> rt_render / rt_render_multi (flatten, upload, device BVH build on
+        every GPU, trace) -> frame in pinned host memory.  e2e_warm: the same call on an unchanged scene (the device copy
+        kept with the rt_scene is reused: nothing but the frame crosses PCIe).
+also    BASELINE config 4 (1M spheres, 7680x4320, the north_star scaling configuration) measured in the same run.
 
---impl reference times the CPU restatement of the reference (oracle/, kind "port": the upstream crate is Rust and
-cannot be built in this image) on the box's host cores on a bounded pixel sample of the same workload.
+--impl reference times the CPU restatement of the reference (oracle/, kind "port": the upstream crate is Rust and cannot
+be built in this image) on all host cores on a bounded pixel sample of the same workload.
 """
 import argparse
 import importlib
@@ -47,23 +54,29 @@ WORKLOADS = {
     "spheres-10k-4k-d8-linear": dict(gen="spheres_10k", gen_kw=dict(width=3840, height=2160), opts=dict(max_depth=8, seed=3), accel="linear"),
 }
 DEFAULT_WORKLOAD = "spheres-10k-4k-d8"
+ALSO_WORKLOAD = "spheres-1m-8k-d8"   # north_star's scaling configuration, carried by the default line
+METRIC = "Mrays/s (primary+secondary+shadow) at 4K"
+
+
+def host_threads():
+    """Host cores this process may use.  Never omp_get_max_threads(): torchrun exports OMP_NUM_THREADS=1."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+def pkg():
+    return importlib.import_module("rust-raytrace_b200")
 
 
 def make_desc(name):
+    """(description dict | None, scene text | None) of a workload; the generators live in the product package"""
     w = WORKLOADS[name]
-    if w["gen"] == "cornell":
-        sys.path.insert(0, os.path.join(ROOT, "tests"))
-        from test_gpu_parity import REF_TEXT_SCENE
-        return None, REF_TEXT_SCENE
     scenes = importlib.import_module("rust-raytrace_b200.scenes")
+    if w["gen"] == "cornell":
+        return None, scenes.TEST_SCENE_TEXT
     return getattr(scenes, w["gen"])(**w["gen_kw"]), None
-
-
-def frame_size(name, desc):
-    o = WORKLOADS[name]["opts"]
-    if desc is not None:
-        return o.get("width") or desc["options"]["width"], o.get("height") or desc["options"]["height"], o.get("antialias", desc["options"]["antialias"])
-    return o.get("width", 800), o.get("height", 800), o.get("antialias", 1024)   # test_scene.txt's own options block
 
 
 class ClockSampler:
@@ -121,7 +134,7 @@ def load_peaks():
 
 
 # ---------------------------------------------------------------------------------------------------------------------
-# CPU side: the oracle on a bounded pixel sample
+# CPU side: the oracle on a bounded pixel sample (test infrastructure; only these two legs may touch oracle/)
 # ---------------------------------------------------------------------------------------------------------------------
 def oracle_scene(name):
     from oracle import oracle as orc, scene_text
@@ -131,13 +144,18 @@ def oracle_scene(name):
     return orc.OracleScene(desc), desc
 
 
+def oracle_frame_size(name, desc):
+    o = WORKLOADS[name]["opts"]
+    return (o.get("width") or desc["options"]["width"], o.get("height") or desc["options"]["height"], o.get("antialias", desc["options"]["antialias"]))
+
+
 def sample_pixels(width, height, n, seed):
     rng = np.random.default_rng(seed)
     return rng.choice(width * height, size=min(n, width * height), replace=False).astype(np.uint32)
 
 
-def oracle_sample_rate(osc, name, desc, n_pixels, seed, threads=0):
-    w, h, aa = frame_size(name, desc)
+def oracle_sample_rate(osc, name, desc, n_pixels, seed, threads):
+    w, h, aa = oracle_frame_size(name, desc)
     o = WORKLOADS[name]["opts"]
     px = sample_pixels(w, h, n_pixels, seed)
     r = osc.render_pixels(px, width=w, height=h, antialias=aa, max_depth=o["max_depth"], seed=o["seed"], threads=threads)
@@ -147,97 +165,119 @@ def oracle_sample_rate(osc, name, desc, n_pixels, seed, threads=0):
 
 def cpu_baseline(name, budget_s=12.0):
     """Oracle ('port') on all host cores over a pixel sample sized to ~budget_s of CPU work."""
+    threads = host_threads()
     osc, desc = oracle_scene(name)
-    rays, sec, threads, npx = oracle_sample_rate(osc, name, desc, 256, 1234)
+    rays, sec, used, npx = oracle_sample_rate(osc, name, desc, 64 * threads, 1234, threads)
     per_px = max(sec, 1e-4) / npx
-    n = int(max(256, min(2_000_000, budget_s / per_px)))
-    rays, sec, threads, npx = oracle_sample_rate(osc, name, desc, n, 4321)
-    return {"value": rays / sec / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "port",
-            "sample": "%d pseudo-random pixels of the %s frame (%d rays, %.1f s), counter RNG, OpenMP over pixels" % (npx, name, rays, sec)}
+    n = int(max(64 * threads, min(2_000_000, budget_s / per_px)))
+    rays, sec, used, npx = oracle_sample_rate(osc, name, desc, n, 4321, threads)
+    return {"value": rays / sec / 1e6, "unit": "Mrays/s", "cores": used, "kind": "port",
+            "sample": "%d pseudo-random pixels of the %s frame (%d rays, %.1f s), counter RNG, OpenMP over pixels, linear scan as upstream" % (npx, name, rays, sec)}
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU algorithm (oracle port) on the host cores; rank 0 only."""
+    """--impl reference: the reference's CPU algorithm (oracle port) on all host cores; rank 0 only."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    threads = host_threads()
     name = args.workload
     osc, desc = oracle_scene(name)
-    rays, sec, threads, npx = oracle_sample_rate(osc, name, desc, 256, 99)
+    rays, sec, used, npx = oracle_sample_rate(osc, name, desc, 64 * threads, 99, threads)
     per_px = max(sec, 1e-4) / npx
     total_budget = 90.0
-    n = int(max(128, min(1_000_000, total_budget / (args.steps + args.warmup) / per_px)))
+    n = int(max(32 * threads, min(1_000_000, total_budget / (args.steps + args.warmup) / per_px)))
     for i in range(args.warmup):
-        oracle_sample_rate(osc, name, desc, n, 1000 + i)
+        oracle_sample_rate(osc, name, desc, n, 1000 + i, threads)
     tot_rays, tot_sec = 0, 0.0
     for i in range(args.steps):
-        rays, sec, threads, npx = oracle_sample_rate(osc, name, desc, n, 2000 + i)
+        rays, sec, used, npx = oracle_sample_rate(osc, name, desc, n, 2000 + i, threads)
         tot_rays += rays
         tot_sec += sec
     value = tot_rays / tot_sec / 1e6
-    w, h, aa = frame_size(name, desc)
-    sample = "%d pseudo-random pixels of the frame per step (%d rays per step), counter RNG, OpenMP over pixels" % (n, tot_rays // max(1, args.steps))
-    line = {"impl": "reference", "metric": "Mrays/s (primary+secondary+shadow) at 4K", "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
+    w, h, aa = oracle_frame_size(name, desc)
+    scene_mod = importlib.import_module("rust-raytrace_b200.scene")
+    sample = "%d pseudo-random pixels of the frame per step (%d rays per step), counter RNG, OpenMP over pixels, linear scan as upstream" % (
+        n, tot_rays // max(1, args.steps))
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot_sec / max(1, args.steps) * 1e3, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": workload_config(name, w, h, aa, desc),
-            "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": threads, "kind": "port", "sample": sample},
+            "config": workload_config(name, w, h, aa, scene_mod.count_objects(desc), len(desc["lights"])),
+            "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": used, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
 
-def workload_config(name, w, h, aa, desc):
-    scene_mod = importlib.import_module("rust-raytrace_b200.scene")
+def workload_config(name, w, h, aa, n_objects, n_lights):
     return {"workload": name, "width": w, "height": h, "antialias": aa, "max_depth": WORKLOADS[name]["opts"]["max_depth"],
-            "objects": scene_mod.count_objects(desc), "lights": len(desc["lights"]), "accel": WORKLOADS[name]["accel"],
+            "objects": int(n_objects), "lights": int(n_lights), "accel": WORKLOADS[name]["accel"],
             "l2_policy": "inputs larger than L2: per-frame ray queues + accumulators exceed 126 MB and are rewritten every step"}
 
 
 # ---------------------------------------------------------------------------------------------------------------------
 # GPU side
 # ---------------------------------------------------------------------------------------------------------------------
-def scene_h2d_bytes(desc):
-    """bytes the library uploads for this scene (flattened records; see DESIGN.md 'Data layout')"""
-    scene_mod = importlib.import_module("rust-raytrace_b200.scene")
-    n = scene_mod.count_objects(desc)
-    b = n * (32 + 4 + 4 + 4) + len(desc["materials"]) * 96 + len(desc["lights"]) * 104 + 511 * 8
-    if desc["background"]["type"] == "skybox":
+def scene_h2d_bytes(info, desc):
+    """bytes the library uploads per device for this scene (flattened records; see DESIGN.md 'Data layout')"""
+    b = info["n_objects"] * (4 + 4) + info["n_spheres"] * (32 + 4) + info["n_planes"] * 56 + info["n_materials"] * 96 + info["n_lights"] * 104 + 511 * 8
+    if desc is not None and desc["background"]["type"] == "skybox":
         b += sum(int(f.size) for f in desc["background"]["faces"])
     return int(b)
 
 
-def roofline_for(stats_sum, steps, peak_gbs, peak_src, accel):
-    """Dominant kernel class by measured device time; algorithmic bytes per SURVEY.md 8(d) / DESIGN.md."""
-    cls = max(stats_sum["class_ms"], key=lambda k: stats_sum["class_ms"][k])
-    ms = stats_sum["class_ms"][cls]
-    launches = max(1, stats_sum["class_launches"][cls])
+def roofline_for(prof, peak_gbs, peak_src, accel, hw):
+    """Dominant kernel class by measured device time (profiling pass); algorithmic bytes / flops per SURVEY.md 8(d) and
+    DESIGN.md.  BVH and shading kernels: compulsory queue-record bytes against the measured HBM copy peak, the L1/L2-served
+    tree bytes beside it against the measured L2 read bandwidth.  Linear-scan kernels: 25 flop per exact sphere test
+    (src/shapes.rs:60-65; device counter) + 14 per plane test against the measured FP64 FMA peak."""
+    steps = prof["steps"]
+    cls = max(prof["class_ms"], key=lambda k: prof["class_ms"][k])
+    ms = prof["class_ms"][cls]
+    launches = max(1, prof["class_launches"][cls])
     R_CLOSEST, H_CLOSEST = 48, 12          # origin+direction read, id+t written
     R_SHADOW = 84                          # origin, direction, range, pending colour, pixel read
     R_SHADE_IN, R_CHILD, R_SHADOW_OUT = 108, 96, 84
-    rays_c = stats_sum["rays_primary"] + stats_sum["rays_secondary"]
+    rays_c = prof["rays_primary"] + prof["rays_secondary"]
+    tree = 0
     if cls == "closest":
         queue = rays_c * (R_CLOSEST + H_CLOSEST)
-        tree = stats_sum["bvh_nodes"]["closest"] * stats_sum.get("node_bytes", 64) + stats_sum["bvh_prims"]["closest"] * 32
+        tree = prof["bvh_nodes"]["closest"] * prof["node_bytes"] + prof["bvh_prims"]["closest"] * 32
     elif cls == "shadow":
-        queue = stats_sum["rays_shadow"] * R_SHADOW
-        tree = stats_sum["bvh_nodes"]["shadow"] * stats_sum.get("node_bytes", 64) + stats_sum["bvh_prims"]["shadow"] * 32
+        queue = prof["rays_shadow"] * R_SHADOW
+        tree = prof["bvh_nodes"]["shadow"] * prof["shadow_node_bytes"] + prof["bvh_prims"]["shadow"] * 32
     elif cls == "shade":
-        queue = rays_c * R_SHADE_IN + stats_sum["rays_secondary"] * R_CHILD + stats_sum["rays_shadow"] * R_SHADOW_OUT
-        tree = 0
+        queue = rays_c * R_SHADE_IN + prof["rays_secondary"] * R_CHILD + prof["rays_shadow"] * R_SHADOW_OUT
     else:
-        queue, tree = 0, 0
-    achieved = queue / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
-    return {"bound": "hbm", "kernel": {"closest": "k_closest_bvh" if accel == "bvh" else "k_closest_scan",
-                                       "shadow": "k_shadow_bvh" if accel == "bvh" else "k_shadow_scan", "shade": "k_shade",
-                                       "primary": "k_primary", "resolve": "k_resolve"}[cls],
-            "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs, "traffic": None,
-            "peak_source": peak_src, "algorithmic_bytes_per_launch": queue / launches, "avg_launch_ms": ms / launches,
-            "share_of_step": ms / max(1e-9, sum(stats_sum["class_ms"].values())),
-            "class_ms_per_step": {k: v / steps for k, v in stats_sum["class_ms"].items()},
-            "tree_bytes_per_launch_L2": tree / launches, "bvh_node_bytes": stats_sum.get("node_bytes", 0),
-            "tree_gbs_L2": tree / (ms * 1e-3) / 1e9 if ms > 0 else 0.0,
-            "note": "achieved = compulsory queue-record bytes of the dominant kernel / its device time; BVH node+leaf fetches "
-                    "(tree_*) are served by L1/L2 and reported beside it"}
+        queue = 0
+    kernel = {"closest": "k_closest_bvh" if accel == "bvh" else "k_closest_scan", "shadow": "k_shadow_bvh" if accel == "bvh" else "k_shadow_scan",
+              "shade": "k_shade", "primary": "k_primary", "resolve": "k_resolve"}[cls]
+    sec = ms * 1e-3
+    out = {"kernel": kernel, "peak_source": peak_src, "avg_launch_ms": ms / launches, "launches_per_step": launches / steps,
+           "share_of_step": ms / max(1e-9, sum(prof["class_ms"].values())),
+           "class_ms_per_step": {k: v / steps for k, v in prof["class_ms"].items()},
+           "hbm_peak_gbs": peak_gbs, "fp64_peak_tflops": hw["fp64_tflops"], "fp32_peak_tflops": hw["fp32_tflops"], "l2_peak_gbs": hw["l2_read_gbs"],
+           "traffic": None}
+    if accel == "linear" and cls in ("closest", "shadow"):
+        n_planes = prof["n_planes"]
+        rays = rays_c if cls == "closest" else prof["rays_shadow"]
+        flops = 25.0 * prof["scan_tests"][cls] + 14.0 * n_planes * rays
+        achieved = flops / sec / 1e12 if sec > 0 else 0.0
+        out.update({"bound": "fp64", "achieved": achieved, "peak": hw["fp64_tflops"], "unit": "TFLOP/s", "frac": achieved / hw["fp64_tflops"],
+                    "frac_of_fp32_peak": achieved / hw["fp32_tflops"], "algorithmic_flops_per_launch": flops / launches,
+                    "sphere_tests_per_ray": prof["scan_tests"][cls] / max(1, rays),
+                    "note": "achieved = (25 flop x exact sphere tests counted on the device + 14 flop x plane tests) / device time of the scan "
+                            "kernel, against the FP64 FMA throughput measured in this run (rt_measure_peaks); tensor cores unused by design"})
+    else:
+        achieved = queue / sec / 1e9 if sec > 0 else 0.0
+        tree_gbs = tree / sec / 1e9 if sec > 0 else 0.0
+        out.update({"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
+                    "algorithmic_bytes_per_launch": queue / launches, "tree_bytes_per_launch_L2": tree / launches,
+                    "bvh_node_bytes": prof["shadow_node_bytes"] if cls == "shadow" else prof["node_bytes"], "tree_gbs_L2": tree_gbs,
+                    "tree_frac_of_l2_peak": tree_gbs / hw["l2_read_gbs"] if hw["l2_read_gbs"] else None,
+                    "note": "achieved = compulsory queue-record bytes of the dominant kernel / its device time against the measured HBM copy "
+                            "peak; BVH node + leaf fetches (tree_*) are served by L1/L2 and quoted against the L2 read bandwidth measured in "
+                            "this run (rt_measure_peaks).  The traversal is bound by instruction issue, not by either (profiles/)"})
+    return out
 
 
 def add_ncu_traffic(roof, workload, world):
@@ -251,173 +291,329 @@ def add_ncu_traffic(roof, workload, world):
         if world == 1 and t.get("workload") == workload and k:
             roof["traffic"] = k["dram_bytes_read"] + k["dram_bytes_write"]
             roof["traffic_source"] = k["source"]
-            # what the same capture says binds the kernel when it is not the HBM roofline
             roof["ncu"] = {m: k[m] for m in ("issue_slots_pct", "lanes_per_instruction", "l1_lsu_wavefronts_pct", "warps_active_pct") if m in k}
     except (OSError, ValueError, KeyError):
         pass
     return roof
 
 
-def run_ours(args):
-    import torch
-    import torch.distributed as dist
+class Dist:
+    """torch.distributed plumbing: one process per GPU, NCCL; trivial at world 1"""
 
-    rt = importlib.import_module("rust-raytrace_b200")
-    name = args.workload
+    def __init__(self, args):
+        import torch
+        self.torch = torch
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        if self.world != args.gpus:
+            raise SystemExit("--gpus %d but WORLD_SIZE=%d: launch N>1 with torchrun (one rank per GPU)" % (args.gpus, self.world))
+        torch.cuda.set_device(self.local_rank)
+        self.dist = None
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local_rank))
+            self.dist = dist
+            self.host_group = dist.new_group(backend="gloo")   # barriers that keep the waiting ranks' GPUs idle
+
+    def barrier(self):
+        if self.dist:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def host_barrier(self):
+        """Host-side barrier (gloo): an NCCL barrier parks a spinning kernel on every waiting rank's GPU, which would time-slice
+        with the work rank 0 runs on those GPUs during the end-to-end leg."""
+        self.torch.cuda.synchronize()
+        if self.dist:
+            self.dist.barrier(group=self.host_group)
+
+    def reduce(self, values, op):
+        t = self.torch.tensor([float(v) for v in values], dtype=self.torch.float64, device="cuda")
+        if self.dist:
+            self.dist.all_reduce(t, op=getattr(self.dist.ReduceOp, op))
+        return [float(x) for x in t]
+
+    def broadcast_bytes(self, arr, n):
+        t = self.torch.zeros(n, dtype=self.torch.uint8, device="cuda")
+        if self.rank == 0:
+            t.copy_(self.torch.from_numpy(np.ascontiguousarray(arr, dtype=np.uint8)))
+        if self.dist:
+            self.dist.broadcast(t, src=0)
+        return t.cpu().numpy()
+
+    def close(self):
+        if self.dist:
+            self.dist.barrier()
+            self.dist.destroy_process_group()
+
+
+def device_view(torch, ptr, nbytes):
+    class _H:
+        pass
+    h = _H()
+    h.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
+    return torch.as_tensor(h, device="cuda")
+
+
+def measure(name, args, D, steps, warmup, hw, want_e2e=True, want_cpu=True, gather="peer", want_nccl_variant=False):
+    """One workload on this process's GPU (shard `rank` of `world`): returns the JSON fields of a bench line."""
+    rt, torch = pkg(), D.torch
     wl = WORKLOADS[name]
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != args.gpus:
-        raise SystemExit("--gpus %d but WORLD_SIZE=%d: launch N>1 with torchrun (one rank per GPU)" % (args.gpus, world))
-    if rt.device_count() < 1:
-        raise SystemExit("no CUDA device visible: the product has no CPU path")
-    torch.cuda.set_device(local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-
+    world, rank = D.world, D.rank
     desc, text = make_desc(name)
-    if desc is None:
-        from oracle import scene_text  # only to describe the workload in `config`; the product parses the text itself
-        scene = rt.serialize.deserialize(text)
-        desc = scene_text.deserialize(text)
-    else:
-        scene = rt.Scene(desc)
-    w, h, aa = frame_size(name, desc)
+    scene = rt.serialize.deserialize(text) if desc is None else rt.Scene(desc)
+    info = scene.info()
+    sw, sh, saa = scene.options()
+    o = wl["opts"]
+    w, h, aa = o.get("width") or sw, o.get("height") or sh, o.get("antialias", saa)
     accel = rt.ACCEL_BVH if wl["accel"] == "bvh" else rt.ACCEL_LINEAR
     fp_mode = rt.FP_FAST if args.fp == "fast" else rt.FP_STRICT
-    opts = dict(wl["opts"], accel=accel, fp_mode=fp_mode, device=local_rank, rank=rank, world=world)
+    base_opts = dict(wl["opts"], accel=accel, fp_mode=fp_mode)
+    opts = dict(base_opts, device=D.local_rank, rank=rank, world=world)
     ctx = rt.Context(scene, **opts)
     stream = torch.cuda.current_stream()
     ctx.set_stream(stream.cuda_stream)
-    ctx.set_profiling(True)
-
-    fb_ptr, fb_bytes = ctx.framebuffer_ptr()
     bytewidth = ctx.bytewidth
-    final = torch.empty(h * bytewidth, dtype=torch.uint8, device="cuda")
-    gathered = torch.empty(world * fb_bytes, dtype=torch.uint8, device="cuda") if world > 1 else None
-    # zero-copy view of the context's device framebuffer for the NCCL gather
-    local_fb = None
-    if world > 1:
-        class _Holder:
-            pass
-        hold = _Holder()
-        hold.__cuda_array_interface__ = {"shape": (fb_bytes,), "typestr": "|u1", "data": (fb_ptr, False), "version": 2}
-        local_fb = torch.as_tensor(hold, device="cuda")
+    frame_bytes = h * bytewidth
+    fb_ptr, fb_bytes = ctx.framebuffer_ptr()
 
-    # N > 1: the gather of frame k runs on its own stream beside the trace of frame k+1 (the shard's bytes are first copied
-    # out of the context's framebuffer, which the next frame's resolve overwrites); frame k is assembled (untile) right
-    # after trace k+1.  drain() assembles the last frame: it is called before the timed region closes.
-    gather_stream = torch.cuda.Stream() if world > 1 else None
-    staging = torch.empty_like(local_fb) if world > 1 else None
-    ev_traced, ev_gathered = torch.cuda.Event(), torch.cuda.Event()
+    # ---- how the shards become one frame (N > 1)
+    frame0 = None         # rank 0: device view of the assembled frame
+    nccl = None
+    if world > 1 and gather == "peer":
+        handle = None
+        if rank == 0:
+            p = ctx.frame_create()
+            handle = ctx.frame_export()
+            frame0 = device_view(torch, p, frame_bytes)
+        handle = D.broadcast_bytes(handle, 64)
+        if rank != 0:
+            ctx.frame_import(handle)
+    elif world > 1:
+        nccl = dict(final=torch.empty(frame_bytes, dtype=torch.uint8, device="cuda"), gathered=torch.empty(world * fb_bytes, dtype=torch.uint8, device="cuda"),
+                    local=device_view(torch, fb_ptr, fb_bytes), stream=torch.cuda.Stream(), ev_traced=torch.cuda.Event(), ev_gathered=torch.cuda.Event(),
+                    pending=False)
+        nccl["staging"] = torch.empty_like(nccl["local"])
+        frame0 = nccl["final"]
+
+    # nccl: the gather of frame k runs on its own stream beside the trace of frame k+1 (the shard's bytes are first copied out
+    # of the context's framebuffer, which the next resolve overwrites); frame k is assembled right after trace k+1
+    def drain():
+        if nccl and nccl["pending"]:
+            stream.wait_event(nccl["ev_gathered"])
+            ctx.untile(nccl["gathered"].data_ptr(), nccl["final"].data_ptr())
+            nccl["pending"] = False
+
+    def step():
+        st = ctx.render()
+        if nccl:
+            drain()
+            nccl["staging"].copy_(nccl["local"])
+            nccl["ev_traced"].record(stream)
+            nccl["stream"].wait_event(nccl["ev_traced"])
+            with torch.cuda.stream(nccl["stream"]):
+                D.dist.all_gather_into_tensor(nccl["gathered"], nccl["staging"])
+                nccl["ev_gathered"].record(nccl["stream"])
+            nccl["pending"] = True
+        return st
+
+    for _ in range(max(3, warmup)):
+        step()
+    drain()
+    D.barrier()
+    sampler = ClockSampler(D.local_rank)
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    rays = launches = 0
+    host_levels = 0
+    D.barrier()
+    t0 = time.perf_counter()
+    ev0.record(stream)
+    for _ in range(steps):
+        st = step()
+        rays += st["rays_total"]
+        launches += st["kernel_launches"] + (1 if nccl else 0)
+        host_levels |= st["host_levels"]
+    drain()
+    ev1.record(stream)
+    D.barrier()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    dev_ms = ev0.elapsed_time(ev1)
+    clocks = sampler.stop() if rank == 0 else None
+    dev_ms, wall_ms = D.reduce([dev_ms, wall_ms], "MAX")
+    rays_all, launches_all = D.reduce([rays, launches], "SUM")
+
+    # ---- kernel-class times: a separate pass with one event pair per launch (not part of the headline timing)
+    ctx.set_profiling(True)
+    P = 3
+    prof = {"steps": P, "class_ms": {}, "class_launches": {}, "rays_primary": 0, "rays_secondary": 0, "rays_shadow": 0,
+            "bvh_nodes": {"closest": 0, "shadow": 0}, "bvh_prims": {"closest": 0, "shadow": 0}, "scan_tests": {"closest": 0, "shadow": 0},
+            "n_planes": info["n_planes"]}
+    for _ in range(P):
+        st = ctx.render()
+        for k in ("rays_primary", "rays_secondary", "rays_shadow"):
+            prof[k] += st[k]
+        for k, v in st["class_ms"].items():
+            prof["class_ms"][k] = prof["class_ms"].get(k, 0.0) + v
+            prof["class_launches"][k] = prof["class_launches"].get(k, 0) + st["class_launches"][k]
+        for k in ("closest", "shadow"):
+            prof["bvh_nodes"][k] += st["bvh_nodes_visited"][k]
+            prof["bvh_prims"][k] += st["bvh_prims_tested"][k]
+            prof["scan_tests"][k] += st["scan_sphere_tests"][k]
+        prof["node_bytes"] = st["bvh_node_bytes"]
+        prof["shadow_node_bytes"] = 64 if st["bvh_node_bytes"] == 32 else st["bvh_node_bytes"]   # four-wide nodes over the grid form
+    ctx.set_profiling(False)
+    D.barrier()
+
+    # ---- correctness of the assembled multi-GPU frame: rank 0 renders the whole frame on its own GPU and compares
+    frame_check = None
+    if world > 1:
+        ctx.render()
+        if nccl:
+            step(); drain()
+        D.barrier()
+        if rank == 0:
+            got = frame0.cpu().numpy().reshape(h, bytewidth)
+            one = rt.Context(scene, **dict(base_opts, device=D.local_rank))
+            one.render()
+            ref_rows, _, _ = one.download()
+            one.close()
+            ref_rows = ref_rows[:h]
+            d = np.abs(got.astype(np.int16) - ref_rows.astype(np.int16))
+            frame_check = {"max_lsb": int(d.max()), "identical": float((d == 0).mean()), "bytes": int(d.size),
+                           "against": "the same frame rendered by one GPU (rank 0, world 1) in this run; differences come from the order of "
+                                      "f64 atomic adds into a pixel only"}
+        D.barrier()
+
+    line = {"value": rays_all / (dev_ms * 1e-3) / 1e6, "ms_per_step": dev_ms / steps, "wall_ms_per_step": wall_ms / steps,
+            "rays_per_step": rays_all / steps, "gpu_launches": int(launches_all), "clocks": clocks, "steps": steps, "warmup": max(3, warmup),
+            "config": workload_config(name, w, h, aa, info["n_objects"], info["n_lights"]),
+            "bvh_build_ms": ctx.create_stats["bvh_build_ms"], "wavefront": "host-driven levels" if host_levels else "device-driven (no count read-backs)"}
+    if world > 1:
+        line["config"]["multi_gpu"] = ("image row bands (4 rows) interleaved over ranks, scene replicated; " +
+                                       ("every rank's resolve kernel stores its rows into rank 0's frame over NVLink (CUDA IPC peer memory)"
+                                        if gather == "peer" else "one NCCL all_gather of the BGR8 shards per frame, pipelined one frame deep with "
+                                        "the next frame's trace, then de-interleave"))
+        line["frame_check"] = frame_check
+    if rank == 0:
+        peak, peak_src = load_peaks()
+        line["roofline"] = add_ncu_traffic(roofline_for(prof, peak, peak_src, wl["accel"], hw), name, world)
+
+    # ---- NCCL variant of the gather, for the record (N > 1, default line only)
+    if want_nccl_variant and world > 1 and gather == "peer":
+        ctx.frame_set(0)
+        sub = measure_nccl_variant(ctx, D, steps, frame_bytes, fb_ptr, fb_bytes)
+        if rank == 0:
+            line["gather_nccl"] = sub
+
+    ctx.close()
+    del ctx
+
+    # ---- end to end through the user-facing call with host buffers
+    if want_e2e:
+        e2e = run_e2e(rt, D, scene, desc, info, base_opts, h, bytewidth, min(steps, 5))
+        if rank == 0:
+            line.update(e2e)
+    if want_cpu and world == 1 and rank == 0:
+        line["cpu_baseline"] = cpu_baseline(name)
+    return line
+
+
+def measure_nccl_variant(ctx, D, steps, frame_bytes, fb_ptr, fb_bytes):
+    torch = D.torch
+    stream = torch.cuda.current_stream()
+    final = torch.empty(frame_bytes, dtype=torch.uint8, device="cuda")
+    gathered = torch.empty(D.world * fb_bytes, dtype=torch.uint8, device="cuda")
+    local = device_view(torch, fb_ptr, fb_bytes)
+    staging = torch.empty_like(local)
+    side = torch.cuda.Stream()
+    ev_t, ev_g = torch.cuda.Event(), torch.cuda.Event()
     pending = [False]
 
     def drain():
         if pending[0]:
-            stream.wait_event(ev_gathered)
+            stream.wait_event(ev_g)
             ctx.untile(gathered.data_ptr(), final.data_ptr())
             pending[0] = False
 
     def step():
         st = ctx.render()
-        if world > 1:
-            drain()
-            staging.copy_(local_fb)
-            ev_traced.record(stream)
-            gather_stream.wait_event(ev_traced)
-            with torch.cuda.stream(gather_stream):
-                dist.all_gather_into_tensor(gathered, staging)
-                ev_gathered.record(gather_stream)
-            pending[0] = True
-        return st
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(max(3, args.warmup)):
-        step()
-    drain()
-    barrier()
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    acc = {"rays_total": 0, "rays_primary": 0, "rays_secondary": 0, "rays_shadow": 0, "kernel_launches": 0, "render_ms": 0.0,
-           "class_ms": {}, "class_launches": {}, "bvh_nodes": {"closest": 0, "shadow": 0}, "bvh_prims": {"closest": 0, "shadow": 0}}
-    barrier()
-    t0 = time.perf_counter()
-    ev0.record(stream)
-    for _ in range(args.steps):
-        st = step()
-        for k in ("rays_total", "rays_primary", "rays_secondary", "rays_shadow", "kernel_launches", "render_ms"):
-            acc[k] += st[k]
-        for k, v in st["class_ms"].items():
-            acc["class_ms"][k] = acc["class_ms"].get(k, 0.0) + v
-            acc["class_launches"][k] = acc["class_launches"].get(k, 0) + st["class_launches"][k]
-        acc["node_bytes"] = st["bvh_node_bytes"]
-        for k in ("closest", "shadow"):
-            acc["bvh_nodes"][k] += st["bvh_nodes_visited"][k]
-            acc["bvh_prims"][k] += st["bvh_prims_tested"][k]
-    drain()
-    ev1.record(stream)
-    barrier()
-    wall_ms = (time.perf_counter() - t0) * 1e3
-    dev_ms = ev0.elapsed_time(ev1)
-    clocks = sampler.stop() if rank == 0 else None
-    if world > 1:
-        acc["kernel_launches"] += args.steps  # k_untile, once per frame
-    return dict(rt=rt, torch=torch, dist=dist, scene=scene, desc=desc, ctx=ctx, acc=acc, dev_ms=dev_ms, wall_ms=wall_ms, clocks=clocks, world=world,
-                rank=rank, local_rank=local_rank, opts=opts, w=w, h=h, aa=aa, final=final, gathered=gathered, local_fb=local_fb, step=step,
-                barrier=barrier, bytewidth=bytewidth)
-
-
-def run_e2e(R, steps):
-    """End to end through the user-facing objects with HOST buffers: every step builds the device context from the host
-    scene (upload + device BVH build + queue allocation), traces, gathers (N > 1) and copies the frame to host memory."""
-    rt, torch, dist = R["rt"], R["torch"], R["dist"]
-    world, rank = R["world"], R["rank"]
-    h, bytewidth = R["h"], R["bytewidth"]
-    host = torch.empty(max(h * bytewidth, R["ctx"].framebuffer_ptr()[1]), dtype=torch.uint8).pin_memory()
-    rays = 0
-
-    def one():
-        ctx = rt.Context(R["scene"], **R["opts"])
-        st = ctx.render()
-        if world > 1:
-            ptr, nbytes = ctx.framebuffer_ptr()
-
-            class _H:
-                pass
-            hh = _H()
-            hh.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
-            dist.all_gather_into_tensor(R["gathered"], torch.as_tensor(hh, device="cuda"))
-            torch.cuda.synchronize()
-            ctx.untile(R["gathered"].data_ptr(), R["final"].data_ptr())
-            ctx.synchronize()
-            if rank == 0:
-                host.copy_(R["final"])
-        else:
-            ctx.download_rows_to(host.data_ptr())  # pinned host memory; local_rows == padded height at world 1
-        torch.cuda.synchronize()
-        ctx.close()
+        drain()
+        staging.copy_(local)
+        ev_t.record(stream)
+        side.wait_event(ev_t)
+        with torch.cuda.stream(side):
+            D.dist.all_gather_into_tensor(gathered, staging)
+            ev_g.record(side)
+        pending[0] = True
         return st["rays_total"]
 
-    one()
-    R["barrier"]()
-    t0 = time.perf_counter()
+    for _ in range(3):
+        step()
+    drain()
+    D.barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    rays = 0
+    ev0.record(stream)
     for _ in range(steps):
-        rays += one()
-    R["barrier"]()
-    sec = time.perf_counter() - t0
-    t = torch.tensor([sec, float(rays)], dtype=torch.float64, device="cuda")
-    if world > 1:
-        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        sec, rays = float(tmax[0]), float(tsum[1])
-    return rays / sec / 1e6, sec / steps * 1e3
+        rays += step()
+    drain()
+    ev1.record(stream)
+    D.barrier()
+    ms, = D.reduce([ev0.elapsed_time(ev1)], "MAX")
+    rays_all, = D.reduce([rays], "SUM")
+    return {"value": rays_all / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": ms / steps,
+            "what": "the same frames gathered with one NCCL all_gather_into_tensor per frame (side stream, one frame deep) + k_untile"}
+
+
+def run_e2e(rt, D, scene, desc, info, base_opts, h, bytewidth, steps):
+    """End to end through rt_render / rt_render_multi with HOST buffers.  N > 1: rank 0 drives all N GPUs through the library's
+    own multi-GPU call (one host thread per device inside the library), the other ranks idle at the barrier.
+    cold: the spheres are rewritten from host memory before every frame (flatten, upload, device BVH build per GPU, trace,
+          frame to pinned host memory);  warm: unchanged scene (the device copy kept with the rt_scene is reused)."""
+    torch = D.torch
+    world, rank = D.world, D.rank
+    out = {}
+    rt.release_cached_memory()   # the bench context's queues: rank 0 is about to allocate on every GPU
+    D.host_barrier()
+    if rank == 0:
+        host = torch.empty(h * bytewidth, dtype=torch.uint8).pin_memory()
+        spheres = None
+        if desc is not None:
+            first = 0
+            for ob in desc["objects"]:
+                if ob["shape"] == "spheres":
+                    spheres = (first, np.ascontiguousarray(ob["data"], dtype=np.float64))
+                    break
+                first += 1
+        devices = None if world == 1 else list(range(world))
+
+        def one(cold):
+            if cold and spheres is not None:
+                scene.update_spheres(spheres[0], spheres[1])
+            st = rt.raytrace.render_into(scene, host.data_ptr(), devices=devices, **dict(base_opts, device=D.local_rank))
+            return st["rays_total"]
+
+        for label, cold in (("e2e", True), ("e2e_warm", False)):
+            one(cold); one(cold)
+            rays = 0
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                rays += one(cold)
+            sec = time.perf_counter() - t0
+            per_dev = scene_h2d_bytes(info, desc) if (cold and spheres is not None) else 0
+            out[label] = {"value": rays / sec / 1e6, "unit": "Mrays/s", "ms_per_step": sec / steps * 1e3,
+                          "h2d_bytes_per_step": per_dev * world, "d2h_bytes_per_step": h * bytewidth,
+                          "what": ("caller rewrites the spheres from host memory (rt_scene_update_spheres) -> " if cold and spheres is not None else "unchanged scene -> ") +
+                                  ("rt_render" if world == 1 else "rt_render_multi (%d GPUs driven by one process, one thread per device, each device DMAs "
+                                   "its bands to the host frame)" % world) +
+                                  (": flatten, upload, device BVH build, trace, frame to pinned host memory" if cold and spheres is not None
+                                   else ": device copy of the scene reused, trace, frame to pinned host memory")}
+        rt.release_cached_memory()
+    D.host_barrier()
+    return out
 
 
 def main():
@@ -428,47 +624,38 @@ def main():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--fp", default="strict", choices=["strict", "fast"])
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-also", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
         return
-    R = run_ours(args)
-    torch, dist, world, rank, acc = R["torch"], R["dist"], R["world"], R["rank"], R["acc"]
-    t = torch.tensor([R["dev_ms"], R["wall_ms"]], dtype=torch.float64, device="cuda")
-    tot = torch.tensor([float(acc["rays_total"]), float(acc["kernel_launches"])], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
-    dev_ms, wall_ms = float(t[0]), float(t[1])
-    rays_all, launches_all = float(tot[0]), int(tot[1])
-    e2e_val, e2e_ms = (None, None)
-    if not args.no_e2e:
-        e2e_val, e2e_ms = run_e2e(R, min(args.steps, 5))
-    if rank == 0:
-        peak, peak_src = load_peaks()
-        name = args.workload
-        line = {"metric": "Mrays/s (primary+secondary+shadow) at 4K", "value": rays_all / (dev_ms * 1e-3) / 1e6, "unit": "Mrays/s",
-                "n_gpus": args.gpus, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": dev_ms / args.steps,
-                "wall_ms_per_step": wall_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-                "dtype": "f64", "fp_mode": args.fp, "data": "synthetic", "config": workload_config(name, R["w"], R["h"], R["aa"], R["desc"]),
-                "rays_per_step": rays_all / args.steps, "gpu_launches": launches_all, "clocks": R["clocks"],
-                "roofline": add_ncu_traffic(roofline_for(acc, args.steps, peak, peak_src, WORKLOADS[name]["accel"]), name, world),
-                "bvh_build_ms": R["ctx"].create_stats["bvh_build_ms"]}
-        if world > 1:
-            line["config"]["multi_gpu"] = ("image row bands (4 rows) interleaved over ranks, scene replicated; one NCCL all_gather of the "
-                                           "BGR8 shards per frame, pipelined one frame deep with the next frame's trace, then untile")
-        if e2e_val is not None:
-            line["e2e"] = {"value": e2e_val, "unit": "Mrays/s", "ms_per_step": e2e_ms, "h2d_bytes_per_step": scene_h2d_bytes(R["desc"]),
-                           "d2h_bytes_per_step": R["h"] * R["bytewidth"],
-                           "what": "host scene -> rt_context_create (upload, device BVH build, queues) -> render -> gather -> frame in host memory"}
-        if args.gpus == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline(name)
+    rt = pkg()
+    if rt.device_count() < 1:
+        raise SystemExit("no CUDA device visible: the product has no CPU path")
+    D = Dist(args)
+    hw = rt.measure_peaks(D.local_rank)
+    m = measure(args.workload, args, D, args.steps, args.warmup, hw, want_e2e=not args.no_e2e, want_cpu=not args.no_cpu_baseline,
+                gather=args.gather, want_nccl_variant=(args.workload == DEFAULT_WORKLOAD))
+    also = None
+    if not args.no_also and args.workload == DEFAULT_WORKLOAD:
+        a = measure(ALSO_WORKLOAD, args, D, min(args.steps, 5), 3, hw, want_e2e=not args.no_e2e, want_cpu=not args.no_cpu_baseline, gather=args.gather)
+        if D.rank == 0:
+            a.update({"metric": "Mrays/s (primary+secondary+shadow) at 8K", "unit": "Mrays/s", "n_gpus": args.gpus})
+            also = {ALSO_WORKLOAD: a}
+    if D.rank == 0:
+        line = {"metric": METRIC, "value": m.pop("value"), "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": max(3, args.warmup),
+                "ms_per_step": m.pop("ms_per_step"), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+                "fp_mode": args.fp, "data": "synthetic"}
+        m.pop("steps", None); m.pop("warmup", None)
+        line.update(m)
+        line["host_threads"] = host_threads()
+        if also:
+            line["also"] = also
         print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+    D.close()
 
 
 if __name__ == "__main__":

@@ -76,6 +76,10 @@ RT_API int rt_scene_add_material_transparent(rt_scene*, const double specular[3]
  * `Scene.objects`; it is the id reported for primary hits and the tie-break of the closest-hit search. */
 RT_API int rt_scene_add_spheres(rt_scene*, uint64_t n, const double* center_xyz_radius /* 4n */, const uint32_t* material /* n */);
 RT_API int rt_scene_add_plane(rt_scene*, const double point[3], const double normal[3], uint32_t material);
+/* `scene.objects[i].bounds = Box::new(Sphere { .. })` for n consecutive sphere objects starting at object index
+ * first_object (upstream's fields are pub: src/scene.rs:93-98, src/shapes.rs:43-48): an animation moves its spheres
+ * between frames.  Materials and object order stay; the next context re-uploads the scene and rebuilds the BVH. */
+RT_API int rt_scene_update_spheres(rt_scene*, uint64_t first_object, uint64_t n, const double* center_xyz_radius /* 4n */);
 
 /* lights (src/scene.rs:109-155) */
 RT_API int rt_scene_add_light_point(rt_scene*, const double location[3], const double color[3]);
@@ -170,6 +174,9 @@ typedef struct rt_stats {
     /* 1: the last frame was driven level by level from the host (RT_TUNE_HOST_LEVELS, or a queue overflowed in the
      * device-driven frame, which is then redone); device_driven_overflows counts those redone frames of this context */
     uint32_t host_levels, device_driven_overflows;
+    /* exact sphere tests made by the linear-scan kernels ([0] closest-hit, [1] shadow: a shadow query stops at its first
+     * occluder); with 25 flop per test (src/shapes.rs:60-65) the FP64 work their roofline fraction is computed from */
+    uint64_t scan_sphere_tests[2];
 } rt_stats;
 
 /* One-call frame render: upload, (build BVH), trace, resolve, copy back.
@@ -202,6 +209,20 @@ RT_API int rt_context_download(rt_context*, uint8_t* bgr_rows, int32_t* primary_
  * writes the final bytewidth*height image in BMP row order into `out_dev`.  Runs on the context's device/stream. */
 RT_API int rt_context_untile(rt_context*, const void* gathered_dev, void* out_dev);
 RT_API int rt_context_synchronize(rt_context*);
+/* Whole-frame output.  By default a context resolves into its own shard-sized framebuffer (local row order).  With a frame
+ * set, k_resolve stores every row of the shard at its place in a whole-frame buffer (bytewidth*height bytes, BMP row
+ * order) instead -- the gather of a sharded frame then IS the resolve kernel's stores, over NVLink when the buffer lives
+ * on another GPU.  One process per GPU (torchrun): rank 0 creates the frame and exports it, the others import the handle:
+ *   rt_context_frame_create   allocate the frame on this context's device and resolve into it; *dev_ptr = its address
+ *   rt_context_frame_export   64-byte CUDA IPC handle of the frame created above
+ *   rt_context_frame_import   open another process's frame (peer access is enabled by the driver) and resolve into it
+ *   rt_context_frame_set      resolve into any device address this GPU can store to (own or peer memory of this
+ *                             process); NULL = back to the context's own framebuffer
+ * A frame is complete when every shard's rt_context_render has returned (the caller synchronises the ranks). */
+RT_API int rt_context_frame_create(rt_context*, void** dev_ptr);
+RT_API int rt_context_frame_export(rt_context*, uint8_t handle64[64]);
+RT_API int rt_context_frame_import(rt_context*, const uint8_t handle64[64]);
+RT_API int rt_context_frame_set(rt_context*, void* dev_ptr);
 /* run on a caller-owned CUDA stream (a cudaStream_t / CUstream handle, e.g. torch's current stream) instead of the
  * context's own; pass NULL to go back.  The caller keeps the stream alive for as long as it is set. */
 RT_API int rt_context_set_stream(rt_context*, void* cuda_stream);
@@ -248,6 +269,18 @@ RT_API int rt_trace_rays(const rt_scene*, const rt_render_opts*, uint64_t n, con
 RT_API int rt_project(const rt_scene*, const rt_render_opts*, uint64_t n, const double* pos_xy, double* origin_dir);
 /* Color::write_bgr over n colours (src/color.rs:593-600, :628-632), on the device */
 RT_API int rt_quantize_bgr(const double* rgb, uint64_t n, uint8_t* bgr, int device);
+
+/* Roofline denominators MEASURED_PEAKS.json does not carry, measured on `device` with register-resident
+ * FMA chains and an L2-resident read loop (~50 ms): the FP64 pipe bounds the linear-scan kernels, L2 serves the BVH
+ * kernels' node and leaf fetches.  A measurement hook: nothing on the tracing path uses it. */
+typedef struct rt_peaks {
+    double fp64_tflops;   /* DFMA, 2 flop each */
+    double fp32_tflops;   /* FFMA */
+    double l2_read_gbs;   /* ld.global.cg over a buffer of l2_buffer_bytes (a quarter of the L2) */
+    uint64_t l2_buffer_bytes;
+    int32_t sm_count, _pad;
+} rt_peaks;
+RT_API int rt_measure_peaks(int device, rt_peaks* out);
 
 /* ---------------------------------------------------------------------------------------------------------
  * BMP sink  (src/bmp.rs:10-61 + the row writes of src/main.rs:42,58)

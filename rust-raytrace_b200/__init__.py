@@ -51,6 +51,14 @@ def release_cached_memory():
     lib().rt_release_cached_memory()
 
 
+def measure_peaks(device=0):
+    """FP64 / FP32 FMA throughput and L2 read bandwidth of `device`, measured now (rt_measure_peaks)."""
+    p = B.Peaks()
+    B.check(lib(), lib().rt_measure_peaks(device, C.byref(p)))
+    return {"fp64_tflops": p.fp64_tflops, "fp32_tflops": p.fp32_tflops, "l2_read_gbs": p.l2_read_gbs, "l2_buffer_bytes": int(p.l2_buffer_bytes),
+            "sm_count": int(p.sm_count)}
+
+
 def version():
     return lib().rt_version().decode()
 
@@ -137,6 +145,27 @@ class Context:
 
     def synchronize(self):
         B.check(self._lib, self._lib.rt_context_synchronize(self._h))
+
+    def frame_create(self):
+        """Whole-frame buffer on this context's device; this context now resolves its rows into it.  Returns its address."""
+        p = C.c_void_p()
+        B.check(self._lib, self._lib.rt_context_frame_create(self._h, C.byref(p)))
+        return int(p.value)
+
+    def frame_export(self):
+        """64-byte CUDA IPC handle of the frame (for the other ranks' frame_import)."""
+        h = np.zeros(64, dtype=np.uint8)
+        B.check(self._lib, self._lib.rt_context_frame_export(self._h, B.ptr(h, C.c_uint8)))
+        return h
+
+    def frame_import(self, handle):
+        """Resolve into another process's frame (rank 0's): the gather becomes this GPU's own stores over NVLink."""
+        h = np.ascontiguousarray(handle, dtype=np.uint8)
+        assert h.size == 64
+        B.check(self._lib, self._lib.rt_context_frame_import(self._h, B.ptr(h, C.c_uint8)))
+
+    def frame_set(self, dev_ptr):
+        B.check(self._lib, self._lib.rt_context_frame_set(self._h, C.c_void_p(dev_ptr or 0)))
 
     def set_stream(self, cuda_stream):
         """Run on a caller-owned stream (int handle, e.g. torch.cuda.current_stream().cuda_stream); None = own stream."""
@@ -229,6 +258,21 @@ class _Raytrace:
         st = Stats()
         B.check(L, L.rt_render(scene.handle, C.byref(o), B.ptr(rows, C.c_uint8), B.ptr(ids, C.c_int32), B.ptr(acc, C.c_double), C.byref(st)))
         return Frame(width, height, rows, ids, acc, st.as_dict())
+
+    @staticmethod
+    def render_into(scene, host_ptr, devices=None, gather=GATHER_AUTO, **opts):
+        """rt_render / rt_render_multi with the BGR rows going to caller-owned host memory (bytewidth*height bytes at
+        `host_ptr`, e.g. a pinned buffer).  Returns the stats."""
+        L = lib()
+        o = B.make_opts(L, **opts)
+        st = Stats()
+        dst = C.cast(C.c_void_p(host_ptr), C.POINTER(C.c_uint8))
+        if devices is None:
+            B.check(L, L.rt_render(scene.handle, C.byref(o), dst, None, None, C.byref(st)))
+        else:
+            devs = list(range(devices)) if isinstance(devices, int) else list(devices)
+            B.check(L, L.rt_render_multi(scene.handle, C.byref(o), len(devs), (C.c_int * len(devs))(*devs), int(gather), dst, None, C.byref(st)))
+        return st.as_dict()
 
     @staticmethod
     def render_multi(scene, devices, gather=GATHER_AUTO, want_ids=True, **opts):

@@ -28,18 +28,24 @@ class Stats(C.Structure):
                 ("n_bvh_nodes", C.c_uint64), ("local_rows", C.c_uint32), ("bytewidth", C.c_uint32), ("accel_used", C.c_int32),
                 ("fp_mode_used", C.c_int32), ("bvh_nodes_visited", C.c_uint64 * 2), ("bvh_prims_tested", C.c_uint64 * 2),
                 ("class_ms", C.c_double * 5), ("class_launches", C.c_uint64 * 5), ("heavy_rays", C.c_uint64 * 2), ("bvh_node_bytes", C.c_uint64),
-                ("host_levels", C.c_uint32), ("device_driven_overflows", C.c_uint32)]
+                ("host_levels", C.c_uint32), ("device_driven_overflows", C.c_uint32), ("scan_sphere_tests", C.c_uint64 * 2)]
 
     CLASSES = ("primary", "closest", "shade", "shadow", "resolve")
 
     def as_dict(self):
-        d = {k: getattr(self, k) for k, _ in self._fields_ if not k.startswith(("class_", "bvh_nodes_", "bvh_prims_", "heavy_"))}
+        d = {k: getattr(self, k) for k, _ in self._fields_ if not k.startswith(("class_", "bvh_nodes_", "bvh_prims_", "heavy_", "scan_"))}
+        d["scan_sphere_tests"] = {"closest": int(self.scan_sphere_tests[0]), "shadow": int(self.scan_sphere_tests[1])}
         d["heavy_rays"] = {"closest": int(self.heavy_rays[0]), "shadow": int(self.heavy_rays[1])}
         d["bvh_nodes_visited"] = {"closest": int(self.bvh_nodes_visited[0]), "shadow": int(self.bvh_nodes_visited[1])}
         d["bvh_prims_tested"] = {"closest": int(self.bvh_prims_tested[0]), "shadow": int(self.bvh_prims_tested[1])}
         d["class_ms"] = dict(zip(self.CLASSES, [float(x) for x in self.class_ms]))
         d["class_launches"] = dict(zip(self.CLASSES, [int(x) for x in self.class_launches]))
         return d
+
+
+class Peaks(C.Structure):
+    _fields_ = [("fp64_tflops", C.c_double), ("fp32_tflops", C.c_double), ("l2_read_gbs", C.c_double), ("l2_buffer_bytes", C.c_uint64),
+                ("sm_count", C.c_int32), ("_pad", C.c_int32)]
 
 
 class SceneInfo(C.Structure):
@@ -79,6 +85,7 @@ API = {
     "rt_scene_add_material_transparent": (C.c_int, [C.c_void_p, _dp, C.c_double, C.c_double]),
     "rt_scene_add_spheres": (C.c_int, [C.c_void_p, C.c_uint64, _dp, _u32p]),
     "rt_scene_add_plane": (C.c_int, [C.c_void_p, _dp, _dp, C.c_uint32]),
+    "rt_scene_update_spheres": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, _dp]),
     "rt_scene_add_light_point": (C.c_int, [C.c_void_p, _dp, _dp]),
     "rt_scene_add_light_directional": (C.c_int, [C.c_void_p, _dp, _dp]),
     "rt_scene_add_light_area": (C.c_int, [C.c_void_p, _dp, _dp, _dp, _dp]),
@@ -104,6 +111,10 @@ API = {
     "rt_context_download": (C.c_int, [C.c_void_p, _u8p, _i32p, _dp]),
     "rt_context_untile": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "rt_context_synchronize": (C.c_int, [C.c_void_p]),
+    "rt_context_frame_create": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "rt_context_frame_export": (C.c_int, [C.c_void_p, _u8p]),
+    "rt_context_frame_import": (C.c_int, [C.c_void_p, _u8p]),
+    "rt_context_frame_set": (C.c_int, [C.c_void_p, C.c_void_p]),
     "rt_context_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "rt_context_set_profiling": (C.c_int, [C.c_void_p, C.c_int]),
     "rt_multi_create": (C.c_int, [C.c_void_p, C.POINTER(RenderOpts), C.c_int, C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_void_p)]),
@@ -116,6 +127,7 @@ API = {
     "rt_trace_rays": (C.c_int, [C.c_void_p, C.POINTER(RenderOpts), C.c_uint64, _dp, _i32p, _dp, _dp]),
     "rt_project": (C.c_int, [C.c_void_p, C.POINTER(RenderOpts), C.c_uint64, _dp, _dp]),
     "rt_quantize_bgr": (C.c_int, [_dp, C.c_uint64, _u8p, C.c_int]),
+    "rt_measure_peaks": (C.c_int, [C.c_int, C.POINTER(Peaks)]),
     "rt_bmp_bytewidth": (C.c_uint32, [C.c_uint32]),
     "rt_bmp_header": (None, [C.c_uint32, C.c_uint32, _u8p]),
     "rt_bmp_write": (C.c_int, [C.c_char_p, C.c_uint32, C.c_uint32, _u8p]),
@@ -261,6 +273,11 @@ class Scene:
         o = desc.get("options")
         if o is not None:
             check(L, L.rt_scene_set_options(h, int(o["width"]), int(o["height"]), int(o["antialias"])))
+
+    def update_spheres(self, first_object, center_xyz_radius):
+        """Moves / resizes consecutive sphere objects (an animation step): rt_scene_update_spheres."""
+        a = np.ascontiguousarray(center_xyz_radius, dtype=np.float64).reshape(-1, 4)
+        check(self._lib, self._lib.rt_scene_update_spheres(self._h, int(first_object), a.shape[0], ptr(a, C.c_double)))
 
     # -- introspection ---------------------------------------------------------------------------------
     def options(self):

@@ -66,6 +66,7 @@ def build(force=False, verbose=False):
         ("kernels_fast.o", "kernels.cu", [nvcc] + NVCC_COMMON + ["-DRT_NS=fast", "-fmad=true"]),
         ("bvh_build.o", "bvh_build.cu", [nvcc] + NVCC_COMMON + ["-fmad=false"]),
         ("context.o", "context.cu", [nvcc] + NVCC_COMMON),
+        ("peaks.o", "peaks.cu", [nvcc] + NVCC_COMMON + ["-fmad=true"]),
         ("host_scene.o", "host_scene.cpp", ["g++"] + HOST_FLAGS),
         ("serialize.o", "serialize.cpp", ["g++"] + HOST_FLAGS),
     ]

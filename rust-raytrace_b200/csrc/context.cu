@@ -12,6 +12,7 @@
 #include <dlfcn.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <condition_variable>
@@ -193,6 +194,9 @@ struct DeviceSceneHolder {
     double bvh_ms = 0.0;
     uint32_t build_launches = 0;
     int device = 0;
+    // a device-driven frame of this scene overflowed a queue: later contexts (rt_render makes one per frame) go level by
+    // level from the start instead of paying for the failed attempt again
+    std::atomic<bool> dd_overflowed{false};
 
     ~DeviceSceneHolder() { release(); }
     void release() {
@@ -376,6 +380,8 @@ struct rt_context {
     uint8_t* framebuffer = nullptr;
     size_t fb_bytes = 0;
     uint8_t* final_out = nullptr;  // non-null: k_resolve writes BMP-ordered rows of the whole frame here (rt_multi peer gather)
+    uint8_t* frame_own = nullptr;  // rt_context_frame_create
+    void* frame_ipc = nullptr;     // rt_context_frame_import
     uint32_t slice = 0;
     uint32_t shadow_queued = 0;  // shadow rays appended since the last trace of the shadow queue
     uint64_t total_paths = 0;
@@ -404,6 +410,8 @@ struct rt_context {
         cudaSetDevice(device);
         if (stream) cudaStreamSynchronize(stream);  // blocks go back to the cache: nothing may still be using them
         for (void* p : allocs) g_cache.release(p);
+        if (frame_own) cudaFree(frame_own);  // exported to other processes: not recycled through the cache
+        if (frame_ipc) cudaIpcCloseMemHandle(frame_ipc);
         g_pinned.put(counters_host, n_host_slots);
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
@@ -547,12 +555,15 @@ int frame_device_driven(rt_context* c, bool* overflowed) {
     const uint32_t n_levels = (uint32_t)c->levels.size();
     const uint64_t cap = c->levels[0].cap;
     const uint64_t branch = (uint64_t)std::max(1, c->ds.max_children);
+    // primary batches of cap / branch paths: level 1 then fits whatever the materials do; deeper levels fit unless the
+    // tree of rays keeps growing (it decays in every scene measured), in which case the frame is redone level by level
+    const uint64_t batch = std::max<uint64_t>(cap / branch, 32);
     // what a batch resets: shadow_count, level_count[], lc[] (contiguous in Counters)
     char* batch_state = reinterpret_cast<char*>(&c->counters->shadow_count);
     const size_t batch_state_bytes = sizeof(Counters) - offsetof(Counters, shadow_count);
     size_t slot = 0;
-    for (uint64_t base = 0; base < c->total_paths; base += cap, slot++) {
-        const uint32_t n = (uint32_t)std::min<uint64_t>(cap, c->total_paths - base);
+    for (uint64_t base = 0; base < c->total_paths; base += batch, slot++) {
+        const uint32_t n = (uint32_t)std::min<uint64_t>(batch, c->total_paths - base);
         if (base) CUDA_TRY(cudaMemsetAsync(batch_state, 0, batch_state_bytes, c->stream));
         c->prof_begin(0);
         c->k->primary(c->stream, c->ds, c->fp, c->levels[0], &c->counters->level_count[0], &c->counters->overflow, base, n);
@@ -638,7 +649,7 @@ int rt_context_create(const rt_scene* s, const rt_render_opts* o, rt_context** o
     c->ds.bg_kind = s->bg_kind;
     std::memcpy(c->ds.bg_color, s->bg_color, sizeof c->ds.bg_color);
     c->use_bvh = c->scene->use_bvh;
-    c->host_levels = (o->tuning & RT_TUNE_HOST_LEVELS) != 0;
+    c->host_levels = (o->tuning & RT_TUNE_HOST_LEVELS) != 0 || c->scene->dd_overflowed.load();
 
     FrameParams& fp = c->fp;
     if ((rc = make_frame_params(s, o, &fp)) != RT_OK) return fail(rc);
@@ -681,7 +692,8 @@ int rt_context_create(const rt_scene* s, const rt_render_opts* o, rt_context** o
         // the split-scan scratch behind the list must start zeroed; its users leave it zeroed (k_heavy_scan)
         if (cudaMemsetAsync(c->heavy + HEAVY_CAP, 0, sizeof(HeavyScratch), c->stream) != cudaSuccess) { set_error("cudaMemsetAsync failed"); return fail(RT_ERR_CUDA); }
     }
-    if (g_pinned.get(&c->counters_host, &c->n_host_slots, (size_t)((c->total_paths + cap - 1) / cap) + 1) != cudaSuccess) { set_error("cudaMallocHost failed"); return fail(RT_ERR_CUDA); }
+    const uint64_t dd_batch = std::max<uint64_t>(cap / branch, 32);
+    if (g_pinned.get(&c->counters_host, &c->n_host_slots, (size_t)((c->total_paths + dd_batch - 1) / dd_batch) + 1) != cudaSuccess) { set_error("cudaMallocHost failed"); return fail(RT_ERR_CUDA); }
     if (cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_counts, cudaEventDisableTiming) != cudaSuccess) { set_error("cudaEventCreate failed"); return fail(RT_ERR_CUDA); }
     std::memset(&c->stats, 0, sizeof c->stats);
@@ -711,8 +723,9 @@ int rt_context_render(rt_context* c, rt_stats* stats) {
     if (!c->host_levels) {
         rc = frame_device_driven(c, &redo);
         if (rc != RT_OK) return rc;
-        if (redo) {  // a queue overflowed: this context goes level by level from now on
+        if (redo) {  // a queue overflowed: this context (and later ones of this scene) go level by level from now on
             c->host_levels = true;
+            c->scene->dd_overflowed.store(true);
             c->stats.device_driven_overflows += 1;
             if ((rc = frame_begin(c)) != RT_OK) return rc;
         }
@@ -733,6 +746,7 @@ int rt_context_render(rt_context* c, rt_stats* stats) {
         c->stats.bvh_nodes_visited[k] = c->counters_host->bvh_nodes[k];
         c->stats.bvh_prims_tested[k] = c->counters_host->bvh_prims[k];
         c->stats.heavy_rays[k] = c->counters_host->heavy_rays[k];
+        c->stats.scan_sphere_tests[k] = c->counters_host->scan_tests[k];
     }
     for (int k = 0; k < 5; k++) { c->stats.class_ms[k] = 0.0; c->stats.class_launches[k] = 0; }
     for (size_t i = 0; i < c->prof_class.size(); i++) {
@@ -792,6 +806,46 @@ int rt_context_set_stream(rt_context* c, void* cuda_stream) {
 int rt_context_set_profiling(rt_context* c, int on) {
     if (!c) { set_error("null context"); return RT_ERR_INVALID; }
     c->profiling = on != 0;
+    return RT_OK;
+}
+
+int rt_context_frame_create(rt_context* c, void** dev_ptr) {
+    if (!c) { set_error("null context"); return RT_ERR_INVALID; }
+    CUDA_TRY(cudaSetDevice(c->device));
+    if (!c->frame_own) {
+        CUDA_TRY(cudaMalloc((void**)&c->frame_own, (size_t)c->bytewidth * c->fp.height + 16));
+        CUDA_TRY(cudaMemset(c->frame_own, 0, (size_t)c->bytewidth * c->fp.height + 16));
+    }
+    c->final_out = c->frame_own;
+    if (dev_ptr) *dev_ptr = c->frame_own;
+    return RT_OK;
+}
+
+int rt_context_frame_export(rt_context* c, uint8_t* handle64) {
+    if (!c || !handle64) { set_error("null argument"); return RT_ERR_INVALID; }
+    if (!c->frame_own) { set_error("rt_context_frame_export: no frame (call rt_context_frame_create first)"); return RT_ERR_INVALID; }
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handles are 64 bytes");
+    CUDA_TRY(cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    CUDA_TRY(cudaIpcGetMemHandle(&h, c->frame_own));
+    std::memcpy(handle64, &h, 64);
+    return RT_OK;
+}
+
+int rt_context_frame_import(rt_context* c, const uint8_t* handle64) {
+    if (!c || !handle64) { set_error("null argument"); return RT_ERR_INVALID; }
+    CUDA_TRY(cudaSetDevice(c->device));
+    if (c->frame_ipc) { CUDA_TRY(cudaIpcCloseMemHandle(c->frame_ipc)); c->frame_ipc = nullptr; }
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle64, 64);
+    CUDA_TRY(cudaIpcOpenMemHandle(&c->frame_ipc, h, cudaIpcMemLazyEnablePeerAccess));
+    c->final_out = (uint8_t*)c->frame_ipc;
+    return RT_OK;
+}
+
+int rt_context_frame_set(rt_context* c, void* dev_ptr) {
+    if (!c) { set_error("null context"); return RT_ERR_INVALID; }
+    c->final_out = (uint8_t*)dev_ptr;
     return RT_OK;
 }
 
@@ -1138,7 +1192,10 @@ int rt_multi_render(rt_multi* m, uint8_t* bgr_rows, int32_t* primary_ids, rt_sta
         sum.render_ms = std::max(sum.render_ms, a.render_ms);
         sum.bvh_build_ms = std::max(sum.bvh_build_ms, a.bvh_build_ms);
         sum.local_rows += a.local_rows;
-        for (int k = 0; k < 2; k++) { sum.bvh_nodes_visited[k] += a.bvh_nodes_visited[k]; sum.bvh_prims_tested[k] += a.bvh_prims_tested[k]; sum.heavy_rays[k] += a.heavy_rays[k]; }
+        for (int k = 0; k < 2; k++) {
+            sum.bvh_nodes_visited[k] += a.bvh_nodes_visited[k]; sum.bvh_prims_tested[k] += a.bvh_prims_tested[k]; sum.heavy_rays[k] += a.heavy_rays[k];
+            sum.scan_sphere_tests[k] += a.scan_sphere_tests[k];
+        }
         for (int k = 0; k < 5; k++) { sum.class_ms[k] = std::max(sum.class_ms[k], a.class_ms[k]); sum.class_launches[k] += a.class_launches[k]; }
         sum.host_levels |= a.host_levels; sum.device_driven_overflows += a.device_driven_overflows;
     }

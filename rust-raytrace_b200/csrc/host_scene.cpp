@@ -371,6 +371,19 @@ int rt_scene_add_spheres(rt_scene* s, uint64_t n, const double* cr, const uint32
     s->n_spheres += n;
     return RT_OK;
 }
+int rt_scene_update_spheres(rt_scene* s, uint64_t first_object, uint64_t n, const double* cr) {
+    if (!s || (n && !cr)) { set_error("rt_scene_update_spheres: null argument"); return RT_ERR_INVALID; }
+    if (first_object > s->objects.size() || n > s->objects.size() - first_object) { set_error("rt_scene_update_spheres: object range out of bounds"); return RT_ERR_INVALID; }
+    for (uint64_t i = 0; i < n; i++)
+        if (s->objects[first_object + i].is_plane) { set_error("rt_scene_update_spheres: object " + std::to_string(first_object + i) + " is a plane"); return RT_ERR_INVALID; }
+    scene_touch(s);
+    for (uint64_t i = 0; i < n; i++) {
+        HostObject& o = s->objects[first_object + i];
+        o.p[0] = cr[4 * i]; o.p[1] = cr[4 * i + 1]; o.p[2] = cr[4 * i + 2];
+        o.radius = cr[4 * i + 3];
+    }
+    return RT_OK;
+}
 int rt_scene_add_plane(rt_scene* s, const double* point, const double* normal, uint32_t material) {
     if (!s || !point || !normal) { set_error("rt_scene_add_plane: null argument"); return RT_ERR_INVALID; }
     if (material >= s->materials.size()) { set_error("rt_scene_add_plane: material index out of range"); return RT_ERR_INVALID; }

@@ -148,10 +148,13 @@ struct ScanSmem {
     uint64_t bar[2];
 };
 
+// Returns the number of exact sphere tests this thread made (a shadow query stops at its first occluder): the
+// DFMA-equivalent work the scan's roofline fraction is computed from (bench.py).
 template <bool SHADOW>
-__device__ __forceinline__ void scan_spheres(const DeviceScene& sc, ScanSmem* sm, const RayQ& r, bool active, Closest& best, double range2, Shadow& sh) {
+__device__ __forceinline__ uint32_t scan_spheres(const DeviceScene& sc, ScanSmem* sm, const RayQ& r, bool active, Closest& best, double range2, Shadow& sh) {
     const uint32_t n = sc.n_spheres;
-    if (n == 0) return;
+    uint32_t tested = 0;
+    if (n == 0) return 0;
     const uint32_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
     if (threadIdx.x == 0) {
         mbar_init(&sm->bar[0], 1);
@@ -176,6 +179,7 @@ __device__ __forceinline__ void scan_spheres(const DeviceScene& sc, ScanSmem* sm
         const uint32_t cnt = (n - first) < (uint32_t)SCAN_TILE ? (n - first) : (uint32_t)SCAN_TILE;
         if (!done) {
             const SphereRec* t = sm->tile[buf];
+            tested += cnt;
 #pragma unroll 4
             for (uint32_t j = 0; j < cnt; j++) {
                 const double2 c01 = *reinterpret_cast<const double2*>(&t[j].cx);
@@ -183,7 +187,7 @@ __device__ __forceinline__ void scan_spheres(const DeviceScene& sc, ScanSmem* sm
                 double th;
                 if (sphere_hit(r, c01.x, c01.y, c23.x, c23.y, th)) {
                     if (SHADOW) {
-                        if (shadow_hit_counts(th, range2)) { sh.any = true; done = true; break; }
+                        if (shadow_hit_counts(th, range2)) { sh.any = true; done = true; tested -= cnt - (j + 1u); break; }
                     } else {
                         closest_update(best, th, __ldg(sc.sph_obj + first + j));
                     }
@@ -197,12 +201,19 @@ __device__ __forceinline__ void scan_spheres(const DeviceScene& sc, ScanSmem* sm
             break;
         }
     }
+    return tested;
+}
+__device__ __forceinline__ void flush_scan_tests(uint32_t tested, Counters* counters, int cls) {
+    unsigned long long t = tested;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xFFFFFFFFu, t, o);
+    if ((threadIdx.x & 31) == 0 && t) atomicAdd(&counters->scan_tests[cls], t);
 }
 
 // n_dev (both scan kernels): the ray count is read on the device and the grid was sized for an upper bound -- CTAs past
 // the end leave before they touch a barrier
 __global__ void __launch_bounds__(SCAN_THREADS) k_closest_scan(const __grid_constant__ DeviceScene sc, RayQueue q, uint32_t first, uint32_t n,
-                                                               const uint32_t* n_dev) {
+                                                               const uint32_t* n_dev, Counters* counters) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     ScanSmem* sm = reinterpret_cast<ScanSmem*>(smem_raw);
     if (n_dev) { n = *n_dev < q.cap ? *n_dev : q.cap; if (blockIdx.x * SCAN_THREADS >= n) return; }
@@ -213,15 +224,16 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_closest_scan(const __grid_cons
     Closest best = closest_none();
     planes_closest(sc, r, best);
     Shadow dummy; dummy.nan = false; dummy.any = false;
-    scan_spheres<false>(sc, sm, r, active && !best.nan, best, -1.0, dummy);
+    const uint32_t tested = scan_spheres<false>(sc, sm, r, active && !best.nan, best, -1.0, dummy);
     if (active) {
         q.hit_id[i] = closest_id(best);
         q.hit_t[i] = best.t;
     }
+    flush_scan_tests(tested, counters, 0);
 }
 
 __global__ void __launch_bounds__(SCAN_THREADS) k_shadow_scan(const __grid_constant__ DeviceScene sc, ShadowQueue sq, uint32_t n, double* accum,
-                                                              const uint32_t* n_dev) {
+                                                              const uint32_t* n_dev, Counters* counters) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     ScanSmem* sm = reinterpret_cast<ScanSmem*>(smem_raw);
     if (n_dev) { n = *n_dev < sq.cap ? *n_dev : sq.cap; if (blockIdx.x * SCAN_THREADS >= n) return; }
@@ -233,8 +245,9 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_shadow_scan(const __grid_const
     Shadow s; s.nan = false; s.any = false;
     planes_shadow(sc, r, range2, s);
     Closest dummy = closest_none();
-    scan_spheres<true>(sc, sm, r, active && !s.nan && !s.any, dummy, range2, s);
+    const uint32_t tested = scan_spheres<true>(sc, sm, r, active && !s.nan && !s.any, dummy, range2, s);
     if (active && !shadow_result(s, range2)) accum_add(accum, sq.pixel[i], c3(sq.cr[i], sq.cg[i], sq.cb[i]));
+    flush_scan_tests(tested, counters, 1);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -866,7 +879,7 @@ static void l_closest(cudaStream_t st, const DeviceScene& sc, bool bvh, RayQueue
         k_heavy_scan<false><<<(uint32_t)sm_count * 4u, HEAVY_THREADS, 0, st>>>(sc, q, none, first, nullptr, counters, heavy, lci);
     } else {
         scan_attr_once();
-        k_closest_scan<<<div_up(n, SCAN_THREADS), SCAN_THREADS, sizeof(ScanSmem), st>>>(sc, q, first, n, n_dev);
+        k_closest_scan<<<div_up(n, SCAN_THREADS), SCAN_THREADS, sizeof(ScanSmem), st>>>(sc, q, first, n, n_dev, counters);
     }
 }
 
@@ -896,7 +909,7 @@ static void l_shadow(cudaStream_t st, const DeviceScene& sc, bool bvh, ShadowQue
         k_heavy_scan<true><<<(uint32_t)sm_count * 4u, HEAVY_THREADS, 0, st>>>(sc, none, sq, 0u, accum, counters, heavy, lci);
     } else {
         scan_attr_once();
-        k_shadow_scan<<<div_up(n, SCAN_THREADS), SCAN_THREADS, sizeof(ScanSmem), st>>>(sc, sq, n, accum, n_dev);
+        k_shadow_scan<<<div_up(n, SCAN_THREADS), SCAN_THREADS, sizeof(ScanSmem), st>>>(sc, sq, n, accum, n_dev, counters);
     }
 }
 

@@ -23,6 +23,7 @@ struct Counters {
     unsigned long long bvh_nodes[2];   // BVH nodes fetched: [0] closest-hit kernel, [1] shadow kernel
     unsigned long long bvh_prims[2];   // exact sphere tests done at BVH leaves
     unsigned long long heavy_rays[2];  // rays finished by the block-wide scan: [0] closest, [1] shadow
+    unsigned long long scan_tests[2];  // exact sphere tests made by the linear-scan kernels: [0] closest, [1] shadow
     // per primary batch (a device-driven frame zeroes from here to the end of the record between batches)
     uint32_t shadow_count;     // shadow queue length
     uint32_t _pad1;

@@ -10,6 +10,33 @@ from . import scene as S
 
 _MASK = (1 << 64) - 1
 
+# BASELINE configs 1 and 2: the Cornell-box configuration of the upstream test_scene.txt, values restated (the file is not
+# copied; tests/test_oracle_outbmp.py checks that it parses to the same scene as the original where that is present)
+TEST_SCENE_TEXT = """
+{
+    objects: [
+        { bounds: Plane { point: (0, 0, -3) normal: (0, 0, 1) }
+          material: IndirectPhongMaterial { diffuse: rgb(1.0, 1.0, 1.0) specular: rgb(0.0, 0.0, 0.0) exponent: 1.0 ambient: rgb(0.0, 0.0, 0.0) samples: 1 } }
+        { bounds: Plane { point: (0, 0, 0) normal: (0, 1.0, 0) }
+          material: IndirectPhongMaterial { diffuse: rgb(1.0, 1.0, 1.0) specular: rgb(0.0, 0.0, 0.0) exponent: 1.0 ambient: rgb(0.0, 0.0, 0.0) samples: 1 } }
+        { bounds: Plane { point: (0, 6, 0) normal: (0, -1.0, 0) }
+          material: IndirectPhongMaterial { diffuse: rgb(1.0, 1.0, 1.0) specular: rgb(0.0, 0.0, 0.0) exponent: 1.0 ambient: rgb(0.0, 0.0, 0.0) samples: 1 } }
+        { bounds: Plane { point: (-3, 0, 0) normal: (1, 0, 0) }
+          material: IndirectPhongMaterial { diffuse: rgb(1.0, 0.0, 0.0) specular: rgb(0.0, 0.0, 0.0) exponent: 1.0 ambient: rgb(0.0, 0.0, 0.0) samples: 1 } }
+        { bounds: Plane { point: (3, 0, 0) normal: (-1, 0, 0) }
+          material: IndirectPhongMaterial { diffuse: rgb(0.0, 1.0, 0.0) specular: rgb(0.0, 0.0, 0.0) exponent: 1.0 ambient: rgb(0.0, 0.0, 0.0) samples: 1 } }
+        { bounds: Sphere { center: (0, 1.5, 0) radius: 1.5 }
+          material: IndirectPhongMaterial { diffuse: rgb(1.0, 1.0, 1.0) specular: rgb(0.0, 0.0, 0.0) exponent: 1.0 ambient: rgb(0.0, 0.0, 0.0) samples: 1 } }
+        { bounds: Sphere { center: (0, 10.65, 0) radius: 5 }
+          material: IndirectPhongMaterial { diffuse: rgb(1.0, 1.0, 1.0) specular: rgb(0.0, 0.0, 0.0) exponent: 1.0 ambient: rgb(5.0, 5.0, 5.0) samples: 1 } }
+    ]
+    lights: [ ]
+    camera: SimplePerspectiveCamera new((0, 3, 17), (0, 0, -1), (0, 1, 0), 3.6)
+    background: SolidColorBackground { color: rgb(0.051, 0.051, 0.051) }
+    options: { width: 800 height: 800 antialias: 1024 }
+}
+"""
+
 
 class SplitMix64:
     def __init__(self, seed):

@@ -43,7 +43,7 @@ if __name__ == "__main__":
         run("1M/4K/d8 bvh fast", d, max_depth=8, seed=4, accel=rt.ACCEL_BVH, fp_mode=rt.FP_FAST)
     if "cornell" in which:
         sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
-        from test_gpu_parity import REF_TEXT_SCENE
+        REF_TEXT_SCENE = scenes.TEST_SCENE_TEXT
         sc = rt.serialize.deserialize(REF_TEXT_SCENE)
         for aa in (1, 16):
             ctx = rt.Context(sc, width=3840, height=2160, antialias=aa, seed=1)
