@@ -762,6 +762,40 @@ void orc_project(void* s, uint64_t n, const double* pos, uint64_t seed, double* 
     }
 }
 
+// ray_color for tests (src/raytrace.rs:261-267): colour of each given ray at the given significance and recursion depth.
+// rng_mode ORC_RNG_COUNTER: ray i draws from keys[i].  ORC_RNG_SEQUENTIAL: ONE xorshift128 stream with the given state is
+// threaded through all rays in order, exactly as upstream threads `rng` (so a test can predict every draw, in order).
+// rays_out (optional): Scene::intersect calls made, shadow queries included.
+void orc_ray_color(void* s, uint64_t n, const double* origin_dir, double significance, uint32_t depth, const uint64_t* keys, uint32_t max_depth,
+                   double min_significance, int32_t rng_mode, const uint32_t* xorshift_state4, double* rgb_out, uint64_t* rays_out) {
+    const Scene* sc = (const Scene*)s;
+    TraceCtx c{};
+    c.scene = sc;
+    c.max_depth = max_depth;
+    c.min_significance = min_significance;
+    c.primary_id = nullptr;
+    c.rng.mode = rng_mode;
+    if (xorshift_state4) { c.rng.x = xorshift_state4[0]; c.rng.y = xorshift_state4[1]; c.rng.z = xorshift_state4[2]; c.rng.w = xorshift_state4[3]; }
+    for (uint64_t i = 0; i < n; i++) {
+        Ray r{V3{origin_dir[6 * i], origin_dir[6 * i + 1], origin_dir[6 * i + 2]}, V3{origin_dir[6 * i + 3], origin_dir[6 * i + 4], origin_dir[6 * i + 5]}};
+        Color col = ray_color(c, r, significance, depth, keys ? keys[i] : 0);
+        rgb_out[3 * i] = col.r; rgb_out[3 * i + 1] = col.g; rgb_out[3 * i + 2] = col.b;
+    }
+    if (rays_out) *rays_out = c.stats.rays;
+}
+
+// camera.project with the reference's sequential RNG (src/camera.rs:110-121 draws theta, then the radius)
+void orc_project_sequential(void* s, uint64_t n, const double* pos, const uint32_t* xorshift_state4, double* origin_dir) {
+    Scene* sc = (Scene*)s;
+    Rng rng{}; rng.mode = ORC_RNG_SEQUENTIAL;
+    rng.x = xorshift_state4[0]; rng.y = xorshift_state4[1]; rng.z = xorshift_state4[2]; rng.w = xorshift_state4[3];
+    for (uint64_t i = 0; i < n; i++) {
+        Ray r = camera_project(sc->camera, pos[2 * i], pos[2 * i + 1], rng, 0);
+        origin_dir[6 * i] = r.origin.x; origin_dir[6 * i + 1] = r.origin.y; origin_dir[6 * i + 2] = r.origin.z;
+        origin_dir[6 * i + 3] = r.direction.x; origin_dir[6 * i + 4] = r.direction.y; origin_dir[6 * i + 5] = r.direction.z;
+    }
+}
+
 static void fill_opts(const Scene* sc, const orc_opts* in, Opts* o) {
     o->width = in->width ? in->width : sc->width;
     o->height = in->height ? in->height : sc->height;

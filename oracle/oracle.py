@@ -72,6 +72,11 @@ def lib():
         L.orc_srgb_tables.argtypes = [dp, dp]
         L.orc_trace_rays.argtypes = [C.c_void_p, C.c_uint64, dp, C.POINTER(C.c_int32), dp, dp]
         L.orc_project.argtypes = [C.c_void_p, C.c_uint64, dp, C.c_uint64, dp]
+        L.orc_ray_color.argtypes = [C.c_void_p, C.c_uint64, dp, C.c_double, C.c_uint32, C.POINTER(C.c_uint64), C.c_uint32, C.c_double, C.c_int32,
+                                    C.POINTER(C.c_uint32), dp, C.POINTER(C.c_uint64)]
+        L.orc_ray_color.restype = None
+        L.orc_project_sequential.argtypes = [C.c_void_p, C.c_uint64, dp, C.POINTER(C.c_uint32), dp]
+        L.orc_project_sequential.restype = None
         L.orc_render.argtypes = [C.c_void_p, C.POINTER(OrcOpts), C.POINTER(C.c_uint8), C.POINTER(C.c_int32), dp, C.POINTER(OrcStats)]
         L.orc_render_pixels.argtypes = [C.c_void_p, C.POINTER(OrcOpts), C.c_uint64, C.POINTER(C.c_uint32), C.POINTER(C.c_uint8),
                                         C.POINTER(C.c_int32), dp, C.POINTER(OrcStats)]
@@ -215,6 +220,33 @@ class OracleScene:
         out = np.zeros((p.shape[0], 6), dtype=np.float64)
         lib().orc_project(self._h, p.shape[0], _ptr(p, C.c_double), seed, _ptr(out, C.c_double))
         return out
+
+
+def _ray_color(self, origin_dir, significance=1.0, depth=0, keys=None, max_depth=4, min_significance=1.0 / 512.0, xorshift_state=None):
+    """ray_color (src/raytrace.rs:261-267) of each ray; keys: counter-RNG key per ray, or xorshift_state (x, y, z, w): ONE
+    sequential xorshift128 stream threaded through all rays in order, as upstream threads its rng.  Returns (rgb, rays)."""
+    od = np.ascontiguousarray(origin_dir, dtype=np.float64).reshape(-1, 6)
+    n = od.shape[0]
+    out = np.zeros((n, 3), dtype=np.float64)
+    rays = C.c_uint64(0)
+    k = None if keys is None else np.ascontiguousarray(keys, dtype=np.uint64)
+    st = None if xorshift_state is None else (C.c_uint32 * 4)(*[int(v) & 0xFFFFFFFF for v in xorshift_state])
+    lib().orc_ray_color(self._h, n, _ptr(od, C.c_double), float(significance), int(depth), _ptr(k, C.c_uint64), int(max_depth), float(min_significance),
+                        RNG_SEQUENTIAL if xorshift_state is not None else RNG_COUNTER, st, _ptr(out, C.c_double), C.byref(rays))
+    return out, int(rays.value)
+
+
+def _project_sequential(self, pos, xorshift_state):
+    """Camera::project with the reference's sequential rng (src/camera.rs:110-121)."""
+    p = np.ascontiguousarray(pos, dtype=np.float64).reshape(-1, 2)
+    out = np.zeros((p.shape[0], 6), dtype=np.float64)
+    st = (C.c_uint32 * 4)(*[int(v) & 0xFFFFFFFF for v in xorshift_state])
+    lib().orc_project_sequential(self._h, p.shape[0], _ptr(p, C.c_double), st, _ptr(out, C.c_double))
+    return out
+
+
+OracleScene.ray_color = _ray_color
+OracleScene.project_sequential = _project_sequential
 
 
 def _stats(st):

@@ -427,30 +427,50 @@ def test_config3_spheres10k_4k_depth8(gpu, orc, scenes):
     print("config3: %d rays, bvh %.2f ms, scan %.1f ms, sparse identical %.5f" % (bvh.stats["rays_total"], bvh.stats["render_ms"], lin.stats["render_ms"], same))
 
 
-def test_config4_spheres1m_4k_depth8(gpu, orc, scenes):
-    """1M spheres through the device BVH (4K here; bench.py runs the 8K frame): all 8.3 M primary ids against the f64
-    brute-force scan, and final pixels of a sparse set against the CPU oracle"""
-    desc = scenes.spheres_1m(3840, 2160)
+def test_config4_spheres1m_8k_depth8(gpu, orc, scenes):
+    """BASELINE config 4 at its own size: 1M spheres through the device BVH at 7680x4320, depth 8.
+      * final pixels and primary ids of a seed-determined sparse pixel set against the CPU oracle (linear scan, recursion);
+      * every primary id of one 1/8 row-band shard (4.1 M rays) against the GPU's f64 brute-force scan of the same shard;
+      * the frame assembled from eight shards (rt_multi, the shards sharing this GPU) against the one-context frame."""
+    desc = scenes.spheres_1m(7680, 4320)
     sc = gpu.Scene(desc)
     kw = dict(max_depth=8, seed=4)
     bvh = gpu.raytrace.render(sc, accel=gpu.ACCEL_BVH, **kw)
+    assert bvh.ids.shape == (4320, 7680) and bvh.stats["rays_primary"] == 7680 * 4320
+    same = _sparse_check(bvh, orc.OracleScene(desc), 1024, "config4", antialias=1, **kw)
     # (almost) primary rays only through the scan: max_depth 0 and an unreachable significance threshold leave only the
     # refraction children of transparent hits (upstream spawns those without a significance test, src/raytrace.rs:214-223)
-    prim = gpu.raytrace.render(sc, accel=gpu.ACCEL_LINEAR, max_depth=0, min_significance=1e30, seed=4)
-    assert prim.stats["rays_primary"] == 3840 * 2160 and prim.stats["rays_shadow"] == 0
-    assert prim.stats["rays_secondary"] < 0.1 * prim.stats["rays_primary"]
-    assert np.array_equal(bvh.ids, prim.ids), "BVH and scan disagree on %d primary ids" % int((bvh.ids != prim.ids).sum())
-    same = _sparse_check(bvh, orc.OracleScene(desc), 1024, "config4", antialias=1, **kw)
-    print("config4@4K: %d rays, bvh %.1f ms (build %.1f ms, %d nodes), primary scan %.0f ms, sparse identical %.5f" % (
-        bvh.stats["rays_total"], bvh.stats["render_ms"], bvh.stats["bvh_build_ms"], bvh.stats["n_bvh_nodes"], prim.stats["render_ms"], same))
+    shard = dict(rank=3, world=8)
+    a = gpu.Context(sc, accel=gpu.ACCEL_BVH, **kw, **shard)
+    a.render()
+    _, ids_bvh, _ = a.download(want_rows=False, want_ids=True)
+    a.close()
+    p = gpu.Context(sc, accel=gpu.ACCEL_LINEAR, max_depth=0, min_significance=1e30, seed=4, **shard)
+    st = p.render()
+    _, ids_scan, _ = p.download(want_rows=False, want_ids=True)
+    p.close()
+    assert st["rays_primary"] == 7680 * 4320 // 8 and st["rays_shadow"] == 0 and st["rays_secondary"] < 0.1 * st["rays_primary"]
+    assert np.array_equal(ids_bvh, ids_scan), "BVH and scan disagree on %d primary ids of the shard" % int((ids_bvh != ids_scan).sum())
+    # the shard's rows are the frame's bands 3, 11, 19, ...: same ids as the whole frame there
+    rows_of_shard = (np.arange(ids_bvh.shape[0]) // 4 * 8 + 3) * 4 + np.arange(ids_bvh.shape[0]) % 4
+    assert np.array_equal(ids_bvh, bvh.ids[rows_of_shard])
+    gpu.release_cached_memory()   # the whole-frame context's 29 GB of queues: eight shard contexts are about to share this GPU
+    multi = gpu.raytrace.render_multi(sc, [0] * 8, gather=gpu.GATHER_PEER, accel=gpu.ACCEL_BVH, **kw)
+    assert np.array_equal(multi.ids, bvh.ids) and multi.stats["rays_total"] == bvh.stats["rays_total"]
+    d = np.abs(multi.rows.astype(np.int16) - bvh.rows.astype(np.int16))
+    assert d.max() <= 1 and (d != 0).mean() < 1e-5
+    print("config4@8K: %d rays, bvh %.1f ms (%d nodes), shard scan %.0f ms, sparse identical %.5f" % (
+        bvh.stats["rays_total"], bvh.stats["render_ms"], bvh.stats["n_bvh_nodes"], st["render_ms"], same))
 
 
-def test_config5_skybox100k_4k(gpu, orc, scenes):
-    """textured configuration (the skybox is the only texture path upstream), 4 spp here (bench.py runs 16 spp)"""
-    desc = scenes.skybox_100k(3840, 2160, antialias=4, face_size=256)
+def test_config5_skybox100k_4k_16spp(gpu, orc, scenes):
+    """BASELINE config 5 at its own size: 100k reflective spheres under six 1024x1024 skybox faces (the only texture path
+    upstream), 3840x2160 at 16 samples per pixel (133 M paths in primary batches); sparse pixel set against the CPU oracle"""
+    desc = scenes.skybox_100k(3840, 2160, antialias=16, face_size=1024)
     fr = gpu.raytrace.render(gpu.Scene(desc), max_depth=4, seed=5)
-    same = _sparse_check(fr, orc.OracleScene(desc), 2048, "config5", antialias=4, max_depth=4, seed=5)
-    print("config5@4spp: %d rays, %.1f ms, sparse identical %.5f" % (fr.stats["rays_total"], fr.stats["render_ms"], same))
+    assert fr.stats["paths"] == 3840 * 2160 * 16 and fr.stats["host_levels"] == 0
+    same = _sparse_check(fr, orc.OracleScene(desc), 1024, "config5", antialias=16, max_depth=4, seed=5)
+    print("config5@16spp: %d rays, %.1f ms, sparse identical %.5f" % (fr.stats["rays_total"], fr.stats["render_ms"], same))
 
 
 def test_cli_renders_test_scene_to_out_bmp(gpu, tmp_path):
