@@ -368,6 +368,7 @@ __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_closest_bvh(
             if (!active) {
                 if (li < n_now) {
                     ray = first + li;
+                    RT_CHECK(ray < q.cap);
                     const RayQ r = make_rayq(v3(q.ox[ray], q.oy[ray], q.oz[ray]), v3(q.dx[ray], q.dy[ray], q.dz[ray]));
                     Closest best = closest_none();
                     planes_closest(sc, r, best);
@@ -450,6 +451,7 @@ __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_shadow_bvh(c
             if (!active) {
                 if (li < n_now) {
                     ray = li;
+                    RT_CHECK(ray < sq.cap);
                     const RayQ r = make_rayq(v3(sq.ox[ray], sq.oy[ray], sq.oz[ray]), v3(sq.dx[ray], sq.dy[ray], sq.dz[ray]));
                     const double range2 = sq.r2[ray];
                     Shadow s; s.nan = false; s.any = false;
@@ -571,6 +573,8 @@ __global__ void __launch_bounds__(HEAVY_THREADS) k_heavy_scan(const __grid_const
         const uint32_t k0 = j * chunk < sc.n_spheres ? j * chunk : sc.n_spheres;
         const uint32_t k1 = k0 + chunk < sc.n_spheres ? k0 + chunk : sc.n_spheres;
         const uint32_t i = heavy[e];  // closest: already the absolute queue index (first + local)
+        RT_CHECK(SHADOW ? i < sq.cap : i < q.cap);
+        RT_CHECK(item < HEAVY_SPLIT_ITEMS || G == 1);
         const V3 o = SHADOW ? v3(sq.ox[i], sq.oy[i], sq.oz[i]) : v3(q.ox[i], q.oy[i], q.oz[i]);
         const V3 d = SHADOW ? v3(sq.dx[i], sq.dy[i], sq.dz[i]) : v3(q.dx[i], q.dy[i], q.dz[i]);
         const RayQ r = make_rayq(o, d);
@@ -671,12 +675,14 @@ __global__ void __launch_bounds__(SHADE_THREADS, RT_SHADE_MIN_BLOCKS) k_shade(co
         uint32_t pixel = 0, depth = 0;
         if (active) {
             const uint32_t i = first + li;
+            RT_CHECK(i < in.cap);
             const V3 o = v3(in.ox[i], in.oy[i], in.oz[i]);
             const V3 d = v3(in.dx[i], in.dy[i], in.dz[i]);
             const C3 T = c3(in.tr[i], in.tg[i], in.tb[i]);
             const uint32_t meta = in.meta[i];
             const int32_t hid = in.hit_id[i];
             pixel = in.pixel[i];
+            RT_CHECK(pixel < fp.local_rows * fp.width);
             depth = meta & META_DEPTH_MASK;
             if ((meta & META_RECORD_ID) && ids) ids[pixel] = hid;
             const C3 add = shade_begin(sc, fp, o, d, T, in.sig[i], in.key[i], depth, hid, in.hit_t[i], s);

@@ -32,6 +32,20 @@
 #define RT_NS strict
 #endif
 
+// Bounds checks of our own (compute-sanitizer is closed on the GPU pool this was developed on).  A build with
+// -DRT_CHECK_BOUNDS (tools/build_variant.sh checked -DRT_CHECK_BOUNDS) traps -- the launch fails, the render returns
+// RT_ERR_CUDA -- on a node / leaf / stack / queue / pixel index outside its buffer; the GPU test-suite and
+// tools/gpu_sanitize.py are then run through that library (profiles/r02_bounds_checked_build.txt).  Off: no code.
+#if defined(RT_CHECK_BOUNDS)
+#if defined(__CUDA_ARCH__)
+#define RT_CHECK(c) do { if (!(c)) __trap(); } while (0)
+#else
+#define RT_CHECK(c) do { if (!(c)) abort(); } while (0)
+#endif
+#else
+#define RT_CHECK(c) ((void)0)
+#endif
+
 namespace rt {
 namespace RT_NS {
 
@@ -471,7 +485,7 @@ RT_HD unsigned long long trav_pack(int32_t node, float t) {
     return (unsigned long long)(uint32_t)node | ((unsigned long long)tb << 32);
 }
 
-RT_HD void trav_push(TravStack& st, int& sp, int32_t node, float t) { st.e[sp++] = trav_pack(node, t); }
+RT_HD void trav_push(TravStack& st, int& sp, int32_t node, float t) { RT_CHECK(sp >= 0 && sp < BVH_STACK); st.e[sp++] = trav_pack(node, t); }
 RT_HD int32_t trav_pop(const TravStack& st, int& sp, float bound) {
     while (sp > 0) {
         const unsigned long long e = st.e[--sp];
@@ -487,7 +501,7 @@ RT_HD int32_t trav_pop(const TravStack& st, int& sp, float bound) {
 struct TravStackFixed {
     int32_t e[BVH_STACK];
 };
-RT_HD void trav_push(TravStackFixed& st, int& sp, int32_t node, float) { st.e[sp++] = node; }
+RT_HD void trav_push(TravStackFixed& st, int& sp, int32_t node, float) { RT_CHECK(sp >= 0 && sp < BVH_STACK); st.e[sp++] = node; }
 RT_HD int32_t trav_pop(const TravStackFixed& st, int& sp, float) { return sp > 0 ? st.e[--sp] : TRAV_EMPTY; }
 
 // Walk internal nodes from `cur` (near child first, far child pushed) until the next thing to do is a leaf test
@@ -530,6 +544,7 @@ struct TravStackWide {
 };
 RT_HD int32_t trav_pop(const TravStackWide& st, int& sp, float) { return sp > 0 ? st.e[--sp] : TRAV_EMPTY; }
 RT_HD void trav_push_if(TravStackWide& st, int& sp, bool hit, int32_t node) {
+    RT_CHECK(!hit || (sp >= 0 && sp < BVH_STACK_WIDE));
     if (hit) st.e[sp++] = node;  // two predicated instructions, no branch
 }
 
@@ -538,6 +553,7 @@ RT_HD void trav_push_if(TravStackWide& st, int& sp, bool hit, int32_t node) {
 RT_HD int32_t trav_descend_wide(const DeviceScene& sc, const BoxRay32& br, int32_t cur, float bound, TravStackWide& st, int& sp, TraverseCount& tc,
                                 int max_steps = 0x7FFFFFFF) {
     while (cur >= 0 && max_steps-- > 0) {
+        RT_CHECK((uint32_t)cur < sc.n_bvh_nodes);
         const BvhQNode* p = sc.bvh_wnodes[cur].h;
         const QNodeWords a = load_qnode(p), b = load_qnode(p + 1);
         float t;
@@ -564,6 +580,7 @@ template <bool QNODES, typename STACK>
 RT_HD int32_t trav_descend(const DeviceScene& sc, const BoxRay32& br, int32_t cur, float bound, STACK& st, int& sp, TraverseCount& tc,
                            int max_steps = 0x7FFFFFFF) {
     while (cur >= 0 && max_steps-- > 0) {
+        RT_CHECK((uint32_t)cur < sc.n_bvh_nodes);
         float t0, t1;
         bool h0, h1;
         int32_t c0, c1;
@@ -607,12 +624,14 @@ RT_HD float shadow_bound32(double range2, double t0) {
 
 // exact test of Morton-slot k against the running closest hit; returns the new filter bound
 RT_HD void leaf_closest(const DeviceScene& sc, const RayQ& r, int32_t k, Closest& best, TraverseCount& tc) {
+    RT_CHECK(k >= 0 && (uint32_t)k < sc.n_spheres);
     const SphereRec* s = sc.bvh_sph + k;
     double t;
     tc.prims++;
     if (sphere_hit(r, RT_LDG(&s->cx), RT_LDG(&s->cy), RT_LDG(&s->cz), RT_LDG(&s->r2), t)) closest_update(best, t, RT_LDG(sc.bvh_obj + k));
 }
 RT_HD bool leaf_shadow(const DeviceScene& sc, const RayQ& r, int32_t k, double range2, TraverseCount& tc) {
+    RT_CHECK(k >= 0 && (uint32_t)k < sc.n_spheres);
     const SphereRec* s = sc.bvh_sph + k;
     double t;
     tc.prims++;
@@ -723,6 +742,7 @@ RT_HD uint32_t f64_as_u32(double x) {  // Rust `as u32`: saturating, NaN -> 0
     return (uint32_t)x;
 }
 RT_HD C3 tex_at(const DeviceScene& sc, const TextureRec& t, uint32_t x, uint32_t y) {
+    RT_CHECK(x < t.width && y < t.height);
     size_t idx = 3 * ((size_t)x + (size_t)y * t.width);
     return c3(RT_LDG(sc.srgb_values + RT_LDG(t.data + idx)), RT_LDG(sc.srgb_values + RT_LDG(t.data + idx + 1)), RT_LDG(sc.srgb_values + RT_LDG(t.data + idx + 2)));
 }
@@ -811,6 +831,7 @@ RT_HD C3 shade_begin(const DeviceScene& sc, const FrameParams& fp, V3 o, V3 d, C
     s.alive = false; s.lit = false; s.diffuse = false; s.specular = false; s.has_refr = false;
     s.kind = -1; s.samples = 0;
     if (hit_id < 0) return T * background_color(sc, d);
+    RT_CHECK((uint32_t)hit_id < sc.n_objects);
     const MaterialRec* m = sc.materials + RT_LDG(sc.obj_material + hit_id);
     const int32_t kind = RT_LDG(&m->kind);
     C3 ambient = kind == MAT_TRANSPARENT ? c3(0.0, 0.0, 0.0) : c3(RT_LDG(&m->ambient[0]), RT_LDG(&m->ambient[1]), RT_LDG(&m->ambient[2]));

@@ -264,3 +264,80 @@ def test_cli_reports_like_the_reference_binary(rt, tmp_path):
         r = subprocess.run([CLI, "--width", "16", "--height", "16", "--antialias", "1"], capture_output=True, text=True, cwd=tmp_path)
         assert r.returncode == 1 and "render failed" in r.stderr
         assert not (tmp_path / "out.bmp").exists()
+
+
+# ---- the Rust shim crate (shim/): source only, but its FFI block cannot drift from the header ---------------------------
+def _rust_layout(fields):
+    """size / offsets of a #[repr(C)] struct of primitives and fixed arrays, by the C rules Rust's repr(C) follows"""
+    prim = {"u8": 1, "i8": 1, "u16": 2, "i16": 2, "u32": 4, "i32": 4, "f32": 4, "u64": 8, "i64": 8, "f64": 8, "usize": 8, "c_int": 4}
+    off, align, out = 0, 1, []
+    for name, ty in fields:
+        m = re.fullmatch(r"\[(\w+); (\d+)\]", ty)
+        elem, n = (m.group(1), int(m.group(2))) if m else (ty, 1)
+        sz = prim[elem]
+        off = (off + sz - 1) // sz * sz
+        out.append((name, off, sz * n))
+        off += sz * n
+        align = max(align, sz)
+    return out, (off + align - 1) // align * align
+
+
+def test_rust_shim_ffi_is_generated_from_the_header_and_matches_the_c_layout(rt):
+    import ctypes as C
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("gen_rust_ffi", os.path.join(ROOT, "tools", "gen_rust_ffi.py"))
+    gen = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(gen)
+    text, structs = gen.generate()
+    committed = open(os.path.join(ROOT, "shim", "src", "ffi.rs")).read()
+    assert committed == text, "shim/src/ffi.rs is stale: run python tools/gen_rust_ffi.py"
+    B = __import__("importlib").import_module("rust-raytrace_b200._binding")
+    mirror = {"RtRenderOpts": B.RenderOpts, "RtStats": B.Stats, "RtSceneInfo": B.SceneInfo, "RtPeaks": B.Peaks}
+    found = 0
+    for m in re.finditer(r"#\[repr\(C\)\]\s*#\[derive\([^)]*\)\]\s*pub struct (\w+) \{(.*?)\n\}", committed, flags=re.S):
+        name = m.group(1)
+        fields = re.findall(r"pub (\w+): ([^,\n]+),", m.group(2))
+        assert name in mirror, "no ctypes mirror for %s" % name
+        ct = mirror[name]
+        layout, size = _rust_layout(fields)
+        assert [f for f, _, _ in layout] == [f for f, _ in ct._fields_], name
+        for f, off, sz in layout:
+            d = getattr(ct, f)
+            assert (d.offset, d.size) == (off, sz), "%s.%s: Rust (%d, %d) vs C (%d, %d)" % (name, f, off, sz, d.offset, d.size)
+        assert size == C.sizeof(ct), "%s: %d bytes in Rust, %d in C" % (name, size, C.sizeof(ct))
+        found += 1
+    assert found == len(mirror)
+    # every exported function is declared, with as many parameters as the ctypes table has
+    decls = dict(re.findall(r"pub fn (rt_\w+)\((.*?)\)", committed))
+    assert sorted(decls) == sorted(B.API)
+    for fn, args in decls.items():
+        n = 0 if not args.strip() else args.count(":")
+        assert n == len(B.API[fn][1]), fn
+    assert "pub bvh_node_bytes: u64" in committed and "pub scan_sphere_tests: [u64; 2]" in committed   # r01's drift
+
+
+def test_rust_shim_exports_the_crates_modules():
+    """shim/src/lib.rs keeps the nine module names of upstream's lib.rs (src/lib.rs:4-13), texture behind the same feature"""
+    lib = open(os.path.join(ROOT, "shim", "src", "lib.rs")).read()
+    mods = re.findall(r"^pub mod (\w+);", lib, flags=re.M)
+    assert mods == ["ffi", "shapes", "types", "color", "scene", "camera", "raytrace", "bmp", "serialize", "texture"]
+    assert re.search(r'#\[cfg\(feature = "skybox"\)\]\s*pub mod texture;', lib)
+    for m in mods:
+        assert os.path.exists(os.path.join(ROOT, "shim", "src", m + ".rs")), m
+    cargo = open(os.path.join(ROOT, "shim", "Cargo.toml")).read()
+    assert 'name = "libraytrace"' in cargo and 'name = "raytrace"' in cargo      # upstream's lib and bin names (Cargo.toml:14-21)
+    main = open(os.path.join(ROOT, "shim", "src", "bin", "raytrace.rs")).read()
+    assert main.count('println!("error: {}", e); return') == 3                     # src/main.rs:18,23,28
+    assert '"test_scene.txt"' in main and '"out.bmp"' in main
+    # every ffi function the hand-written modules call exists in the generated block
+    ffi = open(os.path.join(ROOT, "shim", "src", "ffi.rs")).read()
+    declared = set(re.findall(r"pub fn (rt_\w+)\(", ffi))
+    consts = set(re.findall(r"pub const (RT_\w+):", ffi))
+    for m in mods[1:]:
+        src = open(os.path.join(ROOT, "shim", "src", m + ".rs")).read()
+        for call in re.findall(r"ffi::(rt_\w+)", src):
+            assert call in declared, "%s.rs calls undeclared %s" % (m, call)
+        for c in re.findall(r"ffi::(RT_\w+)", src):
+            if c.endswith("_"):      # `ffi::RT_ACCEL_*` in a doc comment
+                continue
+            assert c in consts, "%s.rs uses undeclared %s" % (m, c)

@@ -1,6 +1,6 @@
 #!/bin/bash
 # builds lib/libraytrace_b200_<name>.so with extra -D flags for kernels.cu (kernel tuning sweeps)
-# usage: tools/build_variant.sh NAME -DRT_X=1 -DRT_Y=2
+# usage: tools/build_variant.sh NAME -DRT_X=1 -DRT_Y=2        (tools/build_variant.sh checked -DRT_CHECK_BOUNDS: see rt_device.cuh)
 NAME=$1; shift
 cd "$(dirname "$0")/../rust-raytrace_b200"
 B=build/var_$NAME; mkdir -p $B lib
