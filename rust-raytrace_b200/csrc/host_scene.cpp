@@ -275,7 +275,11 @@ void fill_scene_header(const rt_scene* s, const FlatScene& f, DeviceScene* ds) {
     ds->bvh_cmax = f.cmax;
     ds->bvh_rmin = f.rmin;
     ds->bvh_inv2rmin = 0.5 / f.rmin * (1.0 + 0x1.0p-50);
-    for (int a = 0; a < 3; a++) { ds->bvh_lo[a] = f.box_lo[a]; ds->bvh_hi[a] = f.box_hi[a]; }
+    for (int a = 0; a < 3; a++) {
+        ds->bvh_lo[a] = f.box_lo[a]; ds->bvh_hi[a] = f.box_hi[a];
+        ds->bvh_lo_f[a] = std::nextafterf((float)f.box_lo[a], -INFINITY);   // outward: at least one f32 step beyond the f64 bound
+        ds->bvh_hi_f[a] = std::nextafterf((float)f.box_hi[a], INFINITY);
+    }
     ds->bvh_qnodes = nullptr;  // set by the owner of the device buffers when f.quant
     ds->bvh_wnodes = nullptr;
     ds->_pad_bvh = 0;

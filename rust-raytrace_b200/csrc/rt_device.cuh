@@ -24,8 +24,10 @@
 
 #if defined(__CUDA_ARCH__)
 #define RT_LDG(p) __ldg(p)
+#define RT_PREFETCH_L1(p) asm volatile("prefetch.global.L1 [%0];" ::"l"(p))
 #else
 #define RT_LDG(p) (*(p))
+#define RT_PREFETCH_L1(p) ((void)0)
 #endif
 
 #ifndef RT_NS
@@ -172,7 +174,12 @@ RT_HD bool sphere_hit(const RayQ& r, double cx, double cy, double cz, double r2,
 
 // `t <= 0` rejects, so +inf and NaN are hits (src/shapes.rs:102-104)
 RT_HD bool plane_hit(const RayQ& r, V3 p, V3 n, double& t_out) {
-    double t = dot(n, p - r.o) / dot(n, r.d);
+    const double num = dot(n, p - r.o), den = dot(n, r.d);
+    // opposite signs or a zero numerator over a non-zero denominator: the quotient is negative or +-0 and `t <= 0` rejects
+    // it -- no need to form it (the f64 division is ~30 instructions; a shadow ray leaving the floor towards a light, the
+    // common case, ends here).  Everything else (same signs, a zero denominator, NaN) goes through the division as upstream.
+    if ((num < 0.0 && den > 0.0) || (num > 0.0 && den < 0.0) || (num == 0.0 && den != 0.0 && den == den)) return false;
+    double t = num / den;
     if (t <= 0.0) return false;
     t_out = t;
     return true;
@@ -305,8 +312,68 @@ RT_HD BoxRay32 make_boxray32_t(const DeviceScene& sc, V3 o, V3 d) {
     // min(E / 2 r_min, sqrt(E)) without a division or a square root: sqrt(64 * 2^-52 * St^2) = 2^-23 * St, and
     // bvh_inv2rmin = 0.5 / r_min rounded up on the host
     const double infl = fmin(E * sc.bvh_inv2rmin, St * (0x1.0p-23 * (1.0 + 0x1.0p-50)));
-    // one reciprocal per axis serves the advance and (rounded to f32) the filter
     const double da[3] = {d.x, d.y, d.z};
+    float sl[3], fa[3], fb[3];
+    uint32_t sn[3] = {0u, 0u, 0u}, sf[3] = {0u, 0u, 0u};
+    const double m = infl + St * 0x1.0p-40;
+    if (QNODES && b.enter && s < 4096.0 && dm < 1e18) {
+        // Origins of scene magnitude -- every ray but the few that start 10^4+ units out (ground-plane hits near the horizon),
+        // which take the f64 path below: the clip against the bounds of all sphere boxes and the per-ray constants of the
+        // filter are formed in f32.  (In f64 they were a quarter of the traversal kernels' instructions: three f64 reciprocals,
+        // an f64 slab test, f64 offsets; and a warp whose lanes split between "inside the bounds" and "outside" paid for
+        // two versions.)  Error budget, all absorbed by padding so that the filter stays conservative:
+        //   clip        planes widened by mg = 2^-20 St + m in space (roundings of fl32(o), of the differences: < 2^-22 St),
+        //               entry shrunk / exit grown by 2^-20 (reciprocal 2^-23, product 2^-24): t0 <= the true entry distance,
+        //               and a ray is only declared a miss when it misses the widened box;
+        //   reciprocal  fl32(1 / fl32(d)): relative error 2^-23 against 1 / d;
+        //   slope       fl32(fl32(cell) * inv): 2^-22 against cell / d; over at most 65535 cells = the extent <= 2 S that is
+        //               2^-21 S in space;
+        //   offset      g = fl32(q_org - o') (one rounding of the f64 difference; o' = o + d t0 in f64), (g -+ padq) and its
+        //               product with inv: 2^-22 relative on a distance of at most 2 S + padq: 2^-21 S in space; the rounding
+        //               of the final FMA (2^23 slope - ...) is the half cell the 0.75 cell in padq covers (the 2^23 slope
+        //               term itself is exact);
+        //   plane FMA   2^-24 on a slab distance, 2^-23 S in space.
+        // Together below 5 * 2^-22 S; the pad is S * 2^-18 = 16 * 2^-22 S (a box grows by 5e-4 units where the spheres' radii
+        // are 0.2 and up: nothing the walk can measure).  S = St + |d| t0 bounds the magnitude of o' and of the boxes.
+        const float mg = f64_to_f32_up(St * 0x1.0p-20 + m);
+        const double oa0[3] = {o.x, o.y, o.z};
+        float inv[3];
+        float te = 0.0f, tx = INFINITY;
+        for (int a = 0; a < 3; a++) {
+            inv[a] = fabs(da[a]) < 1e-30 ? (float)copysign(1e30, da[a]) : 1.0f / (float)da[a];
+            const float of = (float)oa0[a];
+            float t1 = ((sc.bvh_lo_f[a] - mg) - of) * inv[a], t2 = ((sc.bvh_hi_f[a] + mg) - of) * inv[a];
+            if (t1 > t2) { const float w = t1; t1 = t2; t2 = w; }
+            te = fmaxf(te, t1);
+            tx = fminf(tx, t2);
+        }
+        if (!(te * (1.0f - 0x1.0p-20f) <= tx * (1.0f + 0x1.0p-20f))) {  // misses the bounds (or a NaN: 0 * 1e30 cannot occur, inf - inf neither)
+            BoxRay32 none = boxray32_none();
+            return none;
+        }
+        const float t0f = te > 0.0f ? te * (1.0f - 0x1.0p-20f) : 0.0f;
+        b.t0 = (double)t0f;
+        const double oa[3] = {o.x + d.x * b.t0, o.y + d.y * b.t0, o.z + d.z * b.t0};
+        const float padf = f64_to_f32_up((St + dm * b.t0) * 0x1.0p-18 + infl);
+        for (int a = 0; a < 3; a++) {
+            const float iv = inv[a];
+            const float cellf = (float)sc.q_cell[a];
+            const float padq = padf + 0.75f * cellf * 1.0000002f;
+            const bool up = iv > 0.0f;  // the ray runs upward on this axis: it enters boxes through their lower plane
+            sl[a] = cellf * iv;
+            const float base = 8388608.0f * sl[a];  // exact: a power of two
+            const float g = (float)(sc.q_org[a] - oa[a]);
+            const float lo_off = fmaf(-(g - padq), iv, base), hi_off = fmaf(-(g + padq), iv, base);
+            fa[a] = up ? lo_off : hi_off;
+            fb[a] = up ? hi_off : lo_off;
+            sn[a] = up ? 0x7610u : 0x7632u;  // node word = lower | upper << 16 (BvhQNode)
+            sf[a] = up ? 0x7632u : 0x7610u;
+        }
+        b.sx = sl[0]; b.sy = sl[1]; b.sz = sl[2]; b.ax = fa[0]; b.ay = fa[1]; b.az = fa[2]; b.bx = fb[0]; b.by = fb[1]; b.bz = fb[2];
+        b.snx = sn[0]; b.sny = sn[1]; b.snz = sn[2]; b.sfx = sf[0]; b.sfy = sf[1]; b.sfz = sf[2];
+        return b;
+    }
+    // one reciprocal per axis serves the advance and (rounded to f32) the filter
     double rcp[3];
     float inv[3];
     for (int a = 0; a < 3; a++) {
@@ -316,7 +383,6 @@ RT_HD BoxRay32 make_boxray32_t(const DeviceScene& sc, V3 o, V3 d) {
     V3 oo = o;
     if (b.enter) {
         // f64 slab test against the sphere bounds grown by the inflation: where does the ray enter them?
-        const double m = infl + St * 0x1.0p-40;
         const double oa[3] = {o.x, o.y, o.z};
         double te = 0.0, tx = (double)INFINITY;
         bool miss = false;
@@ -342,8 +408,6 @@ RT_HD BoxRay32 make_boxray32_t(const DeviceScene& sc, V3 o, V3 d) {
     const double S = s2 + sc.bvh_cmax;
     const double pad = S * 0x1.0p-20 + infl + (s + dm * b.t0) * 0x1.0p-50;
     const double oa[3] = {oo.x, oo.y, oo.z};
-    float sl[3], fa[3], fb[3];
-    uint32_t sn[3] = {0u, 0u, 0u}, sf[3] = {0u, 0u, 0u};
     for (int a = 0; a < 3; a++) {
         const double iv = (double)inv[a];
         if (!QNODES) {
@@ -536,8 +600,7 @@ RT_HD BvhWNode widen_node(const BvhQNode* qnodes, uint32_t i) {
     w.h[1] = widen_half(p, 1, qnodes);
     return w;
 }
-// every hit child is pushed and one popped: up to three stay per visit, one visit per two binary levels (3 * ceil(95 / 2)),
-// plus the one in transit
+// up to three hit children are postponed per visit, one visit per two binary levels (3 * ceil(95 / 2)), plus one
 constexpr int BVH_STACK_WIDE = 148;
 struct TravStackWide {
     int32_t e[BVH_STACK_WIDE];
@@ -563,13 +626,22 @@ RT_HD int32_t trav_descend_wide(const DeviceScene& sc, const BoxRay32& br, int32
         const bool h2 = box_hit_q(br, b.w[0], b.w[1], b.w[2], bound, t) && c2 != TRAV_EMPTY;
         const bool h3 = box_hit_q(br, b.w[3], b.w[4], b.w[5], bound, t) && c3 != TRAV_EMPTY;
         tc.nodes++;
-        // every hit child goes on the stack and the top comes off again: no branch on which of the four were hit
-        trav_push_if(st, sp, h3, c3);
-        trav_push_if(st, sp, h2, c2);
-        trav_push_if(st, sp, h1, c1);
-        trav_push_if(st, sp, h0, c0);
-        cur = trav_pop(st, sp, bound);
+        // The first hit child (in slot order: the query is unordered) is walked next straight out of its register; the other
+        // hit children are pushed; only a visit that hits nothing pops.  (Pushing all four and popping the top put a local-
+        // memory store -> load round trip on the critical path of EVERY visit: 12 % of the kernel's stall samples sat on the
+        // popped word, as many as on the node fetch itself -- profiles/r02_v3_ncu_k_shadow_bvh.txt.)  Still no branch on
+        // which of the four were hit: three predicated stores, selects, one predicated load.
+        const bool any01 = h0 || h1, any012 = any01 || h2;
+        trav_push_if(st, sp, h3 && any012, c3);
+        trav_push_if(st, sp, h2 && any01, c2);
+        trav_push_if(st, sp, h1 && h0, c1);
+        const int32_t first = h0 ? c0 : (h1 ? c1 : (h2 ? c2 : c3));
+        if (any012 || h3) cur = first;
+        else cur = trav_pop(st, sp, bound);
     }
+    // the walk ends at a leaf: its sphere record is fetched while the other lanes of the warp finish their walks (the leaf
+    // tests of a warp run together, afterwards)
+    if (cur < 0 && cur != TRAV_EMPTY) RT_PREFETCH_L1(sc.bvh_sph + ~cur);
     return cur;
 }
 
@@ -610,6 +682,7 @@ RT_HD int32_t trav_descend(const DeviceScene& sc, const BoxRay32& br, int32_t cu
         if (__popc(__activemask()) < RT_DESCEND_MIN_LANES) break;
 #endif
     }
+    if (cur < 0 && cur != TRAV_EMPTY) RT_PREFETCH_L1(sc.bvh_sph + ~cur);  // see trav_descend_wide
     return cur;
 }
 
@@ -617,6 +690,12 @@ RT_HD int32_t trav_descend(const DeviceScene& sc, const BoxRay32& br, int32_t cu
 RT_HD float closest_bound32(double t, double t0) { return f64_to_f32_up((t - t0) * RT_BVH_TSLACK + (fabs(t) + t0) * 1e-12); }
 RT_HD float shadow_bound32(double range2, double t0) {
     if (range2 < 0.0) return INFINITY;
+    if (t0 == 0.0) {
+        // the usual case (origin inside the bounds): an upper bound of sqrt(range2) * (1 + 2e-12) without the f64 square root --
+        // range2 rounded up to f32, its f32 square root (correctly rounded: within 2^-24), two parts in 2^23 on top
+        const float r = sqrtf(f64_to_f32_up(range2));
+        return r + r * 0x1.0p-22f;
+    }
     const double r = sqrt(range2);
     return f64_to_f32_up((r - t0) * RT_BVH_TSLACK + (r + t0) * 1e-12);
 }

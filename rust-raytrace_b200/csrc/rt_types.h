@@ -113,6 +113,7 @@ struct DeviceScene {
     double bvh_rmin;  // min radius
     double bvh_inv2rmin;  // 0.5 / bvh_rmin, rounded up
     double bvh_lo[3], bvh_hi[3];  // bounds of all sphere boxes (f64): rays are advanced to this box before the f32 filter
+    float bvh_lo_f[3], bvh_hi_f[3];  // the same rounded outward to f32 (+-inf when unusable)
     const BvhQNode* bvh_qnodes;   // non-null: traverse these instead of bvh_nodes
     double q_org[3], q_cell[3];   // the grid of bvh_qnodes
     const BvhWNode* bvh_wnodes;   // non-null (only together with bvh_qnodes): shadow queries walk these
