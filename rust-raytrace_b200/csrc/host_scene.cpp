@@ -9,6 +9,9 @@
 #include <cstring>
 #include <fstream>
 #include <sstream>
+#include <thread>
+#include <vector>
+#include <algorithm>
 
 #include "../../include/raytrace_b200.h"
 #include "../../include/rt_srgb_tables.inc"
@@ -133,7 +136,77 @@ bool load_texture_file(const std::string& path, HostTexture* out, std::string* e
     return false;
 }
 
-static void choose_quantisation(const rt_scene* s, FlatScene* f, uint32_t tuning);
+static void choose_quantisation(FlatScene* f, double rmean, uint32_t tuning);
+
+// Everything of the flat form that depends on where the spheres are and how big: their scan-order records, the bounds,
+// the padding scale terms, the grid of the 32-byte nodes.  (The structure -- which object is which shape, scan order,
+// planes, materials -- is flatten_scene's.)  rt_scene_update_spheres calls it on the cached form in place.
+struct SphereBounds {
+    double centroid_lo[3], centroid_hi[3], box_lo[3], box_hi[3];
+    double cmax = 0.0, rmin = INFINITY, rsum = 0.0;
+    bool finite = true;
+    SphereBounds() { for (int a = 0; a < 3; a++) { centroid_lo[a] = INFINITY; centroid_hi[a] = -INFINITY; box_lo[a] = INFINITY; box_hi[a] = -INFINITY; } }
+    void merge(const SphereBounds& o) {
+        for (int a = 0; a < 3; a++) {
+            centroid_lo[a] = std::fmin(centroid_lo[a], o.centroid_lo[a]); centroid_hi[a] = std::fmax(centroid_hi[a], o.centroid_hi[a]);
+            box_lo[a] = std::fmin(box_lo[a], o.box_lo[a]); box_hi[a] = std::fmax(box_hi[a], o.box_hi[a]);
+        }
+        cmax = std::fmax(cmax, o.cmax); rmin = std::fmin(rmin, o.rmin); rsum += o.rsum; finite = finite && o.finite;
+    }
+};
+
+// runs body(first, last, chunk index) over [0, n) on up to 16 host threads (big scenes: a million objects per frame)
+template <typename F>
+static void parallel_chunks(size_t n, size_t max_chunks, F body) {
+    size_t chunks = n >= (1u << 16) ? std::min<size_t>(std::min<size_t>(std::max(1u, std::thread::hardware_concurrency()), 16), max_chunks) : 1;
+    if (chunks <= 1) { body((size_t)0, n, (size_t)0); return; }
+    std::vector<std::thread> th;
+    const size_t per = (n + chunks - 1) / chunks;
+    for (size_t c = 0; c < chunks; c++) {
+        const size_t lo = c * per, hi = std::min(n, lo + per);
+        if (lo >= hi) break;
+        th.emplace_back([=] { body(lo, hi, c); });
+    }
+    for (std::thread& t : th) t.join();
+}
+
+// Everything of the flat form that depends on where the spheres are and how big: their scan-order records, the bounds,
+// the padding scale terms, the grid of the 32-byte nodes.  (The structure -- which object is which shape, scan order,
+// planes, materials -- is flatten_scene's.)  rt_scene_update_spheres calls it on the cached form in place.
+static void refresh_sphere_data(const rt_scene* s, FlatScene* f, uint32_t tuning) {
+    const size_t n = f->sph.size();
+    SphereBounds part[16];
+    parallel_chunks(n, 16, [&](size_t first, size_t last, size_t c) {
+        SphereBounds b;
+        for (size_t k = first; k < last; k++) {
+            const HostObject& o = s->objects[(size_t)f->sph_obj[k]];
+            SphereRec& r = f->sph[k];
+            r.cx = o.p[0]; r.cy = o.p[1]; r.cz = o.p[2];
+            r.r2 = o.radius * o.radius;  // src/shapes.rs:63
+            const double ar = std::fabs(o.radius);
+            b.rsum += ar;
+            for (int a = 0; a < 3; a++) {
+                if (o.p[a] < b.centroid_lo[a]) b.centroid_lo[a] = o.p[a];
+                if (o.p[a] > b.centroid_hi[a]) b.centroid_hi[a] = o.p[a];
+                const double m = std::fabs(o.p[a]) + ar;
+                if (m > b.cmax) b.cmax = m;
+                if (o.p[a] - ar < b.box_lo[a]) b.box_lo[a] = o.p[a] - ar;
+                if (o.p[a] + ar > b.box_hi[a]) b.box_hi[a] = o.p[a] + ar;
+                if (!std::isfinite(m)) b.finite = false;
+            }
+            if (ar < b.rmin) b.rmin = ar;
+        }
+        part[c] = b;
+    });
+    SphereBounds all;
+    for (int c = 0; c < 16; c++) all.merge(part[c]);
+    for (int a = 0; a < 3; a++) { f->centroid_lo[a] = all.centroid_lo[a]; f->centroid_hi[a] = all.centroid_hi[a]; f->box_lo[a] = all.box_lo[a]; f->box_hi[a] = all.box_hi[a]; }
+    if (!all.finite || f->sph.empty())  // no usable bounds: rays are never advanced (t0 = 0)
+        for (int a = 0; a < 3; a++) { f->box_lo[a] = -INFINITY; f->box_hi[a] = INFINITY; }
+    f->cmax = all.cmax;
+    f->rmin = (all.rmin > 0.0 && std::isfinite(all.rmin)) ? all.rmin : 1e-300;
+    choose_quantisation(f, n ? all.rsum / (double)n : 0.0, tuning);
+}
 
 int flatten_scene(const rt_scene* s, FlatScene* f, uint32_t tuning) {
     if (!s->camera_set) { set_error("scene has no camera"); return RT_ERR_INVALID; }
@@ -144,10 +217,7 @@ int flatten_scene(const rt_scene* s, FlatScene* f, uint32_t tuning) {
     f->sph.clear(); f->sph_obj.clear(); f->planes.clear();
     f->obj_shape.assign(s->objects.size(), 0u);
     f->obj_material.assign(s->objects.size(), 0u);
-    f->sph.reserve(s->n_spheres); f->sph_obj.reserve(s->n_spheres);
-    for (int a = 0; a < 3; a++) { f->centroid_lo[a] = INFINITY; f->centroid_hi[a] = -INFINITY; f->box_lo[a] = INFINITY; f->box_hi[a] = -INFINITY; }
-    double cmax = 0.0, rmin = INFINITY;
-    bool finite = true;
+    f->sph_obj.reserve(s->n_spheres);
     for (size_t i = 0; i < s->objects.size(); i++) {
         const HostObject& o = s->objects[i];
         f->obj_material[i] = o.material;
@@ -159,30 +229,12 @@ int flatten_scene(const rt_scene* s, FlatScene* f, uint32_t tuning) {
             f->obj_shape[i] = 0x80000000u | (uint32_t)f->planes.size();
             f->planes.push_back(p);
         } else {
-            SphereRec r;
-            r.cx = o.p[0]; r.cy = o.p[1]; r.cz = o.p[2];
-            r.r2 = o.radius * o.radius;  // src/shapes.rs:63
-            f->obj_shape[i] = (uint32_t)f->sph.size();
-            f->sph.push_back(r);
+            f->obj_shape[i] = (uint32_t)f->sph_obj.size();
             f->sph_obj.push_back((int32_t)i);
-            const double ar = std::fabs(o.radius);
-            for (int a = 0; a < 3; a++) {
-                if (o.p[a] < f->centroid_lo[a]) f->centroid_lo[a] = o.p[a];
-                if (o.p[a] > f->centroid_hi[a]) f->centroid_hi[a] = o.p[a];
-                const double m = std::fabs(o.p[a]) + ar;
-                if (m > cmax) cmax = m;
-                if (o.p[a] - ar < f->box_lo[a]) f->box_lo[a] = o.p[a] - ar;
-                if (o.p[a] + ar > f->box_hi[a]) f->box_hi[a] = o.p[a] + ar;
-                if (!std::isfinite(m)) finite = false;
-            }
-            if (ar < rmin) rmin = ar;
         }
     }
-    if (!finite || f->sph.empty())  // no usable bounds: rays are never advanced (t0 = 0)
-        for (int a = 0; a < 3; a++) { f->box_lo[a] = -INFINITY; f->box_hi[a] = INFINITY; }
-    f->cmax = cmax;
-    f->rmin = (rmin > 0.0 && std::isfinite(rmin)) ? rmin : 1e-300;
-    choose_quantisation(s, f, tuning);
+    f->sph.assign(f->sph_obj.size(), SphereRec{});
+    refresh_sphere_data(s, f, tuning);
     int mc = 0;
     for (const MaterialRec& m : s->materials) {
         int c = m.kind == MAT_INDIRECT ? (int)m.samples : (m.kind == MAT_TRANSPARENT ? 2 : 1);
@@ -197,6 +249,26 @@ void scene_touch(rt_scene* s) {
         std::lock_guard<std::mutex> g(s->flat_cache.m);
         s->flat_cache.p.reset();
         s->revision++;
+    }
+    std::lock_guard<std::mutex> g(s->device_cache.m);
+    s->device_cache.entries.clear();
+}
+
+// rt_scene_update_spheres: the objects' positions / radii have just changed and nothing else.  The cached flat form (if
+// it is current) is brought up to date IN PLACE -- its vectors keep their addresses, so the page-lock on them stays -- and
+// moves to the new revision; the device copies are dropped as for any other edit.
+void scene_spheres_moved(rt_scene* s) {
+    {
+        std::lock_guard<std::mutex> g(s->flat_cache.m);
+        std::shared_ptr<FlatCache>& c = s->flat_cache.p;
+        const bool current = c && c->revision == s->revision && c->flat.obj_shape.size() == s->objects.size();
+        s->revision++;
+        if (current) {
+            refresh_sphere_data(s, &c->flat, c->node_tuning);
+            c->revision = s->revision;
+        } else {
+            c.reset();
+        }
     }
     std::lock_guard<std::mutex> g(s->device_cache.m);
     s->device_cache.entries.clear();
@@ -231,14 +303,10 @@ int flatten_scene_cached(const rt_scene* s, uint32_t tuning, std::shared_ptr<Fla
 // when 2.25 cells stay under a quarter of the mean radius on every axis and the bounds are small enough for the f32
 // filter terms (2^23 * cell / |d|, |d| clamped at 1e-30) not to overflow.  RT_TUNE_NODES_F32 / RT_TUNE_NODES_Q16 override the
 // size test (A-B measurements, parity tests); unusable bounds always mean f32 nodes.
-static void choose_quantisation(const rt_scene* s, FlatScene* f, uint32_t tuning) {
+static void choose_quantisation(FlatScene* f, double rmean, uint32_t tuning) {
     f->quant = false;
     for (int a = 0; a < 3; a++) { f->q_org[a] = 0.0; f->q_cell[a] = 0.0; }
     if (f->sph.empty()) return;
-    double rsum = 0.0;
-    for (const HostObject& o : s->objects)
-        if (!o.is_plane) rsum += std::fabs(o.radius);
-    const double rmean = rsum / (double)f->sph.size();
     double cell_max = 0.0, ext_max = 0.0;
     for (int a = 0; a < 3; a++) {
         const double lo = f->box_lo[a], hi = f->box_hi[a];
@@ -378,14 +446,25 @@ int rt_scene_add_spheres(rt_scene* s, uint64_t n, const double* cr, const uint32
 int rt_scene_update_spheres(rt_scene* s, uint64_t first_object, uint64_t n, const double* cr) {
     if (!s || (n && !cr)) { set_error("rt_scene_update_spheres: null argument"); return RT_ERR_INVALID; }
     if (first_object > s->objects.size() || n > s->objects.size() - first_object) { set_error("rt_scene_update_spheres: object range out of bounds"); return RT_ERR_INVALID; }
-    for (uint64_t i = 0; i < n; i++)
-        if (s->objects[first_object + i].is_plane) { set_error("rt_scene_update_spheres: object " + std::to_string(first_object + i) + " is a plane"); return RT_ERR_INVALID; }
-    scene_touch(s);
-    for (uint64_t i = 0; i < n; i++) {
-        HostObject& o = s->objects[first_object + i];
-        o.p[0] = cr[4 * i]; o.p[1] = cr[4 * i + 1]; o.p[2] = cr[4 * i + 2];
-        o.radius = cr[4 * i + 3];
+    // the range must hold spheres only: checked through the flat form's structure when it is current (4 bytes per object
+    // instead of the 72-byte HostObject), else on the objects
+    uint64_t bad = n;
+    {
+        std::lock_guard<std::mutex> g(s->flat_cache.m);
+        const std::shared_ptr<FlatCache>& c = s->flat_cache.p;
+        const bool current = c && c->revision == s->revision && c->flat.obj_shape.size() == s->objects.size();
+        for (uint64_t i = 0; i < n && bad == n; i++)
+            if (current ? (c->flat.obj_shape[first_object + i] & 0x80000000u) != 0u : s->objects[first_object + i].is_plane) bad = i;
     }
+    if (bad != n) { set_error("rt_scene_update_spheres: object " + std::to_string(first_object + bad) + " is a plane"); return RT_ERR_INVALID; }
+    parallel_chunks((size_t)n, 16, [&](size_t first, size_t last, size_t) {
+        for (size_t i = first; i < last; i++) {
+            HostObject& o = s->objects[first_object + i];
+            o.p[0] = cr[4 * i]; o.p[1] = cr[4 * i + 1]; o.p[2] = cr[4 * i + 2];
+            o.radius = cr[4 * i + 3];
+        }
+    });
+    scene_spheres_moved(s);
     return RT_OK;
 }
 int rt_scene_add_plane(rt_scene* s, const double* point, const double* normal, uint32_t material) {

@@ -119,6 +119,8 @@ int parse_scene_text(const char* text, size_t len, rt_scene* scene, std::string*
 // Called BEFORE anything changes the objects, materials or skybox faces of a scene: drops the cache entry (and with it the
 // page-lock on the vectors about to be reallocated) and bumps the revision.
 void scene_touch(rt_scene* s);
+// called AFTER the positions / radii of sphere objects changed and nothing else: refreshes the cached flat form in place
+void scene_spheres_moved(rt_scene* s);
 // returns RT_OK or RT_ERR_INVALID (missing camera/background/skybox face)
 int flatten_scene(const rt_scene* s, FlatScene* out, uint32_t tuning = 0);
 // the same through the scene's cache: flattens on the first call after a change, validates every time
