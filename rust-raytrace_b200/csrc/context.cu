@@ -139,6 +139,7 @@ private:
     std::vector<std::pair<Counters*, size_t>> free_;
 };
 PinnedPool g_pinned;
+void (*g_drop_cached_multi)() = nullptr;  // set where the cache of rt_multi objects is defined (end of this file)
 const DeviceAllocator g_cache_allocator = {[](void** p, size_t bytes) { return g_cache.alloc(p, bytes); }, [](void* p) { g_cache.release(p); }};
 
 template <typename T>
@@ -619,7 +620,11 @@ int frame_begin(rt_context* c) {
 
 extern "C" {
 
-void rt_release_cached_memory(void) { g_cache.trim(); g_pinned.trim(); }
+void rt_release_cached_memory(void) {
+    if (g_drop_cached_multi) g_drop_cached_multi();  // the rt_multi objects kept by rt_render_multi hold queues on every device
+    g_cache.trim();
+    g_pinned.trim();
+}
 
 int rt_device_count(void) {
     int n = 0;
@@ -1217,16 +1222,128 @@ const void* rt_multi_frame_device(const rt_multi* m, int index) {
     return m->frames[index];
 }
 
+}  // extern "C"
+
+namespace {
+
+// A context made for an earlier frame of the same scene handle is brought up to date: the device copy of the scene's
+// current revision (uploaded and built now if the scene changed since), camera and background.  Returns RT_ERR_UNSUPPORTED
+// when the context cannot serve the scene as it is now (frame size, branching factor or light count differ from what its
+// queues were sized for): the caller makes a new one.
+int ctx_rebind_scene(rt_context* c, const rt_scene* s) {
+    CUDA_TRY(cudaSetDevice(c->device));
+    FrameParams fp{};
+    int rc = make_frame_params(s, &c->opts, &fp);
+    if (rc != RT_OK) return rc;
+    if (std::memcmp(&fp, &c->fp, sizeof fp) != 0) { set_error("frame parameters changed"); return RT_ERR_UNSUPPORTED; }
+    std::shared_ptr<DeviceSceneHolder> h;
+    bool fresh = false;
+    rc = acquire_device_scene(s, c->opts.accel, c->opts.tuning, c->device, c->stream, &h, &fresh);
+    if (rc != RT_OK) return rc;
+    if (h->use_bvh != c->use_bvh || h->ds.max_children != c->ds.max_children || h->ds.n_lights != c->ds.n_lights) {
+        set_error("scene structure changed");
+        return RT_ERR_UNSUPPORTED;
+    }
+    c->scene = h;
+    uint8_t* keep_out = c->final_out;
+    c->ds = h->ds;
+    c->ds.camera = s->camera;
+    c->ds.bg_kind = s->bg_kind;
+    std::memcpy(c->ds.bg_color, s->bg_color, sizeof c->ds.bg_color);
+    c->final_out = keep_out;
+    c->host_levels = (c->opts.tuning & RT_TUNE_HOST_LEVELS) != 0 || h->dd_overflowed.load();
+    c->stats.bvh_build_ms = fresh ? h->bvh_ms : 0.0;
+    c->stats.n_bvh_nodes = c->ds.n_bvh_nodes;
+    c->stats.bvh_node_bytes = !c->use_bvh ? 0 : (c->ds.bvh_qnodes ? sizeof(BvhQNode) : sizeof(BvhNode));
+    return RT_OK;
+}
+
+// rt_render_multi is one-shot by contract, but a caller rendering frame after frame (the reference's main in a loop) would
+// pay for eight threads, eight contexts and their streams / events per frame (0.9 ms of a 5 ms frame at four GPUs).  The
+// last few rt_multi objects are kept, keyed by (scene handle, options, devices, gather), and re-bound to the scene's current
+// revision on the next call.  rt_release_cached_memory and rt_scene_free drop them.
+struct MultiCache {
+    struct Entry {
+        const rt_scene* scene;
+        rt_render_opts opts;
+        std::vector<int> devices;
+        int gather;
+        rt_multi* m;
+    };
+    std::mutex mu;
+    std::vector<Entry> entries;
+    static bool same_opts(const rt_render_opts& a, const rt_render_opts& b) {
+        rt_render_opts x = a, y = b;
+        x.device = y.device = 0; x.rank = y.rank = 0; x.world = y.world = 1;  // set per device by rt_multi
+        return std::memcmp(&x, &y, sizeof x) == 0;
+    }
+    rt_multi* take(const rt_scene* s, const rt_render_opts& o, const std::vector<int>& devs, int gather) {
+        std::lock_guard<std::mutex> g(mu);
+        for (size_t i = 0; i < entries.size(); i++)
+            if (entries[i].scene == s && entries[i].gather == gather && entries[i].devices == devs && same_opts(entries[i].opts, o)) {
+                rt_multi* m = entries[i].m;
+                entries.erase(entries.begin() + i);
+                return m;
+            }
+        return nullptr;
+    }
+    void put(const rt_scene* s, const rt_render_opts& o, const std::vector<int>& devs, int gather, rt_multi* m) {
+        rt_multi* evict = nullptr;
+        {
+            std::lock_guard<std::mutex> g(mu);
+            entries.push_back({s, o, devs, gather, m});
+            if (entries.size() > 2) { evict = entries.front().m; entries.erase(entries.begin()); }
+        }
+        delete evict;
+    }
+    void drop(const rt_scene* s) {  // s == nullptr: everything
+        std::vector<rt_multi*> dead;
+        {
+            std::lock_guard<std::mutex> g(mu);
+            for (size_t i = 0; i < entries.size();)
+                if (!s || entries[i].scene == s) { dead.push_back(entries[i].m); entries.erase(entries.begin() + i); }
+                else i++;
+        }
+        for (rt_multi* m : dead) delete m;
+    }
+};
+MultiCache g_multi_cache;
+struct MultiCacheHook {
+    MultiCacheHook() {
+        rt::g_scene_free_hook = [](const rt_scene* s) { g_multi_cache.drop(s); };
+        g_drop_cached_multi = [] { g_multi_cache.drop(nullptr); };
+    }
+} g_multi_cache_hook;
+
+}  // namespace
+
+extern "C" {
+
 int rt_render_multi(const rt_scene* s, const rt_render_opts* o, int n_devices, const int* devices, int gather, uint8_t* bgr_rows, int32_t* primary_ids,
                     rt_stats* stats) {
-    rt_multi* m = nullptr;
-    int rc = rt_multi_create(s, o, n_devices, devices, gather, &m);
-    if (rc != RT_OK) return rc;
-    rc = rt_multi_render(m, bgr_rows, primary_ids, stats);
-    std::string keep = rc != RT_OK ? get_error() : "";
-    rt_multi_destroy(m);
-    if (rc != RT_OK) set_error(keep);
-    return rc;
+    if (!s || !o || n_devices < 1) { set_error("rt_render_multi: bad argument"); return RT_ERR_INVALID; }
+    std::vector<int> devs;
+    for (int i = 0; i < n_devices; i++) devs.push_back(devices ? devices[i] : i);
+    const int mode = gather == RT_GATHER_AUTO ? RT_GATHER_DIRECT : gather;
+    rt_multi* m = g_multi_cache.take(s, *o, devs, mode);
+    if (m) {
+        m->scene = s;
+        const int rc = m->run([m](int i) { return ctx_rebind_scene(m->ctx[i], m->scene); });
+        if (rc != RT_OK) { delete m; m = nullptr; }  // cannot serve the scene as it is now: make a new one
+    }
+    if (!m) {
+        const int rc = rt_multi_create(s, o, n_devices, devices, gather, &m);
+        if (rc != RT_OK) return rc;
+    }
+    const int rc = rt_multi_render(m, bgr_rows, primary_ids, stats);
+    if (rc != RT_OK) {
+        const std::string keep = get_error();
+        delete m;
+        set_error(keep);
+        return rc;
+    }
+    g_multi_cache.put(s, *o, devs, mode, m);
+    return RT_OK;
 }
 
 // ---------------------------------------------------------------------------------------------------------

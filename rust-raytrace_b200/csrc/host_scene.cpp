@@ -244,6 +244,8 @@ int flatten_scene(const rt_scene* s, FlatScene* f, uint32_t tuning) {
     return RT_OK;
 }
 
+void (*g_scene_free_hook)(const rt_scene*) = nullptr;
+
 void scene_touch(rt_scene* s) {
     {
         std::lock_guard<std::mutex> g(s->flat_cache.m);
@@ -393,7 +395,10 @@ const char* rt_last_error(void) { return get_error(); }
 const char* rt_version(void) { return "raytrace_b200 0.1 (sm_100a)"; }
 
 rt_scene* rt_scene_new(void) { return new rt_scene(); }
-void rt_scene_free(rt_scene* s) { delete s; }
+void rt_scene_free(rt_scene* s) {
+    if (s && rt::g_scene_free_hook) rt::g_scene_free_hook(s);  // context.cu: nothing cached may keep pointing at the scene
+    delete s;
+}
 
 static int add_material(rt_scene* s, int32_t kind, const double* diffuse, const double* specular, double exponent, const double* ambient, double ior,
                         uint32_t samples) {

@@ -119,6 +119,9 @@ int parse_scene_text(const char* text, size_t len, rt_scene* scene, std::string*
 // Called BEFORE anything changes the objects, materials or skybox faces of a scene: drops the cache entry (and with it the
 // page-lock on the vectors about to be reallocated) and bumps the revision.
 void scene_touch(rt_scene* s);
+// set by context.cu: called by rt_scene_free before the scene goes away (the library keeps multi-GPU render state of the
+// last rt_render_multi calls, which refers to the scene it was made for)
+extern void (*g_scene_free_hook)(const rt_scene*);
 // called AFTER the positions / radii of sphere objects changed and nothing else: refreshes the cached flat form in place
 void scene_spheres_moved(rt_scene* s);
 // returns RT_OK or RT_ERR_INVALID (missing camera/background/skybox face)

@@ -91,3 +91,43 @@ def test_real_multi_gpu_frame(gpu, scenes, gather):
             assert np.array_equal(fr.ids, whole.ids)
             assert fr.stats["rays_total"] == whole.stats["rays_total"]
         mc.close()
+
+
+def test_render_multi_keeps_its_state_between_calls_and_follows_scene_edits(gpu, scenes):
+    """rt_render_multi is one-shot for the caller; the library keeps the rt_multi it made (threads, contexts, streams) for the
+    next call with the same scene handle / options / devices and re-binds it to the scene's current revision: moved spheres are
+    re-uploaded, a changed structure (new light) makes a new one, a freed scene drops it."""
+    import ctypes as C
+    desc = scenes.random_spheres(2000, 17, 25.0, 160, 100)
+    sc = gpu.Scene(desc)
+    kw = dict(max_depth=4, seed=7, accel=gpu.ACCEL_BVH)
+    one = gpu.raytrace.render(sc, **kw)
+    a = gpu.raytrace.render_multi(sc, [0, 0, 0], gather=gpu.GATHER_DIRECT, **kw)
+    b = gpu.raytrace.render_multi(sc, [0, 0, 0], gather=gpu.GATHER_DIRECT, **kw)      # kept state
+    for fr in (a, b):
+        _same_frame(fr.rows, one.rows, 160)
+        assert np.array_equal(fr.ids, one.ids) and fr.stats["rays_total"] == one.stats["rays_total"]
+    assert a.stats["bvh_build_ms"] == 0 and b.stats["bvh_build_ms"] == 0             # the scene's device copy came from `one`
+    # the spheres move: same handle, new revision
+    data = np.array(desc["objects"][1]["data"])
+    data[:, 1] += 0.75
+    sc.update_spheres(1, data)
+    moved = gpu.raytrace.render_multi(sc, [0, 0, 0], gather=gpu.GATHER_DIRECT, **kw)
+    ref = gpu.raytrace.render(sc, **kw)
+    _same_frame(moved.rows, ref.rows, 160)
+    assert np.array_equal(moved.ids, ref.ids) and (moved.ids != one.ids).mean() > 0.01
+    assert moved.stats["bvh_build_ms"] > 0                                            # re-uploaded and rebuilt by the re-bound contexts
+    # a new light changes what the queues were sized for
+    L = gpu.lib()
+    assert L.rt_scene_add_light_point(sc.handle, (C.c_double * 3)(5.0, 30.0, 5.0), (C.c_double * 3)(0.5, 0.5, 0.5)) == 0
+    lit = gpu.raytrace.render_multi(sc, [0, 0, 0], gather=gpu.GATHER_DIRECT, **kw)
+    ref2 = gpu.raytrace.render(sc, **kw)
+    _same_frame(lit.rows, ref2.rows, 160)
+    assert lit.stats["rays_shadow"] == ref2.stats["rays_shadow"] > moved.stats["rays_shadow"]
+    # another scene (the first one freed: whatever was kept for it is dropped with it)
+    del sc
+    sc2 = gpu.Scene(scenes.random_spheres(500, 3, 12.0, 160, 100))
+    x = gpu.raytrace.render_multi(sc2, [0, 0, 0], gather=gpu.GATHER_DIRECT, **kw)
+    y = gpu.raytrace.render(sc2, **kw)
+    _same_frame(x.rows, y.rows, 160)
+    gpu.release_cached_memory()
