@@ -865,9 +865,12 @@ static void scan_attr_once() {
 #ifndef RT_HEAVY_DIV
 #define RT_HEAVY_DIV 8192u
 #endif
+#ifndef RT_HEAVY_MIN
+#define RT_HEAVY_MIN 32
+#endif
 static uint32_t heavy_walks(const DeviceScene& sc) {
     const uint32_t w = sc.n_spheres / RT_HEAVY_DIV;
-    return w < 32u ? 32u : (w > 4096u ? 4096u : w);
+    return w < (uint32_t)RT_HEAVY_MIN ? (uint32_t)RT_HEAVY_MIN : (w > 4096u ? 4096u : w);
 }
 
 static void l_closest(cudaStream_t st, const DeviceScene& sc, bool bvh, RayQueue q, uint32_t first, uint32_t n, Counters* counters, int sm_count,
