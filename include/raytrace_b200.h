@@ -264,6 +264,21 @@ RT_API int rt_render_multi(const rt_scene*, const rt_render_opts*, int n_devices
  * ids: object index or -1; t: hit distance (+inf on miss); normal: shape normal as upstream returns it. */
 RT_API int rt_trace_rays(const rt_scene*, const rt_render_opts*, uint64_t n, const double* origin_dir, int32_t* ids, double* t,
                          double* normal);
+/* Scene::intersect over a list of spheres (object i = sphere i) for callers that may not allocate device memory.
+ * NO COUNTERPART IN THE REFERENCE: added for code under CUDA graph capture, tight
+ * serving loops and harnesses that forbid cudaMalloc.  A variant of the linear-scan closest-hit kernel whose scratch (packed
+ * sphere records, work cursor) is a static __device__ array of RT_NOALLOC_SCRATCH_BYTES that every GPU which loads the
+ * library holds until exit.  All four pointers are DEVICE memory on `device`: spheres as (x, y, z, radius) (16-byte
+ * aligned), rays as origin xyz + direction xyz, ids (object index or -1), dev_t (hit distance, +inf on a miss; may be
+ * NULL).  Results are bit-identical to rt_trace_rays in RT_FP_STRICT on a scene holding just these spheres.
+ * Calls cudaMalloc / cudaFree / stream or event creation never, and does not synchronise: two kernels are queued on
+ * `cuda_stream` (a cudaStream_t; NULL = the default stream).  The first call on a device looks up the array's address
+ * (cudaGetSymbolAddress): make one call before capturing a graph.  More than RT_NOALLOC_MAX_SPHERES spheres:
+ * RT_ERR_INVALID, nothing is launched.  Every call on a device shares the array (each call rewrites what it reads and
+ * zeroes its own counters in stream order), so calls that overlap on the GPU race: keep them on one stream. */
+enum { RT_NOALLOC_MAX_SPHERES = 65536, RT_NOALLOC_SCRATCH_BYTES = 2097408 /* 65536 * 32 + 256 */ };
+RT_API int rt_intersect_spheres_noalloc(int device, void* cuda_stream, const double* dev_center_xyz_radius, uint64_t n_spheres,
+                                        const double* dev_origin_dir, uint64_t n_rays, int32_t* dev_ids, double* dev_t);
 /* Camera::project for a batch of normalised image positions (src/camera.rs:77-79, :110-121); ray i uses the
  * counter-RNG key of (seed, pixel i, sample 0, camera sample 0). */
 RT_API int rt_project(const rt_scene*, const rt_render_opts*, uint64_t n, const double* pos_xy, double* origin_dir);

@@ -13,6 +13,7 @@ FP_STRICT, FP_FAST = 0, 1
 GATHER_AUTO, GATHER_DIRECT, GATHER_PEER, GATHER_NCCL = 0, 1, 2, 3
 ANTIALIAS_FROM_SCENE = 0xFFFFFFFF
 TUNE_NODES_F32, TUNE_NODES_Q16, TUNE_MORTON_AXIS, TUNE_BINARY_SHADOW, TUNE_HOST_LEVELS = 1, 2, 4, 8, 16
+NOALLOC_MAX_SPHERES, NOALLOC_SCRATCH_BYTES = 65536, 65536 * 32 + 256   # rt_intersect_spheres_noalloc's static scratch
 
 
 class RenderOpts(C.Structure):
@@ -125,6 +126,7 @@ API = {
     "rt_multi_gather_used": (C.c_int, [C.c_void_p]),
     "rt_render_multi": (C.c_int, [C.c_void_p, C.POINTER(RenderOpts), C.c_int, C.POINTER(C.c_int), C.c_int, _u8p, _i32p, C.POINTER(Stats)]),
     "rt_trace_rays": (C.c_int, [C.c_void_p, C.POINTER(RenderOpts), C.c_uint64, _dp, _i32p, _dp, _dp]),
+    "rt_intersect_spheres_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
     "rt_project": (C.c_int, [C.c_void_p, C.POINTER(RenderOpts), C.c_uint64, _dp, _dp]),
     "rt_quantize_bgr": (C.c_int, [_dp, C.c_uint64, _u8p, C.c_int]),
     "rt_measure_peaks": (C.c_int, [C.c_int, C.POINTER(Peaks)]),

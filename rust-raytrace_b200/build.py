@@ -67,6 +67,7 @@ def build(force=False, verbose=False):
         ("bvh_build.o", "bvh_build.cu", [nvcc] + NVCC_COMMON + ["-fmad=false"]),
         ("context.o", "context.cu", [nvcc] + NVCC_COMMON),
         ("peaks.o", "peaks.cu", [nvcc] + NVCC_COMMON + ["-fmad=true"]),
+        ("noalloc.o", "noalloc.cu", [nvcc] + NVCC_COMMON + ["-DRT_NS=strict", "-fmad=false"]),
         ("host_scene.o", "host_scene.cpp", ["g++"] + HOST_FLAGS),
         ("serialize.o", "serialize.cpp", ["g++"] + HOST_FLAGS),
     ]

@@ -8,4 +8,4 @@ NV="nvcc -std=c++17 -O3 -lineinfo -Xcompiler -fPIC,-fvisibility=hidden,-ffp-cont
 $NV -DRT_NS=strict -fmad=false "$@" -c csrc/kernels.cu -o $B/ks.o &
 $NV -DRT_NS=fast -fmad=true "$@" -c csrc/kernels.cu -o $B/kf.o &
 wait
-nvcc -shared -o lib/libraytrace_b200_$NAME.so $B/ks.o $B/kf.o build/bvh_build.o build/context.o build/peaks.o build/host_scene.o build/serialize.o -gencode arch=compute_100a,code=sm_100a -cudart static -Xlinker --no-undefined -lpthread -ldl -lrt && echo built $NAME
+nvcc -shared -o lib/libraytrace_b200_$NAME.so $B/ks.o $B/kf.o build/bvh_build.o build/context.o build/peaks.o build/noalloc.o build/host_scene.o build/serialize.o -gencode arch=compute_100a,code=sm_100a -cudart static -Xlinker --no-undefined -lpthread -ldl -lrt && echo built $NAME
