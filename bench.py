@@ -490,7 +490,9 @@ def measure(name, args, D, steps, warmup, hw, want_e2e=True, want_cpu=True, gath
     line = {"value": rays_all / (dev_ms * 1e-3) / 1e6, "ms_per_step": dev_ms / steps, "wall_ms_per_step": wall_ms / steps,
             "rays_per_step": rays_all / steps, "gpu_launches": int(launches_all), "clocks": clocks, "steps": steps, "warmup": max(3, warmup),
             "config": workload_config(name, w, h, aa, info["n_objects"], info["n_lights"]),
-            "bvh_build_ms": ctx.create_stats["bvh_build_ms"], "wavefront": "host-driven levels" if host_levels else "device-driven (no count read-backs)"}
+            "bvh_build_ms": ctx.create_stats["bvh_build_ms"], "wavefront": "host-driven levels" if host_levels else
+            ("device-driven (no count read-backs); each level's shadow queries traced on a second stream beside the next level"
+             if WORKLOADS[name]["accel"] == "bvh" else "device-driven (no count read-backs)")}
     if world > 1:
         line["config"]["multi_gpu"] = ("image row bands (4 rows) interleaved over ranks, scene replicated; " +
                                        ("every rank's resolve kernel stores its rows into rank 0's frame over NVLink (CUDA IPC peer memory)"

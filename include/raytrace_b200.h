@@ -143,8 +143,10 @@ enum {
     RT_TUNE_NODES_Q16 = 2u,       /* BVH: force the 32-byte grid nodes wherever the bounds allow a grid at all */
     RT_TUNE_MORTON_AXIS = 4u,     /* BVH build: scale the Morton grid per axis instead of by the longest extent */
     RT_TUNE_BINARY_SHADOW = 8u,   /* shadow queries walk the binary nodes instead of the four-wide ones */
-    RT_TUNE_HOST_LEVELS = 16u     /* the host reads every wavefront level's ray count back before it launches the next
+    RT_TUNE_HOST_LEVELS = 16u,    /* the host reads every wavefront level's ray count back before it launches the next
                                      level (no device-driven tail); results identical */
+    RT_TUNE_SERIAL_SHADOW = 32u   /* device-driven frames: trace the shadow queue in one launch at the end of the frame instead
+                                     of level by level on a second stream beside the level loop */
 };
 RT_API void rt_render_opts_default(rt_render_opts* opts);
 

@@ -390,6 +390,10 @@ struct rt_context {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_counts = nullptr;
     rt_stats stats{};
     cudaStream_t own_stream = nullptr;
+    cudaStream_t stream2 = nullptr;      // device-driven frames: shadow segments run here beside the level loop (frame_device_driven)
+    uint32_t* heavy2 = nullptr;          // the heavy-ray list of the launches on stream2
+    std::vector<cudaEvent_t> ev_seg;     // [level]: that level's shade pass (and its mark) are done
+    cudaEvent_t ev_join = nullptr;       // every shadow segment of the batch is done
     bool profiling = false;
     std::vector<cudaEvent_t> prof_events;       // pool, two per timed launch
     std::vector<int> prof_class;                // class of launch i (events 2i, 2i+1)
@@ -410,6 +414,7 @@ struct rt_context {
     ~rt_context() {
         cudaSetDevice(device);
         if (stream) cudaStreamSynchronize(stream);  // blocks go back to the cache: nothing may still be using them
+        if (stream2) cudaStreamSynchronize(stream2);
         for (void* p : allocs) g_cache.release(p);
         if (frame_own) cudaFree(frame_own);  // exported to other processes: not recycled through the cache
         if (frame_ipc) cudaIpcCloseMemHandle(frame_ipc);
@@ -418,7 +423,10 @@ struct rt_context {
         if (ev1) cudaEventDestroy(ev1);
         if (ev_counts) cudaEventDestroy(ev_counts);
         for (cudaEvent_t e : prof_events) cudaEventDestroy(e);
+        for (cudaEvent_t e : ev_seg) cudaEventDestroy(e);
+        if (ev_join) cudaEventDestroy(ev_join);
         scene.reset();
+        if (stream2) cudaStreamDestroy(stream2);
         if (own_stream) cudaStreamDestroy(own_stream);
     }
 };
@@ -460,7 +468,7 @@ int flush_shadow(rt_context* c) {
     if (c->shadow_queued) {
         c->prof_begin(3);
         c->k->shadow(c->stream, c->ds, c->use_bvh, c->shadowq, c->shadow_queued, c->accum, c->counters, c->sm_count, c->heavy, nullptr,
-                     &c->counters->lc[LC_SHARED], true);
+                     &c->counters->lc[LC_SHARED], true, nullptr);
         c->prof_end();
         c->stats.kernel_launches += c->use_bvh ? 2 : 1;  // shadow (+ heavy scan)
         c->shadow_queued = 0;
@@ -571,6 +579,13 @@ int frame_device_driven(rt_context* c, bool* overflowed) {
         c->prof_end();
         c->stats.kernel_launches += 1;
         uint64_t bound = n;
+        // The shadow queries of level d are traced on a second stream while the main stream goes on with level d + 1: the two
+        // traversal launches have the same resident grid, so the later one's CTAs move in as the earlier one's run out of rays
+        // -- the tail of every launch (a few long walks holding the GPU while the other lanes have nothing left to pull) is
+        // filled with the other launch's rays.  Each segment [mark[d], mark[d + 1]) of the shadow queue is pinned by a
+        // one-thread kernel between the two shade passes that append to it.  Not while profiling (the per-class times are
+        // taken launch by launch on one stream) and not for the linear scan (no resident grid, no tail).
+        const bool overlap = c->use_bvh && c->stream2 && !c->profiling && !(c->opts.tuning & RT_TUNE_SERIAL_SHADOW);
         for (uint32_t d = 0; d < n_levels; d++) {
             const bool last = d + 1 >= n_levels;
             RayQueue& in = c->levels[d];
@@ -585,12 +600,25 @@ int frame_device_driven(rt_context* c, bool* overflowed) {
             c->prof_end();
             c->stats.kernel_launches += c->use_bvh ? 3 : 2;
             bound = std::min<uint64_t>(cap, bound * branch);
+            if (overlap) {
+                c->k->mark(c->stream, &c->counters->shadow_count, &c->counters->shadow_mark[d + 1]);
+                CUDA_TRY(cudaEventRecord(c->ev_seg[d], c->stream));
+                CUDA_TRY(cudaStreamWaitEvent(c->stream2, c->ev_seg[d], 0));
+                c->k->shadow(c->stream2, c->ds, true, c->shadowq, c->shadowq.cap, c->accum, c->counters, c->sm_count, c->heavy2,
+                             &c->counters->shadow_mark[d + 1], &c->counters->lc[LC_SHADOW_SEG + d], false, &c->counters->shadow_mark[d]);
+                c->stats.kernel_launches += 3;
+            }
         }
-        c->prof_begin(3);
-        c->k->shadow(c->stream, c->ds, c->use_bvh, c->shadowq, c->shadowq.cap, c->accum, c->counters, c->sm_count, c->heavy, &c->counters->shadow_count,
-                     &c->counters->lc[LC_SHADOW], false);
-        c->prof_end();
-        c->stats.kernel_launches += c->use_bvh ? 2 : 1;
+        if (overlap) {
+            CUDA_TRY(cudaEventRecord(c->ev_join, c->stream2));
+            CUDA_TRY(cudaStreamWaitEvent(c->stream, c->ev_join, 0));
+        } else {
+            c->prof_begin(3);
+            c->k->shadow(c->stream, c->ds, c->use_bvh, c->shadowq, c->shadowq.cap, c->accum, c->counters, c->sm_count, c->heavy, &c->counters->shadow_count,
+                         &c->counters->lc[LC_SHADOW], false, nullptr);
+            c->prof_end();
+            c->stats.kernel_launches += c->use_bvh ? 2 : 1;
+        }
         CUDA_TRY(cudaMemcpyAsync(&c->counters_host[slot], c->counters, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
     }
     CUDA_TRY(cudaEventRecord(c->ev_counts, c->stream));
@@ -696,6 +724,19 @@ int rt_context_create(const rt_scene* s, const rt_render_opts* o, rt_context** o
         c->allocs.push_back(c->heavy);
         // the split-scan scratch behind the list must start zeroed; its users leave it zeroed (k_heavy_scan)
         if (cudaMemsetAsync(c->heavy + HEAVY_CAP, 0, sizeof(HeavyScratch), c->stream) != cudaSuccess) { set_error("cudaMemsetAsync failed"); return fail(RT_ERR_CUDA); }
+        if (!(o->tuning & RT_TUNE_SERIAL_SHADOW)) {  // second stream, its heavy list and the events of frame_device_driven's overlap
+            if ((rc = dev_alloc(&c->heavy2, HEAVY_WORDS)) != RT_OK) return fail(rc);
+            c->allocs.push_back(c->heavy2);
+            if (cudaMemsetAsync(c->heavy2 + HEAVY_CAP, 0, sizeof(HeavyScratch), c->stream) != cudaSuccess) { set_error("cudaMemsetAsync failed"); return fail(RT_ERR_CUDA); }
+            if (cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess) { set_error("cudaStreamCreate failed"); return fail(RT_ERR_CUDA); }
+            c->ev_seg.reserve(fp.max_depth + 2);
+            for (uint32_t d = 0; d < fp.max_depth + 2; d++) {
+                cudaEvent_t e = nullptr;
+                if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) { set_error("cudaEventCreate failed"); return fail(RT_ERR_CUDA); }
+                c->ev_seg.push_back(e);
+            }
+            if (cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess) { set_error("cudaEventCreate failed"); return fail(RT_ERR_CUDA); }
+        }
     }
     const uint64_t dd_batch = std::max<uint64_t>(cap / branch, 32);
     if (g_pinned.get(&c->counters_host, &c->n_host_slots, (size_t)((c->total_paths + dd_batch - 1) / dd_batch) + 1) != cudaSuccess) { set_error("cudaMallocHost failed"); return fail(RT_ERR_CUDA); }

@@ -425,10 +425,16 @@ __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_closest_bvh(
 // same kernel.
 template <bool QNODES, bool WIDE = false>
 __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_shadow_bvh(const __grid_constant__ DeviceScene sc, ShadowQueue sq, uint32_t n, double* accum, Counters* counters,
-                                                               uint32_t* heavy, uint32_t heavy_walks, const uint32_t* n_dev, uint32_t lc_index) {
+                                                               uint32_t* heavy, uint32_t heavy_walks, const uint32_t* n_dev, uint32_t lc_index,
+                                                               const uint32_t* first_dev) {
     __shared__ TravSmem sm;
-    __shared__ uint32_t n_s;  // see k_closest_bvh
-    if (threadIdx.x == 0) n_s = n_dev ? (*n_dev < sq.cap ? *n_dev : sq.cap) : n;
+    __shared__ uint32_t n_s, first_s;  // see k_closest_bvh; first_s: where this launch's segment of the queue starts
+    if (threadIdx.x == 0) {
+        const uint32_t end = n_dev ? (*n_dev < sq.cap ? *n_dev : sq.cap) : n;
+        const uint32_t first = first_dev ? (*first_dev < end ? *first_dev : end) : 0u;
+        first_s = first;
+        n_s = end - first;
+    }
     __syncthreads();
     uint32_t range_next = FETCH_NONE;
     uint32_t walks = 0;
@@ -450,7 +456,7 @@ __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_shadow_bvh(c
             const uint32_t li = warp_fetch(idle, &counters->lc[lc_index].cursor, range_next, fetch_chunk(n_now));
             if (!active) {
                 if (li < n_now) {
-                    ray = li;
+                    ray = first_s + li;
                     RT_CHECK(ray < sq.cap);
                     const RayQ r = make_rayq(v3(sq.ox[ray], sq.oy[ray], sq.oz[ray]), v3(sq.dx[ray], sq.dy[ray], sq.dz[ray]));
                     const double range2 = sq.r2[ray];
@@ -902,8 +908,11 @@ static void l_shade(cudaStream_t st, const DeviceScene& sc, const FrameParams& f
     else k_shade<true><<<grid, SHADE_THREADS, 0, st>>>(sc, fp, in, first, n, out, out_count, sq, sq_count, overflow, accum, ids, n_dev, tile_cursor);
 }
 
+__global__ void k_mark(const uint32_t* src, uint32_t* dst) { *dst = *src; }
+static void l_mark(cudaStream_t st, const uint32_t* src, uint32_t* dst) { k_mark<<<1, 1, 0, st>>>(src, dst); }
+
 static void l_shadow(cudaStream_t st, const DeviceScene& sc, bool bvh, ShadowQueue sq, uint32_t n, double* accum, Counters* counters, int sm_count,
-                     uint32_t* heavy, const uint32_t* n_dev, LaunchCursor* lc, bool reset_lc) {
+                     uint32_t* heavy, const uint32_t* n_dev, LaunchCursor* lc, bool reset_lc, const uint32_t* first_dev) {
     if (!n) return;
     if (bvh) {
         if (reset_lc) cudaMemsetAsync(lc, 0, sizeof(LaunchCursor), st);
@@ -911,9 +920,9 @@ static void l_shadow(cudaStream_t st, const DeviceScene& sc, bool bvh, ShadowQue
         uint32_t want = div_up(n, BVH_THREADS);
         uint32_t grid = (uint32_t)sm_count * (uint32_t)RT_BVH_MIN_BLOCKS;
         if (want < grid) grid = want;
-        if (sc.bvh_qnodes && sc.bvh_wnodes) k_shadow_bvh<true, true><<<grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters, heavy, heavy_walks(sc), n_dev, lci);
-        else if (sc.bvh_qnodes) k_shadow_bvh<true><<<grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters, heavy, heavy_walks(sc), n_dev, lci);
-        else k_shadow_bvh<false><<<grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters, heavy, heavy_walks(sc), n_dev, lci);
+        if (sc.bvh_qnodes && sc.bvh_wnodes) k_shadow_bvh<true, true><<<grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters, heavy, heavy_walks(sc), n_dev, lci, first_dev);
+        else if (sc.bvh_qnodes) k_shadow_bvh<true><<<grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters, heavy, heavy_walks(sc), n_dev, lci, first_dev);
+        else k_shadow_bvh<false><<<grid, BVH_THREADS, 0, st>>>(sc, sq, n, accum, counters, heavy, heavy_walks(sc), n_dev, lci, first_dev);
         RayQueue none{};
         k_heavy_scan<true><<<(uint32_t)sm_count * 4u, HEAVY_THREADS, 0, st>>>(sc, none, sq, 0u, accum, counters, heavy, lci);
     } else {
@@ -942,7 +951,7 @@ static void l_quantize(cudaStream_t st, const double* avg, const double* rgb, ui
     k_quantize<<<div_up(n, 256), 256, 0, st>>>(avg, rgb, n, bgr);
 }
 
-static const KernelTable g_table = {l_primary, l_closest, l_shade, l_shadow, l_resolve, l_hit_normals, l_project, l_quantize};
+static const KernelTable g_table = {l_primary, l_closest, l_shade, l_shadow, l_mark, l_resolve, l_hit_normals, l_project, l_quantize};
 
 }  // namespace RT_NS
 

@@ -16,6 +16,7 @@ struct LaunchCursor {
 };
 constexpr int LC_SHADOW = 64;  // Counters.lc index of the frame's shadow launch (0..63: closest-hit pass of that level)
 constexpr int LC_SHARED = 65;  // host-driven launches: one cursor, reset before each launch
+constexpr int LC_SHADOW_SEG = 66;  // + d: the shadow launch of wavefront level d's segment (device-driven frames, RT_TUNE_SERIAL_SHADOW off)
 struct Counters {
     // whole frame
     uint32_t overflow;      // a queue append was dropped -> the frame is redone host-driven (which slices and cannot overflow)
@@ -28,8 +29,9 @@ struct Counters {
     uint32_t shadow_count;     // shadow queue length
     uint32_t _pad1;
     uint32_t level_count[64];  // ray-queue length per wavefront level
-    LaunchCursor lc[66];
+    LaunchCursor lc[66 + 64];
     uint32_t shade_cursor[64];  // tile cursor of the shade pass of level d (device-driven frames)
+    uint32_t shadow_mark[66];   // shadow queue length before level d's shade pass ([0] stays 0): segment d = [mark[d], mark[d + 1])
 };
 constexpr uint32_t HEAVY_CAP = 1u << 16;  // entries of the heavy-ray list (rays beyond it simply keep traversing)
 // Behind the list: scratch for splitting a few heavy rays over many CTAs (k_heavy_scan).  Zeroed once when allocated;
@@ -64,8 +66,11 @@ struct KernelTable {
                   ShadowQueue sq, uint32_t* sq_count, uint32_t* overflow, double* accum, int32_t* ids, int sm_count, const uint32_t* n_dev,
                   uint32_t* tile_cursor);
     // shadow queries; unoccluded rays add their pending contribution to the pixel
+    // first_dev != nullptr (BVH only, with n_dev): the launch traces queue entries [*first_dev, *n_dev) -- one level's segment
     void (*shadow)(cudaStream_t, const DeviceScene&, bool bvh, ShadowQueue sq, uint32_t n, double* accum, Counters* counters, int sm_count,
-                   uint32_t* heavy, const uint32_t* n_dev, LaunchCursor* lc, bool reset_lc);
+                   uint32_t* heavy, const uint32_t* n_dev, LaunchCursor* lc, bool reset_lc, const uint32_t* first_dev);
+    // *dst = *src on the stream (one thread): pins a queue length between two launches that both append to the queue
+    void (*mark)(cudaStream_t, const uint32_t* src, uint32_t* dst);
     // average, quantise (threshold table) and pack BGR rows with padding; 128-bit stores.  final_rows == false: `out` is
     // the shard's own framebuffer (local row order); true: `out` is a whole-frame buffer in BMP row order (possibly another
     // device's memory over NVLink peer access) and every local row goes to its place in it

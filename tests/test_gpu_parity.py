@@ -254,8 +254,13 @@ def test_device_driven_and_host_driven_frames_agree(gpu, orc, scenes):
     ref = orc.OracleScene(desc).render(max_depth=6, seed=2)
     dd = gpu.raytrace.render(sc, max_depth=6, seed=2)
     hl = gpu.raytrace.render(sc, max_depth=6, seed=2, tuning=gpu.TUNE_HOST_LEVELS)
+    # the default frame also traces each level's shadow queries on a second stream beside the next level; RT_TUNE_SERIAL_SHADOW
+    # keeps them for one launch at the end of the frame
+    ss = gpu.raytrace.render(sc, max_depth=6, seed=2, tuning=gpu.TUNE_SERIAL_SHADOW)
     assert dd.stats["host_levels"] == 0 and dd.stats["device_driven_overflows"] == 0 and hl.stats["host_levels"] == 1
-    for fr in (dd, hl):
+    assert ss.stats["host_levels"] == 0 and ss.stats["kernel_launches"] < dd.stats["kernel_launches"]
+    assert (dd.rows != ss.rows).mean() < 1e-5
+    for fr in (dd, hl, ss):
         assert np.array_equal(fr.ids, ref["ids"])
         assert fr.stats["rays_total"] == ref["stats"]["rays"]
         for k in ("rays_primary", "rays_secondary", "rays_shadow", "paths"):
@@ -296,6 +301,8 @@ def test_device_driven_and_host_driven_frames_agree(gpu, orc, scenes):
     fr2 = gpu.raytrace.render(gpu.Scene(desc2), max_depth=4, seed=5, max_rays_in_flight=8192)
     assert fr2.stats["host_levels"] == 0 and fr2.stats["rays_total"] == ref2["stats"]["rays"]
     assert np.array_equal(fr2.ids, ref2["ids"])
+    fr3 = gpu.raytrace.render(gpu.Scene(desc2), max_depth=4, seed=5, max_rays_in_flight=8192, tuning=gpu.TUNE_SERIAL_SHADOW)
+    assert fr3.stats["rays_total"] == fr2.stats["rays_total"] and (fr3.rows != fr2.rows).mean() < 1e-5
     d = np.abs(fr2.rows.astype(np.int16) - ref2["bgr"].astype(np.int16))
     assert d.max() <= 1 and (d == 0).mean() >= 0.999
 
