@@ -47,10 +47,91 @@ Box leaf_box(const SphereRec& s) {
     return b;
 }
 
+// child boxes of every node from its links, bottom-up (iterative post-order from the root)
+void fill_boxes(EmuScene& e, const std::vector<int32_t>& c0, const std::vector<int32_t>& c1) {
+    const size_t n_nodes = c0.size();
+    std::vector<Box> nb(n_nodes);
+    std::vector<std::pair<int32_t, int>> st;
+    st.push_back({0, 0});
+    while (!st.empty()) {
+        auto [node, phase] = st.back();
+        if (phase == 0) {
+            st.back().second = 1;
+            if (c0[node] >= 0) st.push_back({c0[node], 0});
+            if (c1[node] >= 0) st.push_back({c1[node], 0});
+        } else {
+            st.pop_back();
+            Box b0 = c0[node] < 0 ? leaf_box(e.bvh_sph[~c0[node]]) : nb[c0[node]];
+            Box b1 = c1[node] < 0 ? leaf_box(e.bvh_sph[~c1[node]]) : nb[c1[node]];
+            BvhNode& nd = e.nodes[node];
+            for (int a = 0; a < 3; a++) {
+                nd.lo0[a] = b0.lo[a]; nd.hi0[a] = b0.hi[a];
+                nd.lo1[a] = b1.lo[a]; nd.hi1[a] = b1.hi[a];
+                nb[node].lo[a] = std::fmin(b0.lo[a], b1.lo[a]);
+                nb[node].hi[a] = std::fmax(b0.hi[a], b1.hi[a]);
+            }
+            nd.c0 = c0[node]; nd.c1 = c1[node];
+        }
+    }
+}
+
+// EXPERIMENT (EMU_BVH_BUILDER=sah): full-sweep SAH, top-down, one sphere per leaf -- an upper bound on what a better tree than
+// the LBVH could save in node visits.  Same node format, so every walk of rt_device.cuh runs on it unchanged.
+void build_bvh_sah(EmuScene& e) {
+    const uint32_t n = (uint32_t)e.flat.sph.size();
+    std::vector<Box> pb(n);
+    for (uint32_t i = 0; i < n; i++) pb[i] = leaf_box(e.flat.sph[i]);
+    std::vector<uint32_t> idx(n);
+    for (uint32_t i = 0; i < n; i++) idx[i] = i;
+    e.nodes.assign(n - 1, BvhNode{});
+    std::vector<int32_t> c0(n - 1), c1(n - 1);
+    std::vector<uint32_t> leaf_order; leaf_order.reserve(n);
+    auto area = [](const Box& b) {
+        const double x = (double)b.hi[0] - b.lo[0], y = (double)b.hi[1] - b.lo[1], z = (double)b.hi[2] - b.lo[2];
+        return x * y + y * z + z * x;
+    };
+    auto grow = [](Box& a, const Box& b) { for (int k = 0; k < 3; k++) { a.lo[k] = std::fmin(a.lo[k], b.lo[k]); a.hi[k] = std::fmax(a.hi[k], b.hi[k]); } };
+    const Box empty{{INFINITY, INFINITY, INFINITY}, {-INFINITY, -INFINITY, -INFINITY}};
+    uint32_t next_node = 0;
+    struct Job { uint32_t lo, hi; int32_t* link; };
+    std::vector<Job> jobs;
+    int32_t root_link = 0;
+    jobs.push_back({0, n, &root_link});
+    std::vector<double> right_area;
+    while (!jobs.empty()) {
+        const Job j = jobs.back(); jobs.pop_back();
+        const uint32_t cnt = j.hi - j.lo;
+        if (cnt == 1) { *j.link = ~(int32_t)leaf_order.size(); leaf_order.push_back(idx[j.lo]); continue; }
+        double best = INFINITY; int best_axis = 0; uint32_t best_split = j.lo + cnt / 2;
+        for (int a = 0; a < 3; a++) {
+            std::sort(idx.begin() + j.lo, idx.begin() + j.hi, [&](uint32_t x, uint32_t y) { return pb[x].lo[a] + pb[x].hi[a] < pb[y].lo[a] + pb[y].hi[a]; });
+            right_area.assign(cnt, 0.0);
+            Box r = empty;
+            for (uint32_t k = cnt; k-- > 1;) { grow(r, pb[idx[j.lo + k]]); right_area[k] = area(r); }
+            Box l = empty;
+            for (uint32_t k = 1; k < cnt; k++) {
+                grow(l, pb[idx[j.lo + k - 1]]);
+                const double cost = area(l) * k + right_area[k] * (cnt - k);
+                if (cost < best) { best = cost; best_axis = a; best_split = j.lo + k; }
+            }
+        }
+        const int a = best_axis;
+        std::sort(idx.begin() + j.lo, idx.begin() + j.hi, [&](uint32_t x, uint32_t y) { return pb[x].lo[a] + pb[x].hi[a] < pb[y].lo[a] + pb[y].hi[a]; });
+        const uint32_t node = next_node++;
+        *j.link = (int32_t)node;
+        jobs.push_back({best_split, j.hi, &c1[node]});   // child 0 is popped first: leaves come out in depth-first order
+        jobs.push_back({j.lo, best_split, &c0[node]});
+    }
+    e.bvh_sph.resize(n); e.bvh_obj.resize(n);
+    for (uint32_t i = 0; i < n; i++) { e.bvh_sph[i] = e.flat.sph[leaf_order[i]]; e.bvh_obj[i] = e.flat.sph_obj[leaf_order[i]]; }
+    fill_boxes(e, c0, c1);
+}
+
 // the device build's algorithm, serially: same Morton codes, same (code, index) order, same Karras nodes
 void build_bvh(EmuScene& e, bool morton_per_axis) {
     const uint32_t n = (uint32_t)e.flat.sph.size();
     if (n == 0) return;
+    if (n > 1 && getenv("EMU_BVH_BUILDER") && std::string(getenv("EMU_BVH_BUILDER")) == "sah") { build_bvh_sah(e); return; }
     double inv[3];
     morton_scale(e.flat.centroid_lo, e.flat.centroid_hi, inv, morton_per_axis);
     std::vector<std::pair<uint64_t, uint32_t>> keyed(n);
@@ -74,30 +155,7 @@ void build_bvh(EmuScene& e, bool morton_per_axis) {
     e.nodes.assign(n - 1, BvhNode{});
     std::vector<int32_t> c0(n - 1), c1(n - 1);
     for (uint32_t i = 0; i + 1 < n; i++) lbvh_node(keys.data(), (int)n, (int)i, c0[i], c1[i]);
-    std::vector<Box> nb(n - 1);
-    // iterative post-order from the root
-    std::vector<std::pair<int32_t, int>> st;
-    st.push_back({0, 0});
-    while (!st.empty()) {
-        auto [node, phase] = st.back();
-        if (phase == 0) {
-            st.back().second = 1;
-            if (c0[node] >= 0) st.push_back({c0[node], 0});
-            if (c1[node] >= 0) st.push_back({c1[node], 0});
-        } else {
-            st.pop_back();
-            Box b0 = c0[node] < 0 ? leaf_box(e.bvh_sph[~c0[node]]) : nb[c0[node]];
-            Box b1 = c1[node] < 0 ? leaf_box(e.bvh_sph[~c1[node]]) : nb[c1[node]];
-            BvhNode& nd = e.nodes[node];
-            for (int a = 0; a < 3; a++) {
-                nd.lo0[a] = b0.lo[a]; nd.hi0[a] = b0.hi[a];
-                nd.lo1[a] = b1.lo[a]; nd.hi1[a] = b1.hi[a];
-                nb[node].lo[a] = std::fmin(b0.lo[a], b1.lo[a]);
-                nb[node].hi[a] = std::fmax(b0.hi[a], b1.hi[a]);
-            }
-            nd.c0 = c0[node]; nd.c1 = c1[node];
-        }
-    }
+    fill_boxes(e, c0, c1);
 }
 
 int make_scene(const rt_scene* s, int accel, uint32_t tuning, EmuScene* e) {
