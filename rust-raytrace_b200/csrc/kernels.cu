@@ -636,6 +636,11 @@ __global__ void __launch_bounds__(HEAVY_THREADS) k_heavy_scan(const __grid_const
 #ifndef RT_SHADE_MIN_BLOCKS
 #define RT_SHADE_MIN_BLOCKS 4
 #endif
+#ifndef RT_SHADE_PREFETCH
+#define RT_SHADE_PREFETCH 1  // LOOP: prefetch the next tile's ray record into L2 while this tile emits its rays.  Measured
+#endif                       // (profiles/r02_v5_shade_prefetch_ab.txt): shade class 4.57 -> 4.23 ms (10k), 3.55 -> 3.36 ms (1M); into L1
+                             // instead, or with level 0 looping too: the same times (r02_v5_shade_prefetch2_ab.txt)
+#define RT_PREFETCH_L2(p) asm volatile("prefetch.global.L2 [%0];" ::"l"(p))
 #ifndef RT_SHADE_WAVES
 #define RT_SHADE_WAVES 1  // LOOP grid = SMs x resident CTAs x this (tiles come off a cursor: the resident grid is enough)
 #endif
@@ -716,6 +721,19 @@ __global__ void __launch_bounds__(SHADE_THREADS, RT_SHADE_MIN_BLOCKS) k_shade(co
             cta_base[par][0] = bs; cta_base[par][1] = bc;
         }
         __syncthreads();
+#if RT_SHADE_PREFETCH
+        if (LOOP) {  // the next tile's record is on its way from HBM while this tile's rays are being emitted
+            const uint64_t nx = (uint64_t)tile_s[par ^ 1u] * SHADE_THREADS + threadIdx.x;
+            if (nx < nn) {
+                const uint32_t i = first + (uint32_t)nx;
+                RT_PREFETCH_L2(in.ox + i); RT_PREFETCH_L2(in.oy + i); RT_PREFETCH_L2(in.oz + i);
+                RT_PREFETCH_L2(in.dx + i); RT_PREFETCH_L2(in.dy + i); RT_PREFETCH_L2(in.dz + i);
+                RT_PREFETCH_L2(in.tr + i); RT_PREFETCH_L2(in.tg + i); RT_PREFETCH_L2(in.tb + i);
+                RT_PREFETCH_L2(in.sig + i); RT_PREFETCH_L2(in.key + i); RT_PREFETCH_L2(in.hit_t + i);
+                RT_PREFETCH_L2(in.pixel + i); RT_PREFETCH_L2(in.meta + i); RT_PREFETCH_L2(in.hit_id + i);
+            }
+        }
+#endif
         uint32_t sbase = cta_base[par][0], cbase = cta_base[par][1];
 #pragma unroll
         for (int k = 0; k < SHADE_WARPS; k++)
