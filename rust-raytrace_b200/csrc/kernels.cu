@@ -22,6 +22,11 @@ namespace RT_NS {
 
 constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_TILE = 1024;  // spheres per shared-memory tile (32 KB), double buffered
+#define RT_PREFETCH_L2(p) asm volatile("prefetch.global.L2 [%0];" ::"l"(p))
+#ifndef RT_RAY_PREFETCH
+#define RT_RAY_PREFETCH 8192  // k_closest_bvh refills prefetch the queue records this many rays ahead of the cursor (0: off): 5.01 -> 4.97 ms (10k),
+                              // 5.24 -> 5.19 ms (1M), the same at 2048 and 32768; the shadow kernel (reserved blocks) did not gain: profiles/r02_v5_ray_prefetch_ab.txt
+#endif
 constexpr int BVH_THREADS = 128;
 #ifndef RT_SHADE_THREADS
 #define RT_SHADE_THREADS 128
@@ -366,6 +371,13 @@ __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_closest_bvh(
             const uint32_t li = warp_fetch_each(idle, &counters->lc[lc_index].cursor);
             const uint32_t n_now = n_s;
             if (!active) {
+#if RT_RAY_PREFETCH
+                if (li + RT_RAY_PREFETCH < n_now) {  // the rays some warp will take RT_RAY_PREFETCH refills from now: HBM -> L2
+                    const uint32_t pf = first + li + RT_RAY_PREFETCH;
+                    RT_PREFETCH_L2(q.ox + pf); RT_PREFETCH_L2(q.oy + pf); RT_PREFETCH_L2(q.oz + pf);
+                    RT_PREFETCH_L2(q.dx + pf); RT_PREFETCH_L2(q.dy + pf); RT_PREFETCH_L2(q.dz + pf);
+                }
+#endif
                 if (li < n_now) {
                     ray = first + li;
                     RT_CHECK(ray < q.cap);
@@ -640,7 +652,6 @@ __global__ void __launch_bounds__(HEAVY_THREADS) k_heavy_scan(const __grid_const
 #define RT_SHADE_PREFETCH 1  // LOOP: prefetch the next tile's ray record into L2 while this tile emits its rays.  Measured
 #endif                       // (profiles/r02_v5_shade_prefetch_ab.txt): shade class 4.57 -> 4.23 ms (10k), 3.55 -> 3.36 ms (1M); into L1
                              // instead, or with level 0 looping too: the same times (r02_v5_shade_prefetch2_ab.txt)
-#define RT_PREFETCH_L2(p) asm volatile("prefetch.global.L2 [%0];" ::"l"(p))
 #ifndef RT_SHADE_WAVES
 #define RT_SHADE_WAVES 1  // LOOP grid = SMs x resident CTAs x this (tiles come off a cursor: the resident grid is enough)
 #endif
