@@ -2,7 +2,7 @@
 """bench.py -- measures the tracing hot path on N B200s of one node (contract: task prompt, section 4).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl ours|reference] [--fp strict|fast]
-                    [--gather peer|nccl] [--no-also] [--no-e2e] [--no-cpu-baseline]
+                    [--gather peer|nccl] [--frames-in-flight F] [--no-also] [--no-e2e] [--no-cpu-baseline]
 
 A step = one frame of the workload: primary-ray generation -> wavefront (closest-hit, shade, shadow kernels) -> resolve,
 on a device-resident scene (inputs already in HBM).  With N > 1 the frame is sharded by interleaved row bands, one process
@@ -14,7 +14,10 @@ variant beside the headline (`also.gather_nccl`).  Strong scaling of one frame.
 metric  Mrays/s, primary + secondary + shadow: 1 ray = one Scene::intersect call upstream (src/scene.rs:247), counted
         exactly from the wavefront queue lengths.
 value   whole-job rays of K frames / device time of K frames (CUDA events on the launching stream, max over ranks); no
-        per-launch profiling events inside the timed region (kernel-class times come from a separate pass).
+        per-launch profiling events inside the timed region (kernel-class times come from a separate pass).  The frames
+        are independent (upstream's frame loop run for an animation), so --frames-in-flight F (default 2) of them are queued
+        at once per GPU, one rt_context each (rt_context_render_begin / _end): on a shard the deep wavefront levels are bound
+        by the latency of their longest walks and the next frame fills those gaps.  `frame_ms_alone` is one frame by itself.
 e2e     the same metric through the user-facing call with HOST buffers, every step: the caller moves its spheres
         (rt_scene_update_spheres from host memory) -> rt_render / rt_render_multi (flatten, upload, device BVH build on
         every GPU, trace) -> frame in pinned host memory.  e2e_warm: the same call on an unchanged scene (the device copy
@@ -374,6 +377,10 @@ def measure(name, args, D, steps, warmup, hw, want_e2e=True, want_cpu=True, gath
     ctx = rt.Context(scene, **opts)
     stream = torch.cuda.current_stream()
     ctx.set_stream(stream.cuda_stream)
+    # frames in flight (peer gather / one GPU): one context per frame slot, each on its own stream; frame k is queued on slot
+    # k % F before frame k - F + 1 is collected.  The nccl gather pipelines its own way (below) with one context.
+    F = max(1, int(getattr(args, "frames_in_flight", 1))) if (world == 1 or gather == "peer") else 1
+    ctxs = [ctx] + [rt.Context(scene, **opts) for _ in range(F - 1)]
     bytewidth = ctx.bytewidth
     frame_bytes = h * bytewidth
     fb_ptr, fb_bytes = ctx.framebuffer_ptr()
@@ -382,14 +389,16 @@ def measure(name, args, D, steps, warmup, hw, want_e2e=True, want_cpu=True, gath
     frame0 = None         # rank 0: device view of the assembled frame
     nccl = None
     if world > 1 and gather == "peer":
-        handle = None
-        if rank == 0:
-            p = ctx.frame_create()
-            handle = ctx.frame_export()
-            frame0 = device_view(torch, p, frame_bytes)
-        handle = D.broadcast_bytes(handle, 64)
-        if rank != 0:
-            ctx.frame_import(handle)
+        for i, c in enumerate(ctxs):   # one whole-frame buffer on rank 0 per frame slot
+            handle = None
+            if rank == 0:
+                p = c.frame_create()
+                handle = c.frame_export()
+                if i == 0:
+                    frame0 = device_view(torch, p, frame_bytes)
+            handle = D.broadcast_bytes(handle, 64)
+            if rank != 0:
+                c.frame_import(handle)
     elif world > 1:
         nccl = dict(final=torch.empty(frame_bytes, dtype=torch.uint8, device="cuda"), gathered=torch.empty(world * fb_bytes, dtype=torch.uint8, device="cuda"),
                     local=device_view(torch, fb_ptr, fb_bytes), stream=torch.cuda.Stream(), ev_traced=torch.cuda.Event(), ev_gathered=torch.cuda.Event(),
@@ -420,7 +429,12 @@ def measure(name, args, D, steps, warmup, hw, want_e2e=True, want_cpu=True, gath
 
     for _ in range(max(3, warmup)):
         step()
+    for c in ctxs[1:]:
+        c.render()
     drain()
+    D.barrier()
+    # one frame by itself (no other frame in flight): what a caller waiting for this frame sees
+    alone = sorted(ctx.render()["render_ms"] for _ in range(5))[2]
     D.barrier()
     sampler = ClockSampler(D.local_rank)
     if rank == 0:
@@ -431,11 +445,26 @@ def measure(name, args, D, steps, warmup, hw, want_e2e=True, want_cpu=True, gath
     D.barrier()
     t0 = time.perf_counter()
     ev0.record(stream)
-    for _ in range(steps):
-        st = step()
+    def account(st):
+        nonlocal rays, launches, host_levels
         rays += st["rays_total"]
         launches += st["kernel_launches"] + (1 if nccl else 0)
         host_levels |= st["host_levels"]
+
+    if F == 1:
+        for _ in range(steps):
+            account(step())
+    else:
+        queued = []
+        for k in range(steps):
+            c = ctxs[k % F]
+            if len(queued) == F:
+                account(queued.pop(0).render_end())
+            c.render_begin()
+            queued.append(c)
+        for c in queued:
+            account(c.render_end())
+        torch.cuda.synchronize()   # every slot's stream (render_end has already waited for each frame's last event)
     drain()
     ev1.record(stream)
     D.barrier()
@@ -487,7 +516,9 @@ def measure(name, args, D, steps, warmup, hw, want_e2e=True, want_cpu=True, gath
                                       "f64 atomic adds into a pixel only"}
         D.barrier()
 
+    (alone,) = D.reduce([alone], "MAX")
     line = {"value": rays_all / (dev_ms * 1e-3) / 1e6, "ms_per_step": dev_ms / steps, "wall_ms_per_step": wall_ms / steps,
+            "frames_in_flight": F, "frame_ms_alone": alone,
             "rays_per_step": rays_all / steps, "gpu_launches": int(launches_all), "clocks": clocks, "steps": steps, "warmup": max(3, warmup),
             "config": workload_config(name, w, h, aa, info["n_objects"], info["n_lights"]),
             "bvh_build_ms": ctx.create_stats["bvh_build_ms"], "wavefront": "host-driven levels" if host_levels else
@@ -510,8 +541,9 @@ def measure(name, args, D, steps, warmup, hw, want_e2e=True, want_cpu=True, gath
         if rank == 0:
             line["gather_nccl"] = sub
 
-    ctx.close()
-    del ctx
+    for c in ctxs:
+        c.close()
+    del ctx, ctxs
 
     # ---- end to end through the user-facing call with host buffers
     if want_e2e:
@@ -627,6 +659,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--fp", default="strict", choices=["strict", "fast"])
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"])
+    ap.add_argument("--frames-in-flight", type=int, default=2, help="frames queued at once per GPU (one context each); 1 = one frame at a time")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-also", action="store_true")

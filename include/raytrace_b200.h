@@ -201,6 +201,14 @@ RT_API int rt_context_create(const rt_scene*, const rt_render_opts*, rt_context*
 RT_API void rt_context_destroy(rt_context*);
 /* traces the shard and leaves quantised BGR rows (local_rows x bytewidth) in the context's device framebuffer */
 RT_API int rt_context_render(rt_context*, rt_stats* stats);
+/* The same frame in two halves, for a caller that keeps several frames in flight (one context each: upstream's frame loop,
+ * src/main.rs:39-59, run for an animation): _begin queues every launch of the frame on the context's streams and returns
+ * while the GPU works (a context whose scene needs host-driven levels traces the frame before it returns); _end waits for
+ * the frame, reads the counts, retraces the frame level by level if a queue overflowed, and fills `stats`.  Exactly one
+ * _end per _begin; nothing else may be called on the context in between.  On a shard the deep wavefront levels are bound by
+ * the latency of their longest walks, not by throughput: a second frame in flight fills those gaps. */
+RT_API int rt_context_render_begin(rt_context*);
+RT_API int rt_context_render_end(rt_context*, rt_stats* stats);
 RT_API int rt_context_stats(const rt_context*, rt_stats* stats);
 /* device pointer of the local framebuffer (local_rows*bytewidth bytes), e.g. to wrap as a tensor for the NCCL gather */
 RT_API void* rt_context_framebuffer(rt_context*);

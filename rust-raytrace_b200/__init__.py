@@ -126,6 +126,15 @@ class Context:
         B.check(self._lib, self._lib.rt_context_render(self._h, C.byref(st)))
         return st.as_dict()
 
+    def render_begin(self):
+        """Queue one frame and return while the GPU works; `render_end` collects it (several contexts = several frames in flight)."""
+        B.check(self._lib, self._lib.rt_context_render_begin(self._h))
+
+    def render_end(self):
+        st = Stats()
+        B.check(self._lib, self._lib.rt_context_render_end(self._h, C.byref(st)))
+        return st.as_dict()
+
     def framebuffer_ptr(self):
         return int(self._lib.rt_context_framebuffer(self._h)), int(self._lib.rt_context_framebuffer_bytes(self._h))
 

@@ -106,6 +106,8 @@ API = {
     "rt_context_create": (C.c_int, [C.c_void_p, C.POINTER(RenderOpts), C.POINTER(C.c_void_p)]),
     "rt_context_destroy": (None, [C.c_void_p]),
     "rt_context_render": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
+    "rt_context_render_begin": (C.c_int, [C.c_void_p]),
+    "rt_context_render_end": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
     "rt_context_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
     "rt_context_framebuffer": (C.c_void_p, [C.c_void_p]),
     "rt_context_framebuffer_bytes": (C.c_size_t, [C.c_void_p]),

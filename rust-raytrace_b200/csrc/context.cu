@@ -376,6 +376,10 @@ struct rt_context {
     Counters* counters = nullptr;       // device
     Counters* counters_host = nullptr;  // pinned: n_host_slots records (one per primary batch of a device-driven frame)
     size_t n_host_slots = 0;
+    size_t final_slot = 0;        // counters_host[final_slot]: the record copied out behind the resolve kernel (frame-wide counters)
+    size_t dd_batches = 0;        // primary batches of the device-driven frame in flight
+    bool in_flight = false;       // rt_context_render_begin has queued a frame that rt_context_render_end has not collected yet
+    bool in_flight_dd = false;    // ... and it is a device-driven one (its counts are still to be read)
     double* accum = nullptr;
     int32_t* ids = nullptr;
     uint8_t* framebuffer = nullptr;
@@ -559,8 +563,7 @@ int frame_host_levels(rt_context* c) {
 // levels and cannot overflow.  The context then stays host-driven.
 // Returns RT_OK with *overflowed set when the frame has to be redone.
 // ---------------------------------------------------------------------------------------------------------
-int frame_device_driven(rt_context* c, bool* overflowed) {
-    *overflowed = false;
+int frame_device_driven(rt_context* c) {
     const uint32_t n_levels = (uint32_t)c->levels.size();
     const uint64_t cap = c->levels[0].cap;
     const uint64_t branch = (uint64_t)std::max(1, c->ds.max_children);
@@ -621,17 +624,22 @@ int frame_device_driven(rt_context* c, bool* overflowed) {
         }
         CUDA_TRY(cudaMemcpyAsync(&c->counters_host[slot], c->counters, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
     }
-    CUDA_TRY(cudaEventRecord(c->ev_counts, c->stream));
-    CUDA_TRY(cudaEventSynchronize(c->ev_counts));
-    for (size_t b = 0; b < slot; b++) {
+    c->dd_batches = slot;
+    return RT_OK;
+}
+
+// after the frame's last event: the per-batch records of a device-driven frame -> stats; true when a queue overflowed
+bool dd_collect(rt_context* c) {
+    const uint32_t n_levels = (uint32_t)c->levels.size();
+    for (size_t b = 0; b < c->dd_batches; b++) {
         const Counters& h = c->counters_host[b];
-        if (h.overflow) { *overflowed = true; return RT_OK; }
+        if (h.overflow) return true;
         c->stats.paths += h.level_count[0];
         c->stats.rays_primary += h.level_count[0];
         for (uint32_t d = 1; d < n_levels; d++) c->stats.rays_secondary += h.level_count[d];
         c->stats.rays_shadow += h.shadow_count;
     }
-    return RT_OK;
+    return false;
 }
 
 int frame_begin(rt_context* c) {
@@ -739,7 +747,8 @@ int rt_context_create(const rt_scene* s, const rt_render_opts* o, rt_context** o
         }
     }
     const uint64_t dd_batch = std::max<uint64_t>(cap / branch, 32);
-    if (g_pinned.get(&c->counters_host, &c->n_host_slots, (size_t)((c->total_paths + dd_batch - 1) / dd_batch) + 1) != cudaSuccess) { set_error("cudaMallocHost failed"); return fail(RT_ERR_CUDA); }
+    c->final_slot = (size_t)((c->total_paths + dd_batch - 1) / dd_batch);
+    if (g_pinned.get(&c->counters_host, &c->n_host_slots, c->final_slot + 1) != cudaSuccess) { set_error("cudaMallocHost failed"); return fail(RT_ERR_CUDA); }
     if (cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_counts, cudaEventDisableTiming) != cudaSuccess) { set_error("cudaEventCreate failed"); return fail(RT_ERR_CUDA); }
     std::memset(&c->stats, 0, sizeof c->stats);
@@ -756,43 +765,66 @@ int rt_context_create(const rt_scene* s, const rt_render_opts* o, rt_context** o
 
 void rt_context_destroy(rt_context* c) { delete c; }
 
-int rt_context_render(rt_context* c, rt_stats* stats) {
+namespace {
+// resolve + the frame-wide counters + the frame's closing event, queued behind whatever traced the frame
+int frame_finish(rt_context* c) {
+    c->prof_begin(4);
+    c->k->resolve(c->stream, c->ds, c->fp, c->accum, c->final_out ? c->final_out : c->framebuffer, c->bytewidth, c->final_out != nullptr);
+    c->prof_end();
+    c->stats.kernel_launches += 1;
+    CUDA_TRY(cudaMemcpyAsync(&c->counters_host[c->final_slot], c->counters, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaEventRecord(c->ev1, c->stream));
+    return RT_OK;
+}
+}  // namespace
+
+int rt_context_render_begin(rt_context* c) {
     if (!c) { set_error("null context"); return RT_ERR_INVALID; }
+    if (c->in_flight) { set_error("rt_context_render_begin: the previous frame has not been collected (rt_context_render_end)"); return RT_ERR_INVALID; }
     CUDA_TRY(cudaSetDevice(c->device));
-    const FrameParams& fp = c->fp;
     c->stats.kernel_launches = 0;
     c->prof_class.clear();
     CUDA_TRY(cudaEventRecord(c->ev0, c->stream));
     int rc = frame_begin(c);
     if (rc != RT_OK) return rc;
-    bool redo = false;
     if (!c->host_levels) {
-        rc = frame_device_driven(c, &redo);
-        if (rc != RT_OK) return rc;
-        if (redo) {  // a queue overflowed: this context (and later ones of this scene) go level by level from now on
-            c->host_levels = true;
-            c->scene->dd_overflowed.store(true);
-            c->stats.device_driven_overflows += 1;
-            if ((rc = frame_begin(c)) != RT_OK) return rc;
-        }
+        // every launch of the frame, the resolve included, is queued without a single read-back: the call returns while the
+        // GPU works, and the counts (and whether a queue overflowed) are looked at in rt_context_render_end
+        if ((rc = frame_device_driven(c)) != RT_OK) return rc;
+        c->in_flight_dd = true;
+    } else {
+        if ((rc = frame_host_levels(c)) != RT_OK) return rc;  // reads counts back level by level: done when it returns
+        c->in_flight_dd = false;
     }
-    if (c->host_levels) {
-        rc = frame_host_levels(c);
-        if (rc != RT_OK) return rc;
-    }
-    c->prof_begin(4);
-    c->k->resolve(c->stream, c->ds, fp, c->accum, c->final_out ? c->final_out : c->framebuffer, c->bytewidth, c->final_out != nullptr);
-    c->prof_end();
-    c->stats.kernel_launches += 1;
-    CUDA_TRY(cudaMemcpyAsync(c->counters_host, c->counters, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
-    CUDA_TRY(cudaEventRecord(c->ev1, c->stream));
+    if ((rc = frame_finish(c)) != RT_OK) return rc;
+    c->in_flight = true;
+    return RT_OK;
+}
+
+int rt_context_render_end(rt_context* c, rt_stats* stats) {
+    if (!c) { set_error("null context"); return RT_ERR_INVALID; }
+    if (!c->in_flight) { set_error("rt_context_render_end: no frame in flight (rt_context_render_begin)"); return RT_ERR_INVALID; }
+    CUDA_TRY(cudaSetDevice(c->device));
+    c->in_flight = false;
     CUDA_TRY(cudaEventSynchronize(c->ev1));
-    if (c->counters_host->overflow) { set_error("internal error: ray queue or traversal stack overflow"); return RT_ERR_CUDA; }
+    if (c->in_flight_dd && dd_collect(c)) {
+        // a queue overflowed: this context (and later ones of this scene) go level by level from now on, this frame included
+        c->host_levels = true;
+        c->scene->dd_overflowed.store(true);
+        c->stats.device_driven_overflows += 1;
+        int rc = frame_begin(c);
+        if (rc == RT_OK) rc = frame_host_levels(c);
+        if (rc == RT_OK) rc = frame_finish(c);
+        if (rc != RT_OK) return rc;
+        CUDA_TRY(cudaEventSynchronize(c->ev1));
+    }
+    const Counters* fin = &c->counters_host[c->final_slot];
+    if (fin->overflow) { set_error("internal error: ray queue or traversal stack overflow"); return RT_ERR_CUDA; }
     for (int k = 0; k < 2; k++) {
-        c->stats.bvh_nodes_visited[k] = c->counters_host->bvh_nodes[k];
-        c->stats.bvh_prims_tested[k] = c->counters_host->bvh_prims[k];
-        c->stats.heavy_rays[k] = c->counters_host->heavy_rays[k];
-        c->stats.scan_sphere_tests[k] = c->counters_host->scan_tests[k];
+        c->stats.bvh_nodes_visited[k] = fin->bvh_nodes[k];
+        c->stats.bvh_prims_tested[k] = fin->bvh_prims[k];
+        c->stats.heavy_rays[k] = fin->heavy_rays[k];
+        c->stats.scan_sphere_tests[k] = fin->scan_tests[k];
     }
     for (int k = 0; k < 5; k++) { c->stats.class_ms[k] = 0.0; c->stats.class_launches[k] = 0; }
     for (size_t i = 0; i < c->prof_class.size(); i++) {
@@ -810,6 +842,11 @@ int rt_context_render(rt_context* c, rt_stats* stats) {
     c->stats.host_levels = c->host_levels ? 1u : 0u;
     if (stats) *stats = c->stats;
     return RT_OK;
+}
+
+int rt_context_render(rt_context* c, rt_stats* stats) {
+    const int rc = rt_context_render_begin(c);
+    return rc != RT_OK ? rc : rt_context_render_end(c, stats);
 }
 
 int rt_context_stats(const rt_context* c, rt_stats* stats) {
