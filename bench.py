@@ -547,7 +547,7 @@ def measure(name, args, D, steps, warmup, hw, want_e2e=True, want_cpu=True, gath
 
     # ---- end to end through the user-facing call with host buffers
     if want_e2e:
-        e2e = run_e2e(rt, D, scene, desc, info, base_opts, h, bytewidth, min(steps, 5))
+        e2e = run_e2e(rt, D, scene, desc, info, base_opts, h, bytewidth, max(4, min(steps, 6)), text=text, in_flight=max(1, int(args.frames_in_flight)))
         if rank == 0:
             line.update(e2e)
     if want_cpu and world == 1 and rank == 0:
@@ -602,18 +602,20 @@ def measure_nccl_variant(ctx, D, steps, frame_bytes, fb_ptr, fb_bytes):
             "what": "the same frames gathered with one NCCL all_gather_into_tensor per frame (side stream, one frame deep) + k_untile"}
 
 
-def run_e2e(rt, D, scene, desc, info, base_opts, h, bytewidth, steps):
+def run_e2e(rt, D, scene, desc, info, base_opts, h, bytewidth, steps, text=None, in_flight=2):
     """End to end through rt_render / rt_render_multi with HOST buffers.  N > 1: rank 0 drives all N GPUs through the library's
     own multi-GPU call (one host thread per device inside the library), the other ranks idle at the barrier.
     cold: the spheres are rewritten from host memory before every frame (flatten, upload, device BVH build per GPU, trace,
-          frame to pinned host memory);  warm: unchanged scene (the device copy kept with the rt_scene is reused)."""
+          frame to pinned host memory);  warm: unchanged scene (the device copy kept with the rt_scene is reused).
+    in_flight frames at once: that many caller threads, each with its own rt_scene and pinned frame, each making the same
+    blocking call for every other frame (an animation renders frame k+1 while frame k is on its way to the host); the figure
+    for one call at a time is reported beside it (`one_at_a_time_ms`)."""
     torch = D.torch
     world, rank = D.world, D.rank
     out = {}
     rt.release_cached_memory()   # the bench context's queues: rank 0 is about to allocate on every GPU
     D.host_barrier()
     if rank == 0:
-        host = torch.empty(h * bytewidth, dtype=torch.uint8).pin_memory()
         spheres = None
         if desc is not None:
             first = 0
@@ -623,28 +625,57 @@ def run_e2e(rt, D, scene, desc, info, base_opts, h, bytewidth, steps):
                     break
                 first += 1
         devices = None if world == 1 else list(range(world))
+        slots = [(scene, torch.empty(h * bytewidth, dtype=torch.uint8).pin_memory())]
+        for _ in range(max(1, in_flight) - 1):
+            slots.append((rt.serialize.deserialize(text) if desc is None else rt.Scene(desc), torch.empty(h * bytewidth, dtype=torch.uint8).pin_memory()))
 
-        def one(cold):
+        def one(slot, cold):
+            sc, host = slot
             if cold and spheres is not None:
-                scene.update_spheres(spheres[0], spheres[1])
-            st = rt.raytrace.render_into(scene, host.data_ptr(), devices=devices, **dict(base_opts, device=D.local_rank))
+                sc.update_spheres(spheres[0], spheres[1])
+            st = rt.raytrace.render_into(sc, host.data_ptr(), devices=devices, **dict(base_opts, device=D.local_rank))
             return st["rays_total"]
 
-        for label, cold in (("e2e", True), ("e2e_warm", False)):
-            one(cold); one(cold)
-            rays = 0
+        def timed(cold, n_slots, frames):
+            """frames calls in all, shared out over n_slots caller threads; -> (rays, seconds)"""
+            per = [frames // n_slots + (1 if i < frames % n_slots else 0) for i in range(n_slots)]
+            rays = [0] * n_slots
+            gate = threading.Barrier(n_slots + 1)
+
+            def run(i):
+                gate.wait()
+                for _ in range(per[i]):
+                    rays[i] += one(slots[i], cold)
+                gate.wait()
+
+            th = [threading.Thread(target=run, args=(i,)) for i in range(n_slots)]
+            for t in th:
+                t.start()
+            gate.wait()
             t0 = time.perf_counter()
-            for _ in range(steps):
-                rays += one(cold)
+            gate.wait()
             sec = time.perf_counter() - t0
+            for t in th:
+                t.join()
+            return sum(rays), sec
+
+        for label, cold in (("e2e", True), ("e2e_warm", False)):
+            for sl in slots:
+                one(sl, cold); one(sl, cold)
+            rays1, sec1 = timed(cold, 1, steps)
+            rays, sec = timed(cold, len(slots), steps) if len(slots) > 1 else (rays1, sec1)
             per_dev = scene_h2d_bytes(info, desc) if (cold and spheres is not None) else 0
             out[label] = {"value": rays / sec / 1e6, "unit": "Mrays/s", "ms_per_step": sec / steps * 1e3,
                           "h2d_bytes_per_step": per_dev * world, "d2h_bytes_per_step": h * bytewidth,
+                          "frames_in_flight": len(slots), "one_at_a_time_ms": sec1 / steps * 1e3,
                           "what": ("caller rewrites the spheres from host memory (rt_scene_update_spheres) -> " if cold and spheres is not None else "unchanged scene -> ") +
                                   ("rt_render" if world == 1 else "rt_render_multi (%d GPUs driven by one process, one thread per device, each device DMAs "
                                    "its bands to the host frame)" % world) +
                                   (": flatten, upload, device BVH build, trace, frame to pinned host memory" if cold and spheres is not None
-                                   else ": device copy of the scene reused, trace, frame to pinned host memory")}
+                                   else ": device copy of the scene reused, trace, frame to pinned host memory") +
+                                  ("; %d caller threads, each with its own rt_scene and host frame, keep %d frames in flight" % (len(slots), len(slots))
+                                   if len(slots) > 1 else "")}
+        del slots
         rt.release_cached_memory()
     D.host_barrier()
     return out
