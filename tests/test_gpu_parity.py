@@ -594,3 +594,34 @@ def test_bvh_filter_is_conservative_on_odd_scenes(gpu, case):
     assert fb.stats["rays_total"] == fl.stats["rays_total"] and fb.stats["rays_shadow"] == fl.stats["rays_shadow"]
     diff = np.abs(fb.rows.astype(np.int16) - fl.rows.astype(np.int16))
     assert diff.max() <= 1 and (diff == 0).mean() >= 0.999
+
+
+def test_two_frames_in_flight_equal_one_at_a_time(gpu, orc, scenes):
+    """rt_context_render_begin / _end: two contexts queue their frames back to back and are collected afterwards -- same rays,
+    same ids, same bytes as one blocking rt_context_render each; one _end per _begin."""
+    desc = scenes.random_spheres(600, 31, 14.0, 192, 108, antialias=2)
+    sc = gpu.Scene(desc)
+    a = gpu.Context(sc, max_depth=6, seed=2)
+    b = gpu.Context(sc, max_depth=6, seed=9)
+    one = {}
+    for name, c in (("a", a), ("b", b)):
+        st = c.render()
+        rows, ids, _ = c.download(want_ids=True)
+        one[name] = (st, rows.copy(), ids.copy())
+    ref = orc.OracleScene(desc).render(max_depth=6, seed=2)
+    assert np.array_equal(one["a"][2][:108], ref["ids"]) and one["a"][0]["rays_total"] == ref["stats"]["rays"]
+    for _ in range(3):
+        a.render_begin()
+        b.render_begin()
+        with pytest.raises(gpu.RtError):
+            a.render_begin()                       # the frame in flight has not been collected
+        sa, sb = a.render_end(), b.render_end()
+        for name, c, st in (("a", a, sa), ("b", b, sb)):
+            rows, ids, _ = c.download(want_ids=True)
+            assert st["rays_total"] == one[name][0]["rays_total"] and st["host_levels"] == 0
+            assert np.array_equal(ids, one[name][2])
+            assert (rows != one[name][1]).mean() < 1e-5     # order of f64 atomic adds into a pixel only
+    with pytest.raises(gpu.RtError):
+        a.render_end()                             # nothing in flight
+    assert not np.array_equal(one["a"][1], one["b"][1])     # two different frames were in flight
+    a.close(); b.close()
