@@ -2,7 +2,7 @@
 """bench.py -- measures the tracing hot path on N B200s of one node (contract: task prompt, section 4).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl ours|reference] [--fp strict|fast]
-                    [--gather peer|nccl] [--frames-in-flight F] [--no-also] [--no-e2e] [--no-cpu-baseline]
+                    [--gather peer|nccl] [--frames-in-flight F] [--tuning BITS] [--no-also] [--no-e2e] [--no-cpu-baseline]
 
 A step = one frame of the workload: primary-ray generation -> wavefront (closest-hit, shade, shadow kernels) -> resolve,
 on a device-resident scene (inputs already in HBM).  With N > 1 the frame is sharded by interleaved row bands, one process
@@ -373,6 +373,8 @@ def measure(name, args, D, steps, warmup, hw, want_e2e=True, want_cpu=True, gath
     accel = rt.ACCEL_BVH if wl["accel"] == "bvh" else rt.ACCEL_LINEAR
     fp_mode = rt.FP_FAST if args.fp == "fast" else rt.FP_STRICT
     base_opts = dict(wl["opts"], accel=accel, fp_mode=fp_mode)
+    if getattr(args, "tuning", 0):
+        base_opts["tuning"] = int(args.tuning)   # RT_TUNE_* bits (ncu captures use 32: one frame-wide shadow launch, as the class timing pass has it)
     opts = dict(base_opts, device=D.local_rank, rank=rank, world=world)
     ctx = rt.Context(scene, **opts)
     stream = torch.cuda.current_stream()
@@ -691,6 +693,7 @@ def main():
     ap.add_argument("--fp", default="strict", choices=["strict", "fast"])
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"])
     ap.add_argument("--frames-in-flight", type=int, default=2, help="frames queued at once per GPU (one context each); 1 = one frame at a time")
+    ap.add_argument("--tuning", type=int, default=0, help="RT_TUNE_* bits for every context (0 = the defaults)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-also", action="store_true")

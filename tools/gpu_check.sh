@@ -12,8 +12,11 @@ timeout 600 python bench.py > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err; echo 
 cat $O/${TAG}_bench.json
 if [ "$2" != "noncu" ]; then
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${TAG}_launches.csv python bench.py --steps 1 --warmup 3 --no-e2e --no-cpu-baseline --no-also > $O/${TAG}_ncu_list.log 2>&1; echo "ncu list rc=$?"
+# the same frame with one frame-wide shadow launch and one frame at a time (what the per-class timing pass and the full captures below see)
+SERIAL="--tuning 32 --frames-in-flight 1"
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${TAG}_launches_serial.csv python bench.py --steps 1 --warmup 3 --no-e2e --no-cpu-baseline --no-also $SERIAL > $O/${TAG}_ncu_list_serial.log 2>&1; echo "ncu list (serial) rc=$?"
 for K in k_shadow_bvh k_closest_bvh k_shade; do
   SKIP=12; [ $K = k_shadow_bvh ] && SKIP=2   # one shadow launch per frame, ten of the others
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:$K -s $SKIP -c 1 -o $O/${TAG}_full_$K -f python bench.py --steps 1 --warmup 3 --no-e2e --no-cpu-baseline --no-also > $O/${TAG}_ncu_full_$K.log 2>&1; echo "ncu full $K rc=$?"
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:$K -s $SKIP -c 1 -o $O/${TAG}_full_$K -f python bench.py --steps 1 --warmup 3 --no-e2e --no-cpu-baseline --no-also $SERIAL > $O/${TAG}_ncu_full_$K.log 2>&1; echo "ncu full $K rc=$?"
 done
 fi
