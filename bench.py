@@ -15,7 +15,7 @@ metric  Mrays/s, primary + secondary + shadow: 1 ray = one Scene::intersect call
         exactly from the wavefront queue lengths.
 value   whole-job rays of K frames / device time of K frames (CUDA events on the launching stream, max over ranks); no
         per-launch profiling events inside the timed region (kernel-class times come from a separate pass).  The frames
-        are independent (upstream's frame loop run for an animation), so --frames-in-flight F (default 2) of them are queued
+        are independent (upstream's frame loop run for an animation), so --frames-in-flight F (default 2 for the BVH workloads) of them are queued
         at once per GPU, one rt_context each (rt_context_render_begin / _end): on a shard the deep wavefront levels are bound
         by the latency of their longest walks and the next frame fills those gaps.  `frame_ms_alone` is one frame by itself.
 e2e     the same metric through the user-facing call with HOST buffers, every step: the caller moves its spheres
@@ -381,7 +381,10 @@ def measure(name, args, D, steps, warmup, hw, want_e2e=True, want_cpu=True, gath
     ctx.set_stream(stream.cuda_stream)
     # frames in flight (peer gather / one GPU): one context per frame slot, each on its own stream; frame k is queued on slot
     # k % F before frame k - F + 1 is collected.  The nccl gather pipelines its own way (below) with one context.
-    F = max(1, int(getattr(args, "frames_in_flight", 1))) if (world == 1 or gather == "peer") else 1
+    # Default: two for the BVH workloads (their deep levels are latency-bound: DESIGN.md 5b), one for the linear-scan workloads
+    # (every launch fills the machine; a second frame only competes: 427.8 against 408.9 ms on test-scene-800-1024spp).
+    want_f = args.frames_in_flight if getattr(args, "frames_in_flight", None) else (2 if wl["accel"] == "bvh" else 1)
+    F = max(1, int(want_f)) if (world == 1 or gather == "peer") else 1
     ctxs = [ctx] + [rt.Context(scene, **opts) for _ in range(F - 1)]
     bytewidth = ctx.bytewidth
     frame_bytes = h * bytewidth
@@ -549,7 +552,7 @@ def measure(name, args, D, steps, warmup, hw, want_e2e=True, want_cpu=True, gath
 
     # ---- end to end through the user-facing call with host buffers
     if want_e2e:
-        e2e = run_e2e(rt, D, scene, desc, info, base_opts, h, bytewidth, max(4, min(steps, 6)), text=text, in_flight=max(1, int(args.frames_in_flight)))
+        e2e = run_e2e(rt, D, scene, desc, info, base_opts, h, bytewidth, max(4, min(steps, 6)), text=text, in_flight=max(1, int(args.frames_in_flight or 2)))
         if rank == 0:
             line.update(e2e)
     if want_cpu and world == 1 and rank == 0:
@@ -696,7 +699,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--fp", default="strict", choices=["strict", "fast"])
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"])
-    ap.add_argument("--frames-in-flight", type=int, default=2, help="frames queued at once per GPU (one context each); 1 = one frame at a time")
+    ap.add_argument("--frames-in-flight", type=int, default=None,
+                    help="frames queued at once per GPU (one context each); default: 2 for BVH workloads, 1 for linear-scan workloads")
     ap.add_argument("--tuning", type=int, default=0, help="RT_TUNE_* bits for every context (0 = the defaults)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
