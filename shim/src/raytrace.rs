@@ -103,6 +103,48 @@ pub fn render_multi(scene: &Scene, opts: &RenderOptions, devices: &[i32], gather
     Ok(Frame { width: w, height: h, bytewidth: bw, rows: rows, primary_ids: ids, stats: stats })
 }
 
+/// A frame that is being traced: `begin` queues it on the GPU and returns, `finish` waits for it and copies it back.  An
+/// animation keeps two of these alive -- frame k + 1 is begun before frame k is finished -- so that the GPU is never idle in
+/// the latency-bound deep levels of a frame.  One GPU; the scene must not be changed while a frame is in flight.
+pub struct FrameInFlight {
+    ctx: *mut ffi::RtContext,
+    width: u32,
+    height: u32,
+}
+
+impl FrameInFlight {
+    pub fn begin(scene: &Scene, opts: &RenderOptions) -> Result<FrameInFlight, Error> {
+        let (w, h) = frame_size(scene, opts);
+        let o = opts.to_ffi();
+        let mut ctx: *mut ffi::RtContext = ptr::null_mut();
+        check(unsafe { ffi::rt_context_create(scene.handle(), &o, &mut ctx) })?;
+        let f = FrameInFlight { ctx: ctx, width: w, height: h };
+        check(unsafe { ffi::rt_context_render_begin(f.ctx) })?;
+        Ok(f)
+    }
+
+    pub fn finish(self) -> Result<Frame, Error> {
+        let (w, h) = (self.width, self.height);
+        let bw = unsafe { ffi::rt_bmp_bytewidth(w) };
+        let mut stats: ffi::RtStats = unsafe { std::mem::zeroed() };
+        check(unsafe { ffi::rt_context_render_end(self.ctx, &mut stats) })?;
+        // world == 1: the local rows are the image rows, plus band padding at the end that is not part of the frame
+        let local = stats.local_rows as usize;
+        let mut rows = vec![0u8; bw as usize * local];
+        let mut ids = vec![-1i32; w as usize * local];
+        check(unsafe { ffi::rt_context_download(self.ctx, rows.as_mut_ptr(), ids.as_mut_ptr(), ptr::null_mut()) })?;
+        rows.truncate(bw as usize * h as usize);
+        ids.truncate(w as usize * h as usize);
+        Ok(Frame { width: w, height: h, bytewidth: bw, rows: rows, primary_ids: ids, stats: stats })
+    }
+}
+
+impl Drop for FrameInFlight {
+    fn drop(&mut self) {
+        unsafe { ffi::rt_context_destroy(self.ctx) };   // waits for whatever is still queued
+    }
+}
+
 /// `Scene::intersect` (src/scene.rs:247-249) for a batch: (object index or -1, t, normal) per ray.
 pub fn intersect_batch(scene: &Scene, rays: &[Ray], opts: &RenderOptions) -> Result<Vec<(i32, f64, Vec3)>, Error> {
     let n = rays.len();
