@@ -222,10 +222,23 @@ struct DeviceSceneHolder {
     }
 
     int init(const rt_scene* s, int accel, uint32_t tuning, cudaStream_t st) {
-        const int rc = init_queued(s, accel, tuning, st);
+        // Upload and build run on a stream of their own at the device's highest priority.  The build waits for the host three
+        // times (grid check, depth, end); when another caller's frame is being traced on this GPU (two frames in flight, each
+        // with its own scene revision), each of those phases would otherwise queue behind that whole frame's launches -- its
+        // resident grids leave nothing free -- instead of slipping in at the next kernel boundary (a cold two-caller frame at
+        // 1M spheres took 73 ms instead of 42).
+        cudaStream_t hp = nullptr;
+        int lo = 0, hi = 0;
+        if (cudaDeviceGetStreamPriorityRange(&lo, &hi) != cudaSuccess || cudaStreamCreateWithPriority(&hp, cudaStreamNonBlocking, hi) != cudaSuccess) {
+            cudaGetLastError();
+            hp = nullptr;
+        }
+        const cudaStream_t use = hp ? hp : st;
+        const int rc = init_queued(s, accel, tuning, use);
         // nothing of this holder may still be in flight when its blocks go back to the cache (early return), and the flat
         // cache entry the copies read from may go away (scene changed or freed) once this returns
-        cudaStreamSynchronize(st);
+        cudaStreamSynchronize(use);
+        if (hp) cudaStreamDestroy(hp);
         return rc;
     }
 
