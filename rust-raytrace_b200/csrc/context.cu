@@ -227,18 +227,21 @@ struct DeviceSceneHolder {
         // with its own scene revision), each of those phases would otherwise queue behind that whole frame's launches -- its
         // resident grids leave nothing free -- instead of slipping in at the next kernel boundary (a cold two-caller frame at
         // 1M spheres took 73 ms instead of 42).
-        cudaStream_t hp = nullptr;
-        int lo = 0, hi = 0;
-        if (cudaDeviceGetStreamPriorityRange(&lo, &hi) != cudaSuccess || cudaStreamCreateWithPriority(&hp, cudaStreamNonBlocking, hi) != cudaSuccess) {
-            cudaGetLastError();
-            hp = nullptr;
+        // One such stream per host thread and device, made on first use and kept (the callers are long-lived: the worker threads
+        // of an rt_multi, the caller's own thread for rt_render; creating and destroying one per call cost 0.5 ms per frame at
+        // eight GPUs).
+        static thread_local cudaStream_t tl_hp[64] = {};
+        cudaStream_t hp = (device >= 0 && device < 64) ? tl_hp[device] : nullptr;
+        if (!hp && device >= 0 && device < 64) {
+            int lo = 0, hi = 0;
+            if (cudaDeviceGetStreamPriorityRange(&lo, &hi) == cudaSuccess && cudaStreamCreateWithPriority(&hp, cudaStreamNonBlocking, hi) == cudaSuccess) tl_hp[device] = hp;
+            else { cudaGetLastError(); hp = nullptr; }
         }
         const cudaStream_t use = hp ? hp : st;
         const int rc = init_queued(s, accel, tuning, use);
         // nothing of this holder may still be in flight when its blocks go back to the cache (early return), and the flat
         // cache entry the copies read from may go away (scene changed or freed) once this returns
         cudaStreamSynchronize(use);
-        if (hp) cudaStreamDestroy(hp);
         return rc;
     }
 
@@ -1453,6 +1456,7 @@ int rt_trace_rays(const rt_scene* s, const rt_render_opts* o, uint64_t n, const 
     int rc = RT_OK;
     {
         DeviceSceneHolder holder;
+        holder.device = o->device;
         uint32_t* heavy = nullptr;
         const rt_scene* use = s;  // scenes used only for intersection tests may lack camera/background
         rt_scene patched;
