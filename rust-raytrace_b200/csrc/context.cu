@@ -208,14 +208,44 @@ struct DeviceSceneHolder {
 
     // the flat buffers come from the scene's cache (host_scene.h FlatCache) and, for big scenes, from page-locked memory:
     // copies on the context's stream, the BVH build queued right behind them
+    // Arrays that are not page-locked where they lie (small scenes, the tables) go through a page-locked staging block of
+    // the calling thread: a copy from pageable memory is staged by the driver under a lock that the upload threads of all
+    // GPUs share (eight devices re-uploading a 10k-sphere scene spent more time there than in their BVH builds).
+    struct Staging {
+        unsigned char* p = nullptr;
+        size_t cap = 0, used = 0;
+        ~Staging() { if (p) cudaFreeHost(p); }
+        void* take(size_t bytes) {  // nullptr: does not fit (the caller copies from where the data lies)
+            const size_t at = (used + 255) & ~(size_t)255;
+            if (at + bytes > cap) return nullptr;
+            used = at + bytes;
+            return p + at;
+        }
+    };
+    static Staging& staging(size_t want) {
+        static thread_local Staging s;
+        s.used = 0;
+        if (s.cap < want) {
+            if (s.p) cudaFreeHost(s.p);
+            s.p = nullptr; s.cap = 0;
+            const size_t cap = std::max<size_t>(want + (want >> 2), 1u << 20);
+            if (cudaMallocHost((void**)&s.p, cap) == cudaSuccess) s.cap = cap;
+            else cudaGetLastError();
+        }
+        return s;
+    }
     template <typename T>
-    int up_flat(const std::vector<T>& v, const T** out, cudaStream_t st) {
+    int up_flat(const std::vector<T>& v, const T** out, cudaStream_t st, Staging* stage = nullptr) {
         T* p = nullptr;
         int rc = dev_alloc(&p, v.size());
         if (rc != RT_OK) return rc;
         if (p) {
             allocs.push_back(p);
-            CUDA_TRY(cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, st));
+            const void* src = v.data();
+            if (stage) {
+                if (void* h = stage->take(v.size() * sizeof(T))) { std::memcpy(h, v.data(), v.size() * sizeof(T)); src = h; }
+            }
+            CUDA_TRY(cudaMemcpyAsync(p, src, v.size() * sizeof(T), cudaMemcpyHostToDevice, st));
         }
         *out = p;
         return RT_OK;
@@ -255,23 +285,33 @@ private:
         fill_scene_header(s, f, &ds);
         const double* clo = f.centroid_lo;
         const double* chi = f.centroid_hi;
-        if ((rc = up_flat(f.sph, &ds.sph, st)) != RT_OK) return rc;
-        if ((rc = up_flat(f.sph_obj, &ds.sph_obj, st)) != RT_OK) return rc;
-        if ((rc = up_flat(f.planes, &ds.planes, st)) != RT_OK) return rc;
-        if ((rc = up_flat(f.obj_shape, &ds.obj_shape, st)) != RT_OK) return rc;
-        if ((rc = up_flat(f.obj_material, &ds.obj_material, st)) != RT_OK) return rc;
-        if ((rc = up_flat(s->materials, &ds.materials, st)) != RT_OK) return rc;
-        if ((rc = up_flat(s->lights, &ds.lights, st)) != RT_OK) return rc;
+        // big scenes are page-locked in place (pin_flat_cache): only their small arrays are staged
+        const bool pinned = fc->pin && !std::static_pointer_cast<HostPins>(fc->pin)->regions.empty();
+        size_t small = (f.planes.size() * sizeof(PlaneRec) + s->lights.size() * sizeof(LightRec) + 511 * sizeof(double)) + 16 * 256;
+        if (!pinned) {
+            small += f.sph.size() * sizeof(SphereRec) + (f.sph_obj.size() + f.obj_shape.size() + f.obj_material.size()) * 4 + s->materials.size() * sizeof(MaterialRec);
+            if (s->bg_kind == BG_SKYBOX)
+                for (int k = 0; k < 6; k++) small += s->faces[k].data.size();
+        }
+        Staging& stg = staging(small);
+        Staging* big = pinned ? nullptr : &stg;
+        if ((rc = up_flat(f.sph, &ds.sph, st, big)) != RT_OK) return rc;
+        if ((rc = up_flat(f.sph_obj, &ds.sph_obj, st, big)) != RT_OK) return rc;
+        if ((rc = up_flat(f.planes, &ds.planes, st, &stg)) != RT_OK) return rc;
+        if ((rc = up_flat(f.obj_shape, &ds.obj_shape, st, big)) != RT_OK) return rc;
+        if ((rc = up_flat(f.obj_material, &ds.obj_material, st, big)) != RT_OK) return rc;
+        if ((rc = up_flat(s->materials, &ds.materials, st, big)) != RT_OK) return rc;
+        if ((rc = up_flat(s->lights, &ds.lights, st, &stg)) != RT_OK) return rc;
         if (s->bg_kind == BG_SKYBOX)
             for (int k = 0; k < 6; k++) {
                 const uint8_t* p = nullptr;
-                if ((rc = up_flat(s->faces[k].data, &p, st)) != RT_OK) return rc;
+                if ((rc = up_flat(s->faces[k].data, &p, st, big)) != RT_OK) return rc;
                 ds.faces[k].data = p;
             }
         std::vector<double> vals(SRGB_VALUES, SRGB_VALUES + 256), avg(SRGB_AVERAGE, SRGB_AVERAGE + 255);
-        if ((rc = up_flat(vals, &ds.srgb_values, st)) != RT_OK) return rc;
-        if ((rc = up_flat(avg, &ds.srgb_average, st)) != RT_OK) return rc;
-        CUDA_TRY(cudaStreamSynchronize(st));  // vals / avg are locals
+        if ((rc = up_flat(vals, &ds.srgb_values, st, &stg)) != RT_OK) return rc;
+        if ((rc = up_flat(avg, &ds.srgb_average, st, &stg)) != RT_OK) return rc;
+        CUDA_TRY(cudaStreamSynchronize(st));  // vals / avg are locals; the staging block is this thread's next upload's too
         use_bvh = accel_uses_bvh(accel, ds.n_spheres);
         if (use_bvh) {
             cudaEvent_t e0 = nullptr, e1 = nullptr;
