@@ -27,7 +27,10 @@ constexpr int SCAN_TILE = 1024;  // spheres per shared-memory tile (32 KB), doub
 #define RT_RAY_PREFETCH 8192  // k_closest_bvh refills prefetch the queue records this many rays ahead of the cursor (0: off): 5.01 -> 4.97 ms (10k),
                               // 5.24 -> 5.19 ms (1M), the same at 2048 and 32768; the shadow kernel (reserved blocks) did not gain: profiles/r02_v5_ray_prefetch_ab.txt
 #endif
-constexpr int BVH_THREADS = 128;
+#ifndef RT_BVH_THREADS
+#define RT_BVH_THREADS 128  // with RT_BVH_MIN_BLOCKS: 64 x 16 is 0.7-1 % faster on a 1/8 shard (CTAs leave sooner at the end of a launch), 256 x 4
+#endif                      // 1-2 % slower; whole frames within noise (profiles/r02_v8_bvh_threads_shard_ab.txt)
+constexpr int BVH_THREADS = RT_BVH_THREADS;
 #ifndef RT_SHADE_THREADS
 #define RT_SHADE_THREADS 128
 #endif
