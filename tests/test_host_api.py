@@ -82,6 +82,29 @@ def test_no_cpu_fallback(rt, scenes):
         assert e.value.code == -4 and "no CPU fallback" in e.value.message
 
 
+def test_new_entry_points_check_their_arguments_before_they_touch_a_device(rt):
+    """rt_context_render_begin / _end and rt_intersect_spheres_noalloc: bad arguments are RT_ERR_INVALID with a message (whether or
+    not a GPU is visible); without a GPU a well-formed no-alloc call is RT_ERR_CUDA -- no CPU path."""
+    import ctypes as C
+    L = rt.lib()
+    assert L.rt_context_render_begin(None) == -1 and b"null context" in L.rt_last_error()
+    assert L.rt_context_render_end(None, None) == -1
+    fake = C.c_void_p(4096)   # never dereferenced: every check below fails before a launch
+    assert L.rt_intersect_spheres_noalloc(0, None, None, 5, fake, 10, fake, fake) == -1 and b"null argument" in L.rt_last_error()
+    assert L.rt_intersect_spheres_noalloc(0, None, fake, 5, None, 10, fake, fake) == -1
+    assert L.rt_intersect_spheres_noalloc(0, None, fake, 5, fake, 10, None, fake) == -1
+    assert L.rt_intersect_spheres_noalloc(0, None, fake, rt.NOALLOC_MAX_SPHERES + 1, fake, 10, fake, fake) == -1
+    msg = L.rt_last_error().decode()
+    assert "RT_NOALLOC_MAX_SPHERES" in msg and "65536" in msg and "rt_trace_rays" in msg
+    assert rt.NOALLOC_SCRATCH_BYTES == 65536 * 32 + 256
+    assert L.rt_intersect_spheres_noalloc(0, None, C.c_void_p(4096 + 8), 5, fake, 10, fake, fake) == -1 and b"misaligned" in L.rt_last_error()
+    assert L.rt_intersect_spheres_noalloc(0, None, fake, 5, fake, 1 << 31, fake, fake) == -1 and b"too many rays" in L.rt_last_error()
+    if rt.device_count() == 0:
+        assert L.rt_intersect_spheres_noalloc(0, None, fake, 5, fake, 10, fake, fake) == -4 and b"no CPU fallback" in L.rt_last_error()
+    else:
+        assert L.rt_intersect_spheres_noalloc(rt.device_count(), None, fake, 5, fake, 10, fake, fake) == -1 and b"no such device" in L.rt_last_error()
+
+
 # ---- serialize::deserialize -------------------------------------------------------------------------------
 def test_parse_reference_scene(rt):
     sc = rt.serialize.deserialize(REF_TEXT_SCENE)
