@@ -22,7 +22,7 @@ import numpy as np
 
 from . import _binding as B
 from ._binding import (ACCEL_AUTO, ACCEL_BVH, ACCEL_LINEAR, FP_FAST, FP_STRICT, GATHER_AUTO, GATHER_DIRECT, GATHER_NCCL,  # noqa: F401
-                       GATHER_PEER, NOALLOC_MAX_SPHERES, NOALLOC_SCRATCH_BYTES, TUNE_BINARY_SHADOW, TUNE_HOST_LEVELS, TUNE_MORTON_AXIS, TUNE_NODES_F32, TUNE_NODES_Q16, TUNE_SERIAL_SHADOW, RenderOpts,
+                       GATHER_PEER, NOALLOC_MAX_SPHERES, NOALLOC_SCRATCH_BYTES, TUNE_BINARY_SHADOW, TUNE_HOST_LEVELS, TUNE_MORTON_AXIS, TUNE_NODES_F32, TUNE_NODES_Q16, TUNE_FRAME_GRAPH, TUNE_SERIAL_SHADOW, RenderOpts,
                        RtError, Stats, SyntaxError_)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))

@@ -12,7 +12,7 @@ ACCEL_AUTO, ACCEL_LINEAR, ACCEL_BVH = 0, 1, 2
 FP_STRICT, FP_FAST = 0, 1
 GATHER_AUTO, GATHER_DIRECT, GATHER_PEER, GATHER_NCCL = 0, 1, 2, 3
 ANTIALIAS_FROM_SCENE = 0xFFFFFFFF
-TUNE_NODES_F32, TUNE_NODES_Q16, TUNE_MORTON_AXIS, TUNE_BINARY_SHADOW, TUNE_HOST_LEVELS, TUNE_SERIAL_SHADOW = 1, 2, 4, 8, 16, 32
+TUNE_NODES_F32, TUNE_NODES_Q16, TUNE_MORTON_AXIS, TUNE_BINARY_SHADOW, TUNE_HOST_LEVELS, TUNE_SERIAL_SHADOW, TUNE_FRAME_GRAPH = 1, 2, 4, 8, 16, 32, 64
 NOALLOC_MAX_SPHERES, NOALLOC_SCRATCH_BYTES = 65536, 65536 * 32 + 256   # rt_intersect_spheres_noalloc's static scratch
 
 

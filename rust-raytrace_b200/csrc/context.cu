@@ -434,6 +434,18 @@ struct rt_context {
     size_t n_host_slots = 0;
     size_t final_slot = 0;        // counters_host[final_slot]: the record copied out behind the resolve kernel (frame-wide counters)
     size_t dd_batches = 0;        // primary batches of the device-driven frame in flight
+    // RT_TUNE_FRAME_GRAPH: a device-driven BVH frame is the same ~70 launches, memsets and copies every time (counts live on
+    // the device), so once two consecutive frames were queued from identical arguments the whole frame is captured into a CUDA
+    // graph and replayed with one launch call (frame_graph_*).  A re-bound scene (new device pointers), another frame buffer
+    // or profiling go back to plain launches.  Opt-in: the replay takes rt_context_render_begin from 0.30 to 0.01 ms of host
+    // time, but the graph's fork / join per level runs slower on the device than the same launches on two streams (1/8 shard
+    // 2.66 against 2.43 ms; whole frames equal: profiles/r02_v9_graph_ab.txt) -- for callers whose host thread is the bottleneck.
+    cudaGraphExec_t graph_exec = nullptr;
+    DeviceScene graph_ds{};           // what the graph was captured from / what the previous frame was queued from
+    uint8_t* graph_out = nullptr;
+    bool graph_key_valid = false;     // graph_ds / graph_out describe the previous frame
+    bool graph_failed = false;        // capture or instantiation failed once: plain launches from then on
+    uint64_t graph_kernel_launches = 0;
     bool in_flight = false;       // rt_context_render_begin has queued a frame that rt_context_render_end has not collected yet
     bool in_flight_dd = false;    // ... and it is a device-driven one (its counts are still to be read)
     double* accum = nullptr;
@@ -483,6 +495,7 @@ struct rt_context {
         if (ev1) cudaEventDestroy(ev1);
         if (ev_counts) cudaEventDestroy(ev_counts);
         for (cudaEvent_t e : prof_events) cudaEventDestroy(e);
+        if (graph_exec) cudaGraphExecDestroy(graph_exec);
         for (cudaEvent_t e : ev_seg) cudaEventDestroy(e);
         if (ev_join) cudaEventDestroy(ev_join);
         scene.reset();
@@ -823,14 +836,41 @@ void rt_context_destroy(rt_context* c) { delete c; }
 
 namespace {
 // resolve + the frame-wide counters + the frame's closing event, queued behind whatever traced the frame
-int frame_finish(rt_context* c) {
+int frame_finish(rt_context* c, bool closing_event = true) {
     c->prof_begin(4);
     c->k->resolve(c->stream, c->ds, c->fp, c->accum, c->final_out ? c->final_out : c->framebuffer, c->bytewidth, c->final_out != nullptr);
     c->prof_end();
     c->stats.kernel_launches += 1;
     CUDA_TRY(cudaMemcpyAsync(&c->counters_host[c->final_slot], c->counters, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
-    CUDA_TRY(cudaEventRecord(c->ev1, c->stream));
+    if (closing_event) CUDA_TRY(cudaEventRecord(c->ev1, c->stream));
     return RT_OK;
+}
+
+// Captures one device-driven frame (frame_begin .. frame_finish) on the context's own streams into an executable graph.
+// The timing events stay outside: they are recorded around the graph launch on whatever stream the caller gave.
+void frame_graph_capture(rt_context* c) {
+    if (c->graph_exec) { cudaGraphExecDestroy(c->graph_exec); c->graph_exec = nullptr; }
+    const cudaStream_t user = c->stream;
+    c->stream = c->own_stream;
+    cudaGraph_t g = nullptr;
+    int rc = RT_OK;
+    if (cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) rc = RT_ERR_CUDA;
+    if (rc == RT_OK) {
+        c->stats.kernel_launches = 0;
+        rc = frame_begin(c);
+        if (rc == RT_OK) rc = frame_device_driven(c);
+        if (rc == RT_OK) rc = frame_finish(c, false);
+        if (cudaStreamEndCapture(c->stream, &g) != cudaSuccess || !g) rc = RT_ERR_CUDA;
+    }
+    c->stream = user;
+    if (rc == RT_OK && cudaGraphInstantiate(&c->graph_exec, g, 0) != cudaSuccess) { c->graph_exec = nullptr; rc = RT_ERR_CUDA; }
+    if (g) cudaGraphDestroy(g);
+    if (rc != RT_OK) {
+        cudaGetLastError();
+        c->graph_failed = true;
+        return;
+    }
+    c->graph_kernel_launches = c->stats.kernel_launches;
 }
 }  // namespace
 
@@ -840,15 +880,35 @@ int rt_context_render_begin(rt_context* c) {
     CUDA_TRY(cudaSetDevice(c->device));
     c->stats.kernel_launches = 0;
     c->prof_class.clear();
-    CUDA_TRY(cudaEventRecord(c->ev0, c->stream));
-    int rc = frame_begin(c);
-    if (rc != RT_OK) return rc;
+    int rc = RT_OK;
     if (!c->host_levels) {
         // every launch of the frame, the resolve included, is queued without a single read-back: the call returns while the
         // GPU works, and the counts (and whether a queue overflowed) are looked at in rt_context_render_end
+        const bool graphable = c->use_bvh && c->stream2 && !c->profiling && !c->graph_failed && (c->opts.tuning & RT_TUNE_FRAME_GRAPH);
+        uint8_t* out_now = c->final_out ? c->final_out : c->framebuffer;
+        const bool same = c->graph_key_valid && out_now == c->graph_out && std::memcmp(&c->ds, &c->graph_ds, sizeof(DeviceScene)) == 0;
+        if (graphable && same && !c->graph_exec) frame_graph_capture(c);   // second frame from the same arguments: nothing runs yet
+        if (!same && c->graph_exec) { cudaGraphExecDestroy(c->graph_exec); c->graph_exec = nullptr; }
+        c->graph_ds = c->ds; c->graph_out = out_now; c->graph_key_valid = true;
+        if (graphable && same && c->graph_exec) {
+            c->stats.rays_total = c->stats.rays_primary = c->stats.rays_secondary = c->stats.rays_shadow = 0;
+            c->stats.paths = 0;
+            c->stats.kernel_launches = c->graph_kernel_launches;
+            CUDA_TRY(cudaEventRecord(c->ev0, c->stream));
+            CUDA_TRY(cudaGraphLaunch(c->graph_exec, c->stream));   // frame_begin .. frame_finish, the closing event apart
+            CUDA_TRY(cudaEventRecord(c->ev1, c->stream));
+            c->in_flight_dd = true;
+            c->in_flight = true;
+            return RT_OK;
+        }
+        c->stats.kernel_launches = 0;
+        CUDA_TRY(cudaEventRecord(c->ev0, c->stream));
+        if ((rc = frame_begin(c)) != RT_OK) return rc;
         if ((rc = frame_device_driven(c)) != RT_OK) return rc;
         c->in_flight_dd = true;
     } else {
+        CUDA_TRY(cudaEventRecord(c->ev0, c->stream));
+        if ((rc = frame_begin(c)) != RT_OK) return rc;
         if ((rc = frame_host_levels(c)) != RT_OK) return rc;  // reads counts back level by level: done when it returns
         c->in_flight_dd = false;
     }

@@ -625,3 +625,48 @@ def test_two_frames_in_flight_equal_one_at_a_time(gpu, orc, scenes):
         a.render_end()                             # nothing in flight
     assert not np.array_equal(one["a"][1], one["b"][1])     # two different frames were in flight
     a.close(); b.close()
+
+
+def test_replayed_frame_graph_equals_plain_launches(gpu, orc, scenes):
+    """With RT_TUNE_FRAME_GRAPH a context that renders the same frame again replays a CUDA graph of it (captured when the second
+    frame is queued from the same arguments); by default every launch is queued every time.  Same counts, ids and bytes --
+    also after the scene moved (new device pointers: plain launches again, then a new graph) and with several primary batches."""
+    desc = scenes.random_spheres(500, 41, 13.0, 160, 90, antialias=2)
+    sc = gpu.Scene(desc)
+    ref = orc.OracleScene(desc).render(max_depth=6, seed=4)
+    plain = gpu.Context(sc, max_depth=6, seed=4)
+    st0 = plain.render()
+    rows0, ids0, _ = plain.download(want_ids=True)
+    assert np.array_equal(ids0[:90], ref["ids"]) and st0["rays_total"] == ref["stats"]["rays"]
+    for kw in (dict(), dict(max_rays_in_flight=8192)):          # one batch / several batches per frame
+        ctx = gpu.Context(sc, max_depth=6, seed=4, tuning=gpu.TUNE_FRAME_GRAPH, **kw)
+        for frame in range(4):
+            st = ctx.render()
+            rows, ids, _ = ctx.download(want_ids=True)
+            assert st["host_levels"] == 0 and st["rays_total"] == st0["rays_total"], (kw, frame)
+            for k in ("rays_primary", "rays_secondary", "rays_shadow", "paths"):
+                assert st[k] == st0[k]
+            assert np.array_equal(ids, ids0) and (rows != rows0).mean() < 1e-5
+        ctx.close()
+    plain.close()
+    # rt_render_multi keeps its contexts and re-binds them: unchanged scene -> graph, moved spheres -> plain launches, same frames
+    data = None
+    first = 0
+    for ob in desc["objects"]:
+        if ob["shape"] == "spheres":
+            data = np.ascontiguousarray(ob["data"], dtype=np.float64)
+            break
+        first += 1
+    G = dict(gather=gpu.GATHER_DIRECT, max_depth=6, seed=4, tuning=gpu.TUNE_FRAME_GRAPH)
+    frames = [gpu.raytrace.render_multi(sc, [0, 0], **G) for _ in range(3)]
+    moved = data.copy(); moved[:, 1] += 0.25
+    sc.update_spheres(first, moved)
+    up = [gpu.raytrace.render_multi(sc, [0, 0], **G) for _ in range(3)]
+    sc.update_spheres(first, data)
+    back = gpu.raytrace.render_multi(sc, [0, 0], **G)
+    for fr in frames[1:] + [back]:
+        assert np.array_equal(fr.ids, frames[0].ids) and (fr.rows != frames[0].rows).mean() < 1e-5
+    assert np.array_equal(frames[0].ids, ref["ids"])
+    for fr in up[1:]:
+        assert np.array_equal(fr.ids, up[0].ids) and (fr.rows != up[0].rows).mean() < 1e-5
+    assert not np.array_equal(up[0].rows, frames[0].rows)
