@@ -322,6 +322,19 @@ __device__ __forceinline__ uint32_t warp_fetch(unsigned idle_mask, uint32_t* cur
 #define RT_DESCEND_STEPS 16  // walk at most this many nodes before looking at the warp again (sweep: profiles/r01_v5_sweep.md)
 #endif
 constexpr int FETCH_MIN_IDLE = RT_FETCH_MIN_IDLE;  // refill when at least this many lanes of the warp have finished their ray
+// Per kernel (profiles/r02_v9_per_kernel_sweep_ab.txt, r02_v9_closest_refill_*.txt): the closest-hit kernel refills a little later
+// (its refill is the costlier interruption: plane tests in f64, the ordered walk's state) -- 8 / 12 / 16 / 20 / 24 / 28 idle lanes:
+// 5.34 / 5.11 / 4.96 / 4.90 / 4.90 / 4.97 ms per 10k frame, a 1/8 shard 2.43 against 2.47 ms; walk lengths 12 / 24 for it and
+// 6 / 12 wide visits for the shadow kernel are worse on the 10k frame and within noise at 1M.
+#ifndef RT_FETCH_MIN_IDLE_CLOSEST
+#define RT_FETCH_MIN_IDLE_CLOSEST 20
+#endif
+#ifndef RT_DESCEND_STEPS_CLOSEST
+#define RT_DESCEND_STEPS_CLOSEST RT_DESCEND_STEPS
+#endif
+#ifndef RT_SHADOW_WIDE_STEPS
+#define RT_SHADOW_WIDE_STEPS (RT_DESCEND_STEPS / 2)
+#endif
 
 // Persistent "while-while" traversal.  Each lane owns one ray at a time; the warp alternates between
 //   phase 1  every lane walks internal nodes (f32 box filter) until its next job is a leaf test or it is done,
@@ -370,7 +383,7 @@ __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_closest_bvh(
     bool active = false, exhausted = false;
     while (true) {
         const unsigned idle = __ballot_sync(0xFFFFFFFFu, !active);
-        if (idle != 0u && !exhausted && (__popc(idle) >= FETCH_MIN_IDLE || idle == 0xFFFFFFFFu)) {
+        if (idle != 0u && !exhausted && (__popc(idle) >= RT_FETCH_MIN_IDLE_CLOSEST || idle == 0xFFFFFFFFu)) {
             const uint32_t li = warp_fetch_each(idle, &counters->lc[lc_index].cursor);
             const uint32_t n_now = n_s;
             if (!active) {
@@ -409,7 +422,7 @@ __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_closest_bvh(
             continue;
         }
         if (active) {
-            cur = trav_descend<QNODES>(sc, br, cur, bound, st, sp, tc, RT_DESCEND_STEPS);
+            cur = trav_descend<QNODES>(sc, br, cur, bound, st, sp, tc, RT_DESCEND_STEPS_CLOSEST);
         }
         __syncwarp();
         if (active) {
@@ -496,7 +509,7 @@ __global__ void __launch_bounds__(BVH_THREADS, RT_BVH_MIN_BLOCKS) k_shadow_bvh(c
             continue;
         }
         if (active) {
-            if constexpr (WIDE) cur = trav_descend_wide(sc, br, cur, bound, st, sp, tc, RT_DESCEND_STEPS / 2);
+            if constexpr (WIDE) cur = trav_descend_wide(sc, br, cur, bound, st, sp, tc, RT_SHADOW_WIDE_STEPS);
             else cur = trav_descend<QNODES>(sc, br, cur, bound, st, sp, tc, RT_DESCEND_STEPS);
         }
         __syncwarp();
