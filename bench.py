@@ -61,6 +61,25 @@ ALSO_WORKLOAD = "spheres-1m-8k-d8"   # north_star's scaling configuration, carri
 METRIC = "Mrays/s (primary+secondary+shadow) at 4K"
 
 
+_JSON_OUT = None
+
+
+def claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries print there too (NCCL's version banner at N > 1): keep a private
+    handle on the real stdout for that line and point file descriptor 1 at stderr for everything else."""
+    global _JSON_OUT
+    if _JSON_OUT is None:
+        sys.stdout.flush()
+        _JSON_OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    out = _JSON_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def host_threads():
     """Host cores this process may use.  Never omp_get_max_threads(): torchrun exports OMP_NUM_THREADS=1."""
     try:
@@ -208,7 +227,7 @@ def run_reference(args):
             "config": workload_config(name, w, h, aa, scene_mod.count_objects(desc), len(desc["lights"])),
             "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": used, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config(name, w, h, aa, n_objects, n_lights):
@@ -706,6 +725,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-also", action="store_true")
     args = ap.parse_args()
+    claim_stdout()
     if args.impl == "reference":
         run_reference(args)
         return
@@ -731,7 +751,7 @@ def main():
         line["host_threads"] = host_threads()
         if also:
             line["also"] = also
-        print(json.dumps(line), flush=True)
+        emit(line)
     D.close()
 
 
