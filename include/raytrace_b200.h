@@ -191,7 +191,9 @@ typedef struct rt_stats {
  *                the value handed to the quantiser (src/main.rs:56) is (accum / camera_samples) / antialias
  * Requires world == 1 in opts (rt_render_multi shards one frame over several GPUs).
  * The device copy of the scene (flattened buffers + BVH) stays with the rt_scene between calls, per device, until a
- * builder call changes the scene: a caller rendering frame after frame uploads and builds once. */
+ * builder call changes the scene: a caller rendering frame after frame uploads and builds once.  The call's context
+ * (streams, events, ray queues) is kept too, keyed by (scene, options), and re-bound to the scene's current revision by the
+ * next call; rt_release_cached_memory and rt_scene_free drop it. */
 RT_API int rt_render(const rt_scene*, const rt_render_opts*, uint8_t* bgr_rows, int32_t* primary_ids, double* accum, rt_stats* stats);
 
 /* Device-resident path (bench / shards): the scene and all buffers stay in HBM between frames.

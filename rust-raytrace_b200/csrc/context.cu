@@ -49,6 +49,8 @@ namespace {
 // ray queues of several GB); paying cudaMalloc/cudaFree for those every frame costs more than the trace itself, so blocks
 // released by a context are kept (per device, by size) and handed to the next one.  rt_release_cached_memory() returns
 // them to the driver.
+void (*g_drop_cached_multi)() = nullptr;  // drops the contexts / rt_multi objects kept between one-shot calls (set at the end of this file)
+
 class DeviceCache {
 public:
     cudaError_t alloc(void** p, size_t bytes) {
@@ -69,8 +71,9 @@ public:
             }
         }
         e = cudaMalloc(p, sz);
-        if (e != cudaSuccess) {  // out of memory with blocks parked in the cache: give them back and retry once
+        if (e != cudaSuccess) {  // out of memory with blocks parked in the cache (or held by contexts kept between one-shot calls): give them back and retry once
             cudaGetLastError();
+            if (g_drop_cached_multi) g_drop_cached_multi();
             trim();
             e = cudaMalloc(p, sz);
             if (e != cudaSuccess) return e;
@@ -139,7 +142,6 @@ private:
     std::vector<std::pair<Counters*, size_t>> free_;
 };
 PinnedPool g_pinned;
-void (*g_drop_cached_multi)() = nullptr;  // set where the cache of rt_multi objects is defined (end of this file)
 const DeviceAllocator g_cache_allocator = {[](void** p, size_t bytes) { return g_cache.alloc(p, bytes); }, [](void* p) { g_cache.release(p); }};
 
 template <typename T>
@@ -1055,12 +1057,73 @@ int rt_context_synchronize(rt_context* c) {
     return RT_OK;
 }
 
+}  // extern "C"
+
+namespace {
+int ctx_rebind_scene(rt_context* c, const rt_scene* s, double* built_ms = nullptr);  // below, with the multi-GPU code
+
+// rt_render is one-shot by contract -- a context per call, as upstream's main would have it -- but a caller rendering frame
+// after frame would pay for the context's streams, events and ~30 queue blocks every time (0.29 ms of a 16.5 ms frame: create
+// 0.16, destroy 0.13).  The last two contexts are kept, keyed by (scene handle, options), and re-bound to the scene's current
+// revision on the next call (two: two callers with a scene each keep two frames in flight).  rt_release_cached_memory and
+// rt_scene_free drop them.
+struct ContextCache {
+    struct Entry { const rt_scene* scene; rt_render_opts opts; rt_context* c; };
+    std::mutex mu;
+    std::vector<Entry> entries;
+    rt_context* take(const rt_scene* s, const rt_render_opts& o) {
+        std::lock_guard<std::mutex> g(mu);
+        for (size_t i = 0; i < entries.size(); i++)
+            if (entries[i].scene == s && std::memcmp(&entries[i].opts, &o, sizeof o) == 0) {
+                rt_context* c = entries[i].c;
+                entries.erase(entries.begin() + i);
+                return c;
+            }
+        return nullptr;
+    }
+    void put(const rt_scene* s, const rt_render_opts& o, rt_context* c) {
+        rt_context* evict = nullptr;
+        {
+            std::lock_guard<std::mutex> g(mu);
+            entries.push_back({s, o, c});
+            if (entries.size() > 2) { evict = entries.front().c; entries.erase(entries.begin()); }
+        }
+        delete evict;
+    }
+    void drop(const rt_scene* s) {  // s == nullptr: everything
+        std::vector<rt_context*> dead;
+        {
+            std::lock_guard<std::mutex> g(mu);
+            for (size_t i = 0; i < entries.size();)
+                if (!s || entries[i].scene == s) { dead.push_back(entries[i].c); entries.erase(entries.begin() + i); }
+                else i++;
+        }
+        for (rt_context* c : dead) delete c;
+    }
+};
+ContextCache g_context_cache;
+}  // namespace
+
+extern "C" {
+
 int rt_render(const rt_scene* s, const rt_render_opts* o, uint8_t* bgr_rows, int32_t* primary_ids, double* accum, rt_stats* stats) {
     if (!s || !o) { set_error("rt_render: null argument"); return RT_ERR_INVALID; }
     if (o->world != 1) { set_error("rt_render renders whole frames on one GPU: world must be 1 (rt_render_multi shards a frame over GPUs)"); return RT_ERR_INVALID; }
-    rt_context* c = nullptr;
-    int rc = rt_context_create(s, o, &c);
-    if (rc != RT_OK) return rc;
+    rt_render_opts key;
+    std::memset(&key, 0, sizeof key);  // padding bytes too: the key is compared with memcmp
+    key = *o;
+    rt_context* c = g_context_cache.take(s, key);
+    double built_ms = 0.0;  // a build done for the kept context that then could not serve the scene still happened in this call
+    if (c) {
+        if (ctx_rebind_scene(c, s, &built_ms) != RT_OK) { delete c; c = nullptr; }  // cannot serve the scene as it is now: make a new one
+        else c->stats.device_driven_overflows = 0;                                  // a count per call, as with a fresh context
+    }
+    int rc = RT_OK;
+    if (!c) {
+        rc = rt_context_create(s, o, &c);
+        if (rc != RT_OK) return rc;
+        if (built_ms > 0.0 && c->stats.bvh_build_ms == 0.0) c->stats.bvh_build_ms = built_ms;
+    }
     rc = rt_context_render(c, stats);
     if (rc == RT_OK) {
         // world == 1: local rows are the image rows (plus band padding at the end, which is not copied)
@@ -1072,7 +1135,12 @@ int rt_render(const rt_scene* s, const rt_render_opts* o, uint8_t* bgr_rows, int
         if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
         if (e != cudaSuccess) { set_error(std::string("copy back: ") + cudaGetErrorString(e)); rc = RT_ERR_CUDA; }
     }
-    rt_context_destroy(c);
+    if (rc == RT_OK) g_context_cache.put(s, key, c);
+    else {
+        const std::string keep = get_error();
+        rt_context_destroy(c);
+        set_error(keep);
+    }
     return rc;
 }
 
@@ -1424,7 +1492,9 @@ namespace {
 // current revision (uploaded and built now if the scene changed since), camera and background.  Returns RT_ERR_UNSUPPORTED
 // when the context cannot serve the scene as it is now (frame size, branching factor or light count differ from what its
 // queues were sized for): the caller makes a new one.
-int ctx_rebind_scene(rt_context* c, const rt_scene* s) {
+// built_ms: receives the BVH build time when this call had to upload and build the scene -- also when it then finds that the
+// context cannot serve the scene (the device copy stays with the scene: the context made in its place will find it ready)
+int ctx_rebind_scene(rt_context* c, const rt_scene* s, double* built_ms) {
     CUDA_TRY(cudaSetDevice(c->device));
     FrameParams fp{};
     int rc = make_frame_params(s, &c->opts, &fp);
@@ -1434,6 +1504,7 @@ int ctx_rebind_scene(rt_context* c, const rt_scene* s) {
     bool fresh = false;
     rc = acquire_device_scene(s, c->opts.accel, c->opts.tuning, c->device, c->stream, &h, &fresh);
     if (rc != RT_OK) return rc;
+    if (built_ms && fresh) *built_ms = h->bvh_ms;
     if (h->use_bvh != c->use_bvh || h->ds.max_children != c->ds.max_children || h->ds.n_lights != c->ds.n_lights) {
         set_error("scene structure changed");
         return RT_ERR_UNSUPPORTED;
@@ -1504,8 +1575,8 @@ struct MultiCache {
 MultiCache g_multi_cache;
 struct MultiCacheHook {
     MultiCacheHook() {
-        rt::g_scene_free_hook = [](const rt_scene* s) { g_multi_cache.drop(s); };
-        g_drop_cached_multi = [] { g_multi_cache.drop(nullptr); };
+        rt::g_scene_free_hook = [](const rt_scene* s) { g_multi_cache.drop(s); g_context_cache.drop(s); };
+        g_drop_cached_multi = [] { g_multi_cache.drop(nullptr); g_context_cache.drop(nullptr); };
     }
 } g_multi_cache_hook;
 
